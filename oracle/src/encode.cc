@@ -1,0 +1,304 @@
+// ORACLE (test infrastructure) — restates encode.ts and enc-constants.ts, and exports the
+// C entry points the tests and bench.py's cpu_baseline bind with ctypes.
+#include "common.h"
+#include "bit_writer.h"
+#include "command.h"
+#include "entropy.h"
+#include "metablock.h"
+#include "greedy.h"
+#include "zopfli.h"
+#include <memory>
+#include <thread>
+#include <atomic>
+
+namespace oracle {
+
+// enc-constants.ts:86-97, 209-233 (only the fields the live code reads)
+struct EncoderParams { int mode = 0, quality = 11, lgwin = 22, lgblock = 0; uint32_t npostfix = 0, ndirect = 0; };
+
+// encode.ts:57-71 + enc-constants.ts:111-127 (clamp, never reject; FONT acts at q >= 4)
+static EncoderParams MakeParams(int quality, int lgwin, int mode) {
+  EncoderParams p;
+  p.quality = std::max(0, std::min(11, quality));
+  p.lgwin = std::max(10, std::min(24, lgwin));
+  p.mode = mode;
+  if (p.quality >= 4 && p.mode == 2) { p.npostfix = 1; p.ndirect = 12; }
+  // enc-constants.ts:129-147 computeLgBlock (params.lgblock is always 0 on entry)
+  if (p.quality == 0 || p.quality == 1) p.lgblock = p.lgwin;
+  else if (p.quality < 4) p.lgblock = 14;
+  else { p.lgblock = 16; if (p.quality >= 9 && p.lgwin > p.lgblock) p.lgblock = std::min(18, p.lgwin); }
+  return p;
+}
+static inline uint32_t DistanceAlphabetSize(const EncoderParams& p) { return 16 + p.ndirect + (48u << p.npostfix); }  // encode.ts:283-287
+
+// encode.ts:92-103
+static std::vector<uint8_t> EncodeEmptyInput() {
+  BitWriter w(16); unsigned bits, value;
+  EncodeWindowBits(10, &bits, &value);
+  w.writeBits(bits, value); w.writeBits(1, 1); w.writeBits(1, 1); w.alignToByte();
+  return w.finish();
+}
+// encode.ts:105-138
+static std::vector<uint8_t> EncodeUncompressed(const uint8_t* in, size_t n) {
+  BitWriter w(n + 32);
+  int lgwin = std::max(10, std::min(24, n <= 1 ? 10 : (int)std::ceil(std::log2((double)n)) + 1));
+  unsigned bits, value; EncodeWindowBits(lgwin, &bits, &value);
+  w.writeBits(bits, value);
+  const size_t maxBlock = ((size_t)1 << 24) - 1;
+  size_t pos = 0;
+  while (pos < n) {
+    size_t bs = std::min(n - pos, maxBlock);
+    StoreUncompressedMetaBlock(w, in, pos, bs, pos + bs >= n);
+    pos += bs;
+  }
+  return w.finish();
+}
+
+// encode.ts:250-267 trailing-insert merge
+static void MergeTrailingInsert(std::vector<Command>& commands, uint32_t lastInsertLen, size_t metablockLen) {
+  if (lastInsertLen > 0) {
+    if (commands.empty()) commands.push_back(CreateInsertCommand((uint32_t)metablockLen));
+    else {
+      Command& last = commands.back();
+      if (CommandCopyLen(last) == 0) last.insertLen += lastInsertLen;
+      else commands.push_back(CreateInsertCommand(lastInsertLen));
+    }
+  } else if (commands.empty()) commands.push_back(CreateInsertCommand((uint32_t)metablockLen));
+}
+
+// Commands for one metablock of a one-shot encode (encode.ts:213-267), any quality >= 5.
+static void OneShotCommands(const Bytes& data, size_t pos, size_t metablockLen, const EncoderParams& p, size_t mask,
+                            HashChainHasher* hc, BinaryTreeHasher* bt, int32_t* distCache, std::vector<Command>& commands) {
+  size_t numLiterals = 0; uint32_t lastInsertLen = 0;
+  if (p.quality >= 11) CreateHqZopfliBackwardReferences(metablockLen, pos, data, mask, *bt, distCache, 0, p.npostfix, p.ndirect, commands, &numLiterals, &lastInsertLen);
+  else if (p.quality >= 10) CreateZopfliBackwardReferences(metablockLen, pos, data, mask, p.quality, *bt, distCache, 0, p.npostfix, p.ndirect, commands, &numLiterals, &lastInsertLen);
+  else CreateBackwardReferences(metablockLen, pos, data, mask, *hc, distCache, 0, p.npostfix, p.ndirect, commands, &numLiterals, &lastInsertLen);
+  MergeTrailingInsert(commands, lastInsertLen, metablockLen);
+}
+
+// encode.ts:181-281.  forceTrivial selects storeMetaBlockTrivial for stage-parity tests.
+static std::vector<uint8_t> EncodeStandard(const uint8_t* in, size_t n, const EncoderParams& p, bool forceTrivial, MetaBlockStats* stats) {
+  BitWriter w(std::max<size_t>(1024, (size_t)((double)n * 1.2)));
+  unsigned bits, value; EncodeWindowBits(p.lgwin, &bits, &value);
+  w.writeBits(bits, value);
+  std::unique_ptr<HashChainHasher> hc; std::unique_ptr<BinaryTreeHasher> bt;
+  if (p.quality <= 9) hc.reset(CreateHashChainHasher(p.quality, p.lgwin));
+  else bt.reset(new BinaryTreeHasher(p.lgwin, n));
+  int32_t distCache[16] = {4, 11, 15, 16};
+  size_t mask = ((size_t)1 << p.lgwin) - 1;
+  Bytes data{in, n};
+  const size_t maxMetablock = (size_t)1 << 24;
+  size_t pos = 0;
+  while (pos < n) {
+    size_t mlen = std::min(n - pos, maxMetablock);
+    bool isLast = pos + mlen >= n;
+    std::vector<Command> commands;
+    OneShotCommands(data, pos, mlen, p, mask, hc.get(), bt.get(), distCache, commands);
+    if (forceTrivial) StoreMetaBlockTrivial(w, in, pos, mlen, mask, isLast, commands, DistanceAlphabetSize(p), p.npostfix, p.ndirect);
+    else StoreMetaBlock(w, data, pos, mlen, mask, isLast, commands, DistanceAlphabetSize(p), p.quality, p.npostfix, p.ndirect, 0, 0, stats);
+    pos += mlen;
+  }
+  return w.finish();
+}
+
+// encode.ts:50-90
+static int BrotliEncode(const uint8_t* in, size_t n, int quality, int lgwin, int mode, bool forceTrivial,
+                        std::vector<uint8_t>& out, MetaBlockStats* stats = nullptr) {
+  EncoderParams p = MakeParams(quality, lgwin, mode);
+  if (n == 0) { out = EncodeEmptyInput(); return 0; }
+  if (p.quality == 0 || n < 64) { out = EncodeUncompressed(in, n); return 0; }
+  if (p.quality < 5) return -2;  // q1-4 (SimpleHasher / encodeFast) are outside the hot path
+  out = EncodeStandard(in, n, p, forceTrivial, stats);
+  return 0;
+}
+
+// encode.ts:290-490 streaming encoder (always trivial metablocks, :471-475)
+class BrotliEncoder {
+ public:
+  EncoderParams p; std::vector<uint8_t> ring; size_t mask; int32_t distCache[16] = {4, 11, 15, 16};
+  std::unique_ptr<HashChainHasher> hc; std::unique_ptr<BinaryTreeHasher> bt;
+  size_t inputPos = 0, lastProcessedPos = 0; bool initialized = false, lastEmitted = false;
+  BitWriter w; std::vector<uint8_t> outBuf;
+  BrotliEncoder(int quality, int lgwin, int mode) : p(MakeParams(quality, lgwin, mode)), ring((size_t)1 << p.lgwin, 0), mask(ring.size() - 1), w(4096) {}
+  void initialize() {
+    if (initialized) return;
+    unsigned bits, value; EncodeWindowBits(p.lgwin, &bits, &value);
+    w.writeBits(bits, value);
+    if (p.quality <= 9) hc.reset(CreateHashChainHasher(std::max(p.quality, 5), p.lgwin));
+    else bt.reset(new BinaryTreeHasher(p.lgwin, (size_t)1 << p.lgwin));
+    initialized = true;
+  }
+  void append(const std::vector<uint8_t>& v) { outBuf.insert(outBuf.end(), v.begin(), v.end()); }
+  void processBlock(size_t blockLen, bool isLast) {
+    size_t pos = lastProcessedPos;
+    Bytes data{ring.data(), ring.size()};
+    std::vector<Command> commands; size_t numLiterals = 0; uint32_t lastInsertLen = 0;
+    if (hc) CreateBackwardReferences(blockLen, pos, data, mask, *hc, distCache, 0, p.npostfix, p.ndirect, commands, &numLiterals, &lastInsertLen);
+    else if (p.quality >= 11) CreateHqZopfliBackwardReferences(blockLen, pos, data, mask, *bt, distCache, 0, p.npostfix, p.ndirect, commands, &numLiterals, &lastInsertLen);
+    else CreateZopfliBackwardReferences(blockLen, pos, data, mask, p.quality, *bt, distCache, 0, p.npostfix, p.ndirect, commands, &numLiterals, &lastInsertLen);
+    MergeTrailingInsert(commands, lastInsertLen, blockLen);
+    StoreMetaBlockTrivial(w, ring.data(), pos, blockLen, mask, isLast, commands, DistanceAlphabetSize(p), p.npostfix, p.ndirect);
+    lastProcessedPos += blockLen;
+    if (isLast) lastEmitted = true;
+    append(w.takeBytes());
+  }
+  void update(const uint8_t* in, size_t n) {
+    initialize();
+    for (size_t i = 0; i < n; i++) ring[(inputPos + i) & mask] = in[i];
+    inputPos += n;
+    size_t blockSize = (size_t)1 << p.lgblock;
+    while (inputPos - lastProcessedPos >= blockSize) processBlock(blockSize, false);
+  }
+  void finish() {
+    initialize();
+    size_t remaining = inputPos - lastProcessedPos;
+    if (remaining > 0) { processBlock(remaining, true); return; }
+    if (!lastEmitted) { w.writeBits(1, 1); w.writeBits(1, 1); w.alignToByte(); lastEmitted = true; }
+    append(w.takeBytes());
+  }
+};
+
+}  // namespace oracle
+
+using namespace oracle;
+
+extern "C" {
+
+int oracle_encode(const uint8_t* in, size_t n, int quality, int lgwin, int mode, int force_trivial,
+                  uint8_t* out, size_t cap, size_t* out_len) {
+  std::vector<uint8_t> v;
+  int rc = BrotliEncode(in, n, quality, lgwin, mode, force_trivial != 0, v);
+  if (rc) return rc;
+  *out_len = v.size();
+  if (v.size() > cap) return -1;
+  memcpy(out, v.data(), v.size());
+  return 0;
+}
+
+// stats[0..6] = trivial, litTypes, cmdTypes, distTypes, litClusters, distClusters, contextMode
+int oracle_encode_stats(const uint8_t* in, size_t n, int quality, int lgwin, int mode, size_t* out_len, int* stats) {
+  std::vector<uint8_t> v; MetaBlockStats s;
+  int rc = BrotliEncode(in, n, quality, lgwin, mode, false, v, &s);
+  if (rc) return rc;
+  *out_len = v.size();
+  stats[0] = s.trivial; stats[1] = s.litTypes; stats[2] = s.cmdTypes; stats[3] = s.distTypes;
+  stats[4] = s.litClusters; stats[5] = s.distClusters; stats[6] = s.contextMode;
+  return 0;
+}
+
+// Encode `count` independent shards on `threads` host threads (CPU-baseline helper).
+// Returns the total compressed size in *total_out; out buffers are discarded.
+int oracle_encode_shards(const uint8_t* in, size_t n, size_t shard, int quality, int lgwin, int mode, int threads, size_t* total_out) {
+  size_t count = (n + shard - 1) / shard;
+  std::atomic<size_t> next(0), total(0); std::atomic<int> err(0);
+  auto work = [&]() {
+    for (;;) {
+      size_t i = next.fetch_add(1);
+      if (i >= count) break;
+      size_t off = i * shard, len = std::min(shard, n - off);
+      std::vector<uint8_t> v;
+      int rc = BrotliEncode(in + off, len, quality, lgwin, mode, false, v);
+      if (rc) err = rc;
+      total += v.size();
+    }
+  };
+  std::vector<std::thread> th;
+  for (int t = 1; t < threads; t++) th.emplace_back(work);
+  work();
+  for (auto& t : th) t.join();
+  *total_out = total;
+  return err;
+}
+
+// hash-chains.ts chain part alone ("candidate-exact" stage): for every position p with at
+// least 4 bytes left, the result of findLongestMatch with an empty distance cache, all
+// earlier positions stored, maxLength = min(n-p, 128), maxBackward = min(p, 4M-16).
+int oracle_h5_chain_best(const uint8_t* in, size_t n, int quality, int lgwin, uint32_t* len, uint32_t* dist) {
+  std::unique_ptr<HashChainHasher> h(CreateHashChainHasher(quality, lgwin));
+  h->numLastDistancesToCheck = 0;
+  Bytes data{in, n}; size_t mask = ((size_t)1 << lgwin) - 1;
+  int32_t dc[16] = {0};
+  for (size_t p = 0; p < n; p++) { len[p] = 0; dist[p] = 0; }
+  for (size_t p = 0; p + 4 <= n; p++) {
+    HasherSearchResult r;
+    h->findLongestMatch(data, mask, dc, p, (uint32_t)std::min<size_t>(n - p, 128), std::min<size_t>(p, ((size_t)1 << 22) - 16), r);
+    len[p] = r.len; dist[p] = r.distance;
+  }
+  return 0;
+}
+
+// Commands of the one-shot encode of a single-metablock input (encode.ts:213-267).
+int oracle_commands(const uint8_t* in, size_t n, int quality, int lgwin, int mode, Command* cmds, size_t cap, size_t* ncmd) {
+  EncoderParams p = MakeParams(quality, lgwin, mode);
+  if (p.quality < 5 || n == 0 || n > ((size_t)1 << 24)) return -2;
+  std::unique_ptr<HashChainHasher> hc; std::unique_ptr<BinaryTreeHasher> bt;
+  if (p.quality <= 9) hc.reset(CreateHashChainHasher(p.quality, p.lgwin)); else bt.reset(new BinaryTreeHasher(p.lgwin, n));
+  int32_t distCache[16] = {4, 11, 15, 16};
+  std::vector<Command> commands;
+  OneShotCommands(Bytes{in, n}, 0, n, p, ((size_t)1 << p.lgwin) - 1, hc.get(), bt.get(), distCache, commands);
+  *ncmd = commands.size();
+  if (commands.size() > cap) return -1;
+  memcpy(cmds, commands.data(), commands.size() * sizeof(Command));
+  return 0;
+}
+
+// storeMetaBlockTrivial on caller-supplied commands, preceded by `start_nbits` header bits
+// (start_value, LSB-first) — the window header for shard 0, nothing for later shards.
+// tables (may be NULL): lit/cmd/dist histograms, depths and codes as laid out in TrivialTables.
+int oracle_store_trivial(const uint8_t* in, size_t n, const Command* cmds, size_t ncmd, int is_last, int mode_font,
+                         unsigned start_nbits, unsigned start_value, uint8_t* out, size_t cap, size_t* out_len, uint64_t* out_bits,
+                         TrivialTables* tables) {
+  uint32_t npostfix = mode_font ? 1 : 0, ndirect = mode_font ? 12 : 0;
+  BitWriter w(n + 1024);
+  w.writeBits(start_nbits, start_value);
+  std::vector<Command> commands(cmds, cmds + ncmd);
+  StoreMetaBlockTrivial(w, in, 0, n, ~(size_t)0, is_last != 0, commands, 16 + ndirect + (48u << npostfix), npostfix, ndirect, tables);
+  *out_bits = w.pos;
+  std::vector<uint8_t> v = w.finish();
+  *out_len = v.size();
+  if (v.size() > cap) return -1;
+  memcpy(out, v.data(), v.size());
+  return 0;
+}
+
+int oracle_huffman(const uint32_t* hist, size_t n, int tree_limit, uint8_t* depths, uint16_t* bits) {
+  CreateHuffmanTree(hist, n, tree_limit, depths, bits);
+  return 0;
+}
+
+// buildAndStoreHuffmanTree alone: serialised tree bits + the code it defines.
+int oracle_build_store_tree(const uint32_t* hist, size_t n, uint8_t* depths, uint16_t* bits, uint8_t* out, size_t cap, uint64_t* out_bits) {
+  BitWriter w(1024);
+  memset(depths, 0, n); memset(bits, 0, 2 * n);
+  BuildAndStoreHuffmanTree(w, hist, n, depths, bits);
+  *out_bits = w.pos;
+  std::vector<uint8_t> v = w.finish();
+  if (v.size() > cap) return -1;
+  memcpy(out, v.data(), v.size());
+  return 0;
+}
+
+const uint8_t* oracle_context_lut(void) { return ContextLookupTable(); }
+const double* oracle_log2_table(void) { return kLog2Table(); }
+
+void* oracle_stream_create(int quality, int lgwin, int mode) {
+  EncoderParams p = MakeParams(quality, lgwin, mode);
+  if (p.quality >= 1 && p.quality < 5) return nullptr;
+  return new BrotliEncoder(quality, lgwin, mode);
+}
+// Returns the bytes completed by this call; the pointer is valid until the next call.
+int oracle_stream_update(void* s, const uint8_t* in, size_t n, const uint8_t** out, size_t* out_len) {
+  BrotliEncoder* e = (BrotliEncoder*)s;
+  e->outBuf.clear(); e->update(in, n);
+  *out = e->outBuf.data(); *out_len = e->outBuf.size();
+  return 0;
+}
+int oracle_stream_finish(void* s, const uint8_t** out, size_t* out_len) {
+  BrotliEncoder* e = (BrotliEncoder*)s;
+  e->outBuf.clear(); e->finish();
+  *out = e->outBuf.data(); *out_len = e->outBuf.size();
+  return 0;
+}
+void oracle_stream_destroy(void* s) { delete (BrotliEncoder*)s; }
+
+}  // extern "C"

@@ -1,0 +1,230 @@
+"""ctypes bindings for the oracle (test infrastructure) and the independent decoders.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs may
+import this module.
+"""
+import ctypes as C
+import os
+import subprocess
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ORACLE_DIR = os.path.join(ROOT, "oracle")
+_LIB = None
+
+
+def build_oracle(force=False):
+    so = os.path.join(ORACLE_DIR, "liboracle.so")
+    srcs = [os.path.join(ORACLE_DIR, "src", f) for f in os.listdir(os.path.join(ORACLE_DIR, "src"))]
+    stale = (not os.path.exists(so)) or any(os.path.getmtime(s) > os.path.getmtime(so) for s in srcs)
+    if force or stale:
+        subprocess.check_call(["make", "-C", ORACLE_DIR, "liboracle.so"], stdout=subprocess.DEVNULL)
+    return so
+
+
+class Command(C.Structure):
+    _fields_ = [("insertLen", C.c_uint32), ("copyLen", C.c_uint32), ("distExtra", C.c_uint32),
+                ("cmdPrefix", C.c_uint16), ("distPrefix", C.c_uint16)]
+
+
+CMD_DTYPE = np.dtype([("insertLen", "<u4"), ("copyLen", "<u4"), ("distExtra", "<u4"),
+                      ("cmdPrefix", "<u2"), ("distPrefix", "<u2")])
+
+TRIVIAL_DTYPE = np.dtype([("litHisto", "<u4", 256), ("cmdHisto", "<u4", 704), ("distHisto", "<u4", 544),
+                          ("litDepths", "u1", 256), ("cmdDepths", "u1", 704), ("distDepths", "u1", 544),
+                          ("litBits", "<u2", 256), ("cmdBits", "<u2", 704), ("distBits", "<u2", 544)])
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        L = C.CDLL(build_oracle())
+        u8p, szp = C.c_void_p, C.POINTER(C.c_size_t)
+        L.oracle_encode.argtypes = [u8p, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, u8p, C.c_size_t, szp]
+        L.oracle_encode_stats.argtypes = [u8p, C.c_size_t, C.c_int, C.c_int, C.c_int, szp, C.POINTER(C.c_int)]
+        L.oracle_encode_shards.argtypes = [u8p, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, szp]
+        L.oracle_h5_chain_best.argtypes = [u8p, C.c_size_t, C.c_int, C.c_int, u8p, u8p]
+        L.oracle_commands.argtypes = [u8p, C.c_size_t, C.c_int, C.c_int, C.c_int, u8p, C.c_size_t, szp]
+        L.oracle_store_trivial.argtypes = [u8p, C.c_size_t, u8p, C.c_size_t, C.c_int, C.c_int, C.c_uint, C.c_uint,
+                                           u8p, C.c_size_t, szp, C.POINTER(C.c_uint64), u8p]
+        L.oracle_huffman.argtypes = [u8p, C.c_size_t, C.c_int, u8p, u8p]
+        L.oracle_build_store_tree.argtypes = [u8p, C.c_size_t, u8p, u8p, u8p, C.c_size_t, C.POINTER(C.c_uint64)]
+        L.oracle_context_lut.restype = C.POINTER(C.c_uint8)
+        L.oracle_log2_table.restype = C.POINTER(C.c_double)
+        L.oracle_stream_create.restype = C.c_void_p
+        L.oracle_stream_create.argtypes = [C.c_int, C.c_int, C.c_int]
+        L.oracle_stream_update.argtypes = [C.c_void_p, u8p, C.c_size_t, C.POINTER(C.c_void_p), szp]
+        L.oracle_stream_finish.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), szp]
+        L.oracle_stream_destroy.argtypes = [C.c_void_p]
+        _LIB = L
+    return _LIB
+
+
+def _buf(data):
+    a = np.frombuffer(bytes(data), dtype=np.uint8) if not isinstance(data, np.ndarray) else np.ascontiguousarray(data, dtype=np.uint8)
+    return a, (a.ctypes.data if a.size else None)
+
+
+def encode(data, quality=11, lgwin=22, mode=0, force_trivial=False):
+    a, p = _buf(data)
+    cap = a.size + a.size // 4 + 4096
+    out = np.empty(cap, dtype=np.uint8)
+    n = C.c_size_t(0)
+    rc = lib().oracle_encode(p, a.size, quality, lgwin, mode, int(force_trivial), out.ctypes.data, cap, C.byref(n))
+    if rc:
+        raise RuntimeError(f"oracle_encode rc={rc}")
+    return out[: n.value].tobytes()
+
+
+def encode_stats(data, quality=11, lgwin=22, mode=0):
+    a, p = _buf(data)
+    n = C.c_size_t(0)
+    st = (C.c_int * 7)()
+    rc = lib().oracle_encode_stats(p, a.size, quality, lgwin, mode, C.byref(n), st)
+    if rc:
+        raise RuntimeError(f"oracle_encode_stats rc={rc}")
+    return n.value, list(st)
+
+
+def encode_shards_total(data, shard, quality, lgwin=22, mode=0, threads=1):
+    a, p = _buf(data)
+    n = C.c_size_t(0)
+    rc = lib().oracle_encode_shards(p, a.size, shard, quality, lgwin, mode, threads, C.byref(n))
+    if rc:
+        raise RuntimeError(f"oracle_encode_shards rc={rc}")
+    return n.value
+
+
+def h5_chain_best(data, quality=5, lgwin=22):
+    a, p = _buf(data)
+    ln = np.zeros(a.size, dtype=np.uint32)
+    ds = np.zeros(a.size, dtype=np.uint32)
+    lib().oracle_h5_chain_best(p, a.size, quality, lgwin, ln.ctypes.data, ds.ctypes.data)
+    return ln, ds
+
+
+def commands(data, quality=5, lgwin=22, mode=0):
+    a, p = _buf(data)
+    cap = a.size // 2 + 16
+    out = np.zeros(cap, dtype=CMD_DTYPE)
+    n = C.c_size_t(0)
+    rc = lib().oracle_commands(p, a.size, quality, lgwin, mode, out.ctypes.data, cap, C.byref(n))
+    if rc:
+        raise RuntimeError(f"oracle_commands rc={rc}")
+    return out[: n.value].copy()
+
+
+def store_trivial(data, cmds, is_last=True, font=False, start_nbits=0, start_value=0):
+    a, p = _buf(data)
+    cmds = np.ascontiguousarray(cmds, dtype=CMD_DTYPE)
+    cap = a.size + a.size // 4 + 4096
+    out = np.zeros(cap, dtype=np.uint8)
+    n = C.c_size_t(0)
+    nb = C.c_uint64(0)
+    tab = np.zeros(1, dtype=TRIVIAL_DTYPE)
+    rc = lib().oracle_store_trivial(p, a.size, cmds.ctypes.data, cmds.size, int(is_last), int(font), start_nbits, start_value,
+                                    out.ctypes.data, cap, C.byref(n), C.byref(nb), tab.ctypes.data)
+    if rc:
+        raise RuntimeError(f"oracle_store_trivial rc={rc}")
+    return out[: n.value].tobytes(), nb.value, tab[0]
+
+
+def huffman(hist, tree_limit=15):
+    h = np.ascontiguousarray(hist, dtype=np.uint32)
+    d = np.zeros(h.size, dtype=np.uint8)
+    b = np.zeros(h.size, dtype=np.uint16)
+    lib().oracle_huffman(h.ctypes.data, h.size, tree_limit, d.ctypes.data, b.ctypes.data)
+    return d, b
+
+
+def build_store_tree(hist):
+    h = np.ascontiguousarray(hist, dtype=np.uint32)
+    d = np.zeros(h.size, dtype=np.uint8)
+    b = np.zeros(h.size, dtype=np.uint16)
+    out = np.zeros(4096, dtype=np.uint8)
+    nb = C.c_uint64(0)
+    rc = lib().oracle_build_store_tree(h.ctypes.data, h.size, d.ctypes.data, b.ctypes.data, out.ctypes.data, out.size, C.byref(nb))
+    if rc:
+        raise RuntimeError("oracle_build_store_tree failed")
+    return d, b, out[: (nb.value + 7) // 8].tobytes(), nb.value
+
+
+class StreamEncoder:
+    def __init__(self, quality=11, lgwin=22, mode=0):
+        self._h = lib().oracle_stream_create(quality, lgwin, mode)
+        if not self._h:
+            raise RuntimeError("unsupported quality for oracle streaming")
+
+    def update(self, chunk):
+        a, p = _buf(chunk)
+        o = C.c_void_p()
+        n = C.c_size_t(0)
+        lib().oracle_stream_update(self._h, p, a.size, C.byref(o), C.byref(n))
+        return C.string_at(o, n.value) if n.value else b""
+
+    def finish(self):
+        o = C.c_void_p()
+        n = C.c_size_t(0)
+        lib().oracle_stream_finish(self._h, C.byref(o), C.byref(n))
+        return C.string_at(o, n.value) if n.value else b""
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().oracle_stream_destroy(self._h)
+            self._h = None
+
+
+# ---------------------------------------------------------------- independent decoders
+_DEC = {}
+
+
+def _decoder(which):
+    if which not in _DEC:
+        if which == "system":
+            L = C.CDLL("libbrotlidec.so.1")
+        else:
+            path = os.path.join(ORACLE_DIR, "_ref", "libbrotli_ref.so")
+            if not os.path.exists(path):
+                if os.path.isdir("/root/reference/bench/vendor/brotli/c"):
+                    subprocess.check_call(["make", "-C", ORACLE_DIR, "ref"], stdout=subprocess.DEVNULL)
+                else:
+                    return None
+            L = C.CDLL(path)
+        L.BrotliDecoderDecompress.argtypes = [C.c_size_t, C.c_void_p, C.POINTER(C.c_size_t), C.c_void_p]
+        L.BrotliDecoderDecompress.restype = C.c_int
+        _DEC[which] = L
+    return _DEC[which]
+
+
+def have_ref_decoder():
+    return _decoder("ref") is not None
+
+
+def decode(stream, max_out, which="system"):
+    """Google C decoder (system libbrotlidec 1.1.0, or the vendored 1.2.0 build under oracle/_ref).
+    Returns bytes or raises ValueError."""
+    L = _decoder(which)
+    if L is None:
+        raise RuntimeError("decoder unavailable: " + which)
+    s = np.frombuffer(bytes(stream), dtype=np.uint8)
+    out = np.empty(max_out + 16, dtype=np.uint8)
+    n = C.c_size_t(out.size)
+    rc = L.BrotliDecoderDecompress(s.size, s.ctypes.data, C.byref(n), out.ctypes.data)
+    if rc != 1:
+        raise ValueError(f"BrotliDecoderDecompress failed rc={rc}")
+    return out[: n.value].tobytes()
+
+
+def ref_encode(data, quality, lgwin=22, mode=0, which="system"):
+    """Google C encoder — context line only, never a parity target."""
+    L = C.CDLL("libbrotlienc.so.1") if which == "system" else _decoder("ref")
+    L.BrotliEncoderCompress.argtypes = [C.c_int, C.c_int, C.c_int, C.c_size_t, C.c_void_p, C.POINTER(C.c_size_t), C.c_void_p]
+    L.BrotliEncoderCompress.restype = C.c_int
+    a, p = _buf(data)
+    cap = a.size + a.size // 4 + 4096
+    out = np.empty(cap, dtype=np.uint8)
+    n = C.c_size_t(cap)
+    rc = L.BrotliEncoderCompress(quality, lgwin, mode, a.size, p, C.byref(n), out.ctypes.data)
+    if rc != 1:
+        raise ValueError("BrotliEncoderCompress failed")
+    return out[: n.value].tobytes()
