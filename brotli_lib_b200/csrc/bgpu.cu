@@ -1,0 +1,721 @@
+// libbrotligpu.so — C ABI (include/brotligpu.h) and host orchestration of the sm_100a kernels.
+// The host side mirrors src/encode/encode.ts:50-287 of the reference: option clamping, the
+// empty/uncompressed special cases (host only), shard splitting and stitching.
+#include "../../include/brotligpu.h"
+#include "kernels.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace bgpu;
+
+static thread_local std::string g_cuda_err;
+
+#define CK(call)                                                                          \
+  do {                                                                                    \
+    cudaError_t e_ = (call);                                                              \
+    if (e_ != cudaSuccess) {                                                              \
+      char b_[512];                                                                       \
+      snprintf(b_, sizeof b_, "%s at %s:%d: %s", #call, __FILE__, __LINE__, cudaGetErrorString(e_)); \
+      g_cuda_err = b_;                                                                    \
+      return e_ == cudaErrorMemoryAllocation ? BGPU_E_NOMEM : BGPU_E_CUDA;                \
+    }                                                                                     \
+  } while (0)
+
+namespace {
+
+struct DBuf {
+  void* p = nullptr; size_t cap = 0;
+  int reserve(size_t n) {
+    if (n <= cap) return 0;
+    if (p) cudaFree(p);
+    p = nullptr; cap = 0;
+    size_t want = n + n / 8 + 4096;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e != cudaSuccess) { g_cuda_err = std::string("cudaMalloc: ") + cudaGetErrorString(e); p = nullptr; return BGPU_E_NOMEM; }
+    cap = want;
+    return 0;
+  }
+  void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+  template <typename T> T* as() const { return reinterpret_cast<T*>(p); }
+};
+
+struct EncParams { int quality, lgwin, mode; Params k; };
+
+// encode.ts:57-71, enc-constants.ts:111-127, hash-chains.ts:240-261
+EncParams make_params(int quality, int lgwin, int mode) {
+  EncParams p;
+  p.quality = std::max(0, std::min(11, quality));
+  p.lgwin = std::max(10, std::min(24, lgwin));
+  p.mode = mode;
+  p.k.npostfix = 0; p.k.ndirect = 0;
+  if (p.quality >= 4 && mode == BGPU_MODE_FONT) { p.k.npostfix = 1; p.k.ndirect = 12; }
+  p.k.dist_alphabet = 16 + p.k.ndirect + (48u << p.k.npostfix);   // encode.ts:283-287
+  int q = std::max(5, std::min(9, p.quality));
+  p.k.bucket_bits = q < 7 ? 14 : 15;
+  p.k.depth = 1 << (q - 1);
+  p.k.num_last = q < 7 ? 4 : (q < 9 ? 10 : 16);
+  p.k.sh = 2;
+  return p;
+}
+
+void window_bits(int lgwin, uint32_t* nbits, uint32_t* value) {  // bit-writer.ts:172-194
+  if (lgwin == 16) { *value = 0; *nbits = 1; }
+  else if (lgwin == 17) { *value = 1; *nbits = 7; }
+  else if (lgwin > 17 && lgwin <= 24) { *value = ((lgwin - 17) << 1) | 1; *nbits = 4; }
+  else { *value = ((lgwin - 8) << 4) | 1; *nbits = 7; }
+}
+
+struct StreamPlan { size_t in_off = 0, len = 0; uint32_t first_shard = 0, n_shard = 0; };
+
+struct Job {
+  std::vector<ShardD> shards; std::vector<MbD> mbs; std::vector<SegD> segs; std::vector<uint32_t> tile_seg;
+  std::vector<StreamPlan> streams;
+  size_t in_bytes = 0, out_bytes = 0;
+};
+
+constexpr size_t IN_PAD = 1024;
+
+}  // namespace
+
+struct bgpu_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  bgpu_tuning tune{0, 0, 0, 0};
+  DBuf in, link, best, role, ins, cmds, out, shards, mbs, segs, tile_seg, seg_ncmd, seg_trail, hist, codes, tree_bits, tree_nbits,
+      tile_bits, tile_off, shard_bytes, huff_meta;
+  std::vector<uint32_t> h_shard_bytes;
+  // timings
+  static const int kMaxStages = 16;
+  cudaEvent_t ev[kMaxStages + 1]; const char* names[kMaxStages]; float ms[kMaxStages]; int n_stage = 0; int launches = 0;
+  bool ev_ok = false;
+};
+
+namespace {
+
+uint32_t eff(uint32_t v, uint32_t dflt) { return v ? v : dflt; }
+
+// Splits every stream into shards / metablocks / parse segments / tiles.
+void plan_job(const bgpu_ctx* ctx, const EncParams& P, const size_t* lens, int count, Job& job) {
+  uint32_t shard_bytes = std::min<uint32_t>(eff(ctx->tune.shard_bytes, 1u << 22), 1u << 22);
+  if (P.lgwin < 22) shard_bytes = std::min<uint32_t>(shard_bytes, ((1u << P.lgwin) - 16) & ~3u);
+  shard_bytes = std::max<uint32_t>(shard_bytes & ~3u, 64);
+  uint32_t seg_bytes = eff(ctx->tune.segment_bytes, 1u << 16);
+  seg_bytes = seg_bytes >= shard_bytes ? shard_bytes : std::max<uint32_t>(seg_bytes & ~(TILE - 1), TILE);
+  uint32_t mb_bytes = eff(ctx->tune.metablock_bytes, shard_bytes);
+  mb_bytes = mb_bytes >= shard_bytes ? shard_bytes : std::max<uint32_t>((mb_bytes / seg_bytes) * seg_bytes, seg_bytes);
+  uint32_t wb_n, wb_v; window_bits(P.lgwin, &wb_n, &wb_v);
+  size_t in_off = 0, out_off = 0;
+  for (int s = 0; s < count; s++) {
+    StreamPlan sp; sp.in_off = in_off; sp.len = lens[s]; sp.first_shard = (uint32_t)job.shards.size();
+    size_t n = lens[s];
+    for (size_t so = 0; so < n; so += shard_bytes) {
+      ShardD sh; memset(&sh, 0, sizeof sh);
+      sh.in_off = in_off + so; sh.len = (uint32_t)std::min<size_t>(shard_bytes, n - so);
+      sh.flags = (so == 0 ? 1u : 0u) | (so + shard_bytes >= n ? 2u : 0u);
+      sh.start_nbits = wb_n; sh.start_value = wb_v;
+      sh.first_mb = (uint32_t)job.mbs.size();
+      uint32_t shard_idx = (uint32_t)job.shards.size();
+      for (uint32_t mo = 0; mo < sh.len; mo += mb_bytes) {
+        MbD mb; memset(&mb, 0, sizeof mb);
+        mb.shard = shard_idx; mb.rel_pos = mo; mb.len = std::min(mb_bytes, sh.len - mo);
+        mb.first_seg = (uint32_t)job.segs.size(); mb.first_tile = (uint32_t)job.tile_seg.size();
+        mb.is_last = ((sh.flags & 2) && mo + mb_bytes >= sh.len) ? 1 : 0;
+        uint32_t mb_idx = (uint32_t)job.mbs.size();
+        for (uint32_t go = 0; go < mb.len; go += seg_bytes) {
+          SegD sg; memset(&sg, 0, sizeof sg);
+          sg.shard = shard_idx; sg.rel_pos = mo + go; sg.len = std::min(seg_bytes, mb.len - go); sg.mb = mb_idx;
+          sg.first_tile = (uint32_t)job.tile_seg.size();
+          sg.ring_known = (so == 0 && mo == 0 && go == 0) ? 1 : 0;   // encode.ts:202 {4,11,15,16} only at stream start
+          uint32_t seg_idx = (uint32_t)job.segs.size();
+          for (uint32_t to = 0; to < sg.len; to += TILE) job.tile_seg.push_back(seg_idx);
+          job.segs.push_back(sg);
+        }
+        mb.n_seg = (uint32_t)job.segs.size() - mb.first_seg; mb.n_tile = (uint32_t)job.tile_seg.size() - mb.first_tile;
+        job.mbs.push_back(mb);
+      }
+      sh.n_mb = (uint32_t)job.mbs.size() - sh.first_mb;
+      sh.out_off = out_off;
+      sh.out_cap = (uint32_t)(2 * (size_t)sh.len + 4096 + (size_t)sh.n_mb * 2048);
+      sh.out_cap = (sh.out_cap + 255) & ~255u;
+      out_off += sh.out_cap;
+      job.shards.push_back(sh);
+    }
+    sp.n_shard = (uint32_t)job.shards.size() - sp.first_shard;
+    job.streams.push_back(sp);
+    in_off += (n + 255) & ~(size_t)255;
+  }
+  job.in_bytes = in_off; job.out_bytes = out_off;
+}
+
+int upload(bgpu_ctx* ctx, DBuf& b, const void* src, size_t bytes) {
+  int rc = b.reserve(bytes ? bytes : 16);
+  if (rc) return rc;
+  if (bytes) CK(cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  return 0;
+}
+
+void stage_mark(bgpu_ctx* ctx, const char* name) {
+  if (!ctx->ev_ok || ctx->n_stage >= bgpu_ctx::kMaxStages) return;
+  ctx->names[ctx->n_stage] = name;
+  cudaEventRecord(ctx->ev[ctx->n_stage + 1], ctx->stream);
+  ctx->n_stage++;
+}
+
+// Entropy back end (K7 -> K10 -> K11) over roles/commands already on the device.
+int run_backend(bgpu_ctx* ctx, const Job& job, const EncParams& P, const uint8_t* d_in) {
+  cudaStream_t st = ctx->stream;
+  const uint32_t n_tile = (uint32_t)job.tile_seg.size(), n_mb = (uint32_t)job.mbs.size(), n_shard = (uint32_t)job.shards.size();
+  int rc;
+  if ((rc = ctx->hist.reserve((size_t)n_mb * sizeof(MbHist)))) return rc;
+  if ((rc = ctx->codes.reserve((size_t)n_mb * CODE_STRIDE * 4))) return rc;
+  if ((rc = ctx->tree_bits.reserve((size_t)n_mb * 3 * TREE_WORDS * 4))) return rc;
+  if ((rc = ctx->tree_nbits.reserve((size_t)n_mb * 3 * 4))) return rc;
+  if ((rc = ctx->tile_bits.reserve((size_t)n_tile * 4))) return rc;
+  if ((rc = ctx->tile_off.reserve((size_t)n_tile * 4))) return rc;
+  if ((rc = ctx->shard_bytes.reserve((size_t)n_shard * 4))) return rc;
+  if ((rc = ctx->out.reserve(job.out_bytes + 64))) return rc;
+  int meta[6] = {ALPHA_LIT, ALPHA_CMD, (int)P.k.dist_alphabet, 0, ALPHA_LIT, ALPHA_LIT + ALPHA_CMD};
+  if ((rc = upload(ctx, ctx->huff_meta, meta, sizeof meta))) return rc;
+  CK(cudaMemsetAsync(ctx->hist.p, 0, (size_t)n_mb * sizeof(MbHist), st));
+  CK(cudaMemsetAsync(ctx->out.p, 0, job.out_bytes + 64, st));
+  const ShardD* d_sh = ctx->shards.as<ShardD>(); const MbD* d_mb = ctx->mbs.as<MbD>(); const SegD* d_sg = ctx->segs.as<SegD>();
+  const uint32_t* d_ts = ctx->tile_seg.as<uint32_t>();
+  k_hist<<<(n_tile + 7) / 8, 256, 0, st>>>(d_in, d_sh, d_sg, d_ts, n_tile, ctx->role.as<uint8_t>(), ctx->ins.as<uint32_t>(),
+                                           ctx->cmds.as<Cmd>(), ctx->hist.as<MbHist>(), P.k);
+  ctx->launches++; stage_mark(ctx, "k_hist");
+  k_huff<<<n_mb * 3, 128, 0, st>>>(ctx->hist.as<uint32_t>(), CODE_STRIDE, 3, ctx->huff_meta.as<int>(), ctx->huff_meta.as<int>() + 3,
+                                   ctx->codes.as<uint32_t>(), ctx->tree_bits.as<uint32_t>(), ctx->tree_nbits.as<uint32_t>());
+  ctx->launches++; stage_mark(ctx, "k_huff");
+  k_tilebits<<<n_tile, 256, 0, st>>>(d_in, d_sh, d_sg, d_ts, ctx->role.as<uint8_t>(), ctx->ins.as<uint32_t>(), ctx->cmds.as<Cmd>(),
+                                     ctx->codes.as<uint32_t>(), ctx->tile_bits.as<uint32_t>(), P.k);
+  ctx->launches++; stage_mark(ctx, "k_tilebits");
+  k_offsets<<<n_shard, 256, 0, st>>>(d_sh, d_mb, ctx->tile_bits.as<uint32_t>(), ctx->tile_off.as<uint32_t>(), ctx->tree_bits.as<uint32_t>(),
+                                     ctx->tree_nbits.as<uint32_t>(), ctx->out.as<uint8_t>(), ctx->shard_bytes.as<uint32_t>(), P.k);
+  ctx->launches++; stage_mark(ctx, "k_offsets");
+  k_write<<<n_tile, 256, 0, st>>>(d_in, d_sh, d_sg, d_ts, ctx->role.as<uint8_t>(), ctx->ins.as<uint32_t>(), ctx->cmds.as<Cmd>(),
+                                  ctx->codes.as<uint32_t>(), ctx->tile_bits.as<uint32_t>(), ctx->tile_off.as<uint32_t>(),
+                                  ctx->out.as<uint8_t>(), P.k);
+  ctx->launches++; stage_mark(ctx, "k_write");
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int upload_plan(bgpu_ctx* ctx, const Job& job) {
+  int rc;
+  if ((rc = upload(ctx, ctx->shards, job.shards.data(), job.shards.size() * sizeof(ShardD)))) return rc;
+  if ((rc = upload(ctx, ctx->mbs, job.mbs.data(), job.mbs.size() * sizeof(MbD)))) return rc;
+  if ((rc = upload(ctx, ctx->segs, job.segs.data(), job.segs.size() * sizeof(SegD)))) return rc;
+  if ((rc = upload(ctx, ctx->tile_seg, job.tile_seg.data(), job.tile_seg.size() * 4))) return rc;
+  return 0;
+}
+
+int reserve_front(bgpu_ctx* ctx, const Job& job, const EncParams& P) {
+  int rc; size_t N = job.in_bytes + IN_PAD;
+  if ((rc = ctx->role.reserve(N))) return rc;
+  if ((rc = ctx->ins.reserve(((N >> P.k.sh) + 4) * 4))) return rc;
+  if ((rc = ctx->cmds.reserve(((N >> P.k.sh) + 4) * sizeof(Cmd)))) return rc;
+  return 0;
+}
+
+// Match finding + parse (K2, K3, K5, stitch).
+int run_frontend(bgpu_ctx* ctx, const Job& job, const EncParams& P, const uint8_t* d_in) {
+  cudaStream_t st = ctx->stream;
+  int rc; size_t N = job.in_bytes + IN_PAD;
+  const uint32_t n_tile = (uint32_t)job.tile_seg.size(), n_mb = (uint32_t)job.mbs.size(), n_shard = (uint32_t)job.shards.size(),
+                 n_seg = (uint32_t)job.segs.size();
+  if ((rc = ctx->link.reserve(N * 4))) return rc;
+  if ((rc = ctx->best.reserve(N * 4))) return rc;
+  if ((rc = reserve_front(ctx, job, P))) return rc;
+  if ((rc = ctx->seg_ncmd.reserve((size_t)n_seg * 4))) return rc;
+  if ((rc = ctx->seg_trail.reserve((size_t)n_seg * 4))) return rc;
+  const ShardD* d_sh = ctx->shards.as<ShardD>(); const MbD* d_mb = ctx->mbs.as<MbD>(); const SegD* d_sg = ctx->segs.as<SegD>();
+  const uint32_t* d_ts = ctx->tile_seg.as<uint32_t>();
+  size_t smem = (size_t)4 << P.k.bucket_bits;
+  CK(cudaFuncSetAttribute(k_link, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  k_link<<<n_shard, 32, smem, st>>>(d_in, d_sh, ctx->link.as<uint32_t>(), P.k.bucket_bits);
+  ctx->launches++; stage_mark(ctx, "k_link");
+  k_probe<<<n_tile, 256, 0, st>>>(d_in, d_sh, d_sg, d_ts, ctx->link.as<uint32_t>(), ctx->best.as<uint32_t>(), P.k.depth);
+  ctx->launches++; stage_mark(ctx, "k_probe");
+  CK(cudaMemsetAsync(ctx->role.p, 0, N, st));
+  k_parse<<<(n_seg + 3) / 4, 128, 0, st>>>(d_in, d_sh, d_sg, n_seg, ctx->best.as<uint32_t>(), ctx->role.as<uint8_t>(), ctx->ins.as<uint32_t>(),
+                                           ctx->cmds.as<Cmd>(), ctx->seg_ncmd.as<uint32_t>(), ctx->seg_trail.as<uint32_t>(), P.k);
+  ctx->launches++; stage_mark(ctx, "k_parse");
+  k_stitch<<<(n_mb + 63) / 64, 64, 0, st>>>(d_sh, d_mb, d_sg, n_mb, ctx->role.as<uint8_t>(), ctx->ins.as<uint32_t>(), ctx->cmds.as<Cmd>(),
+                                            ctx->seg_ncmd.as<uint32_t>(), ctx->seg_trail.as<uint32_t>(), P.k);
+  ctx->launches++; stage_mark(ctx, "k_stitch");
+  CK(cudaGetLastError());
+  return 0;
+}
+
+void timing_begin(bgpu_ctx* ctx) {
+  ctx->n_stage = 0; ctx->launches = 0;
+  if (ctx->ev_ok) cudaEventRecord(ctx->ev[0], ctx->stream);
+}
+void timing_end(bgpu_ctx* ctx) {
+  if (!ctx->ev_ok) return;
+  for (int i = 0; i < ctx->n_stage; i++) { float m = 0; cudaEventElapsedTime(&m, ctx->ev[i], ctx->ev[i + 1]); ctx->ms[i] = m; }
+}
+
+// ---- host-only paths (encode.ts:92-138; a18 in SURVEY.md §8a) ----
+struct HostBits {
+  std::vector<uint8_t> b; uint64_t pos = 0;
+  void put(unsigned n, uint64_t v) {
+    for (unsigned i = 0; i < n; i++, pos++) {
+      if ((pos >> 3) >= b.size()) b.push_back(0);
+      b[pos >> 3] |= (uint8_t)(((v >> i) & 1) << (pos & 7));
+    }
+  }
+  void align() { pos = (pos + 7) & ~7ull; }
+  void bytes(const uint8_t* p, size_t n) { b.resize(pos >> 3); b.insert(b.end(), p, p + n); pos += (uint64_t)n * 8; }
+};
+void encode_empty(std::vector<uint8_t>& out) {
+  HostBits w; uint32_t n, v; window_bits(10, &n, &v);
+  w.put(n, v); w.put(1, 1); w.put(1, 1);
+  out = w.b;
+}
+void encode_uncompressed(const uint8_t* in, size_t n, std::vector<uint8_t>& out) {
+  HostBits w; uint32_t wn, wv;
+  int lgwin = std::max(10, std::min(24, n <= 1 ? 10 : (int)std::ceil(std::log2((double)n)) + 1));
+  window_bits(lgwin, &wn, &wv);
+  w.put(wn, wv);
+  const size_t maxBlock = ((size_t)1 << 24) - 1;
+  for (size_t pos = 0; pos < n;) {
+    size_t bs = std::min(n - pos, maxBlock);
+    w.put(1, 0);                                     // ISLAST = 0 (metablock.ts:257-271)
+    int lg = bs == 1 ? 1 : (63 - __builtin_clzll((unsigned long long)(bs - 1))) + 1;
+    int mnibbles = (lg < 16 ? 16 : lg + 3) / 4;
+    w.put(2, mnibbles - 4); w.put(mnibbles * 4, bs - 1);
+    w.put(1, 1);                                     // ISUNCOMPRESSED
+    w.align();
+    w.bytes(in + pos, bs);
+    pos += bs;
+  }
+  w.put(1, 1); w.put(1, 1);                          // ISLAST + ISEMPTY (metablock.ts:848-853)
+  out = w.b;
+}
+
+int host_special_case(const uint8_t* in, size_t n, const EncParams& P, std::vector<uint8_t>& v) {
+  if (n == 0) { encode_empty(v); return 1; }
+  if (P.quality == 0 || n < 64) { encode_uncompressed(in, n, v); return 1; }
+  return 0;
+}
+
+// Copies every stream's shards, concatenated, to the caller's buffers.
+int collect(bgpu_ctx* ctx, const Job& job, uint8_t* const* out, const size_t* out_cap, size_t* out_len, const int* map, int count) {
+  cudaStream_t st = ctx->stream;
+  ctx->h_shard_bytes.resize(job.shards.size());
+  CK(cudaMemcpyAsync(ctx->h_shard_bytes.data(), ctx->shard_bytes.p, job.shards.size() * 4, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  int rc = 0;
+  for (int s = 0; s < count; s++) {
+    const StreamPlan& sp = job.streams[s];
+    size_t total = 0;
+    for (uint32_t k = 0; k < sp.n_shard; k++) {
+      uint32_t b = ctx->h_shard_bytes[sp.first_shard + k];
+      if (b > job.shards[sp.first_shard + k].out_cap) { g_cuda_err = "shard output exceeded its device region"; return BGPU_E_CUDA; }
+      total += b;
+    }
+    int dst = map ? map[s] : s;
+    out_len[dst] = total;
+    if (total > out_cap[dst] || !out[dst]) { rc = BGPU_E_OUTPUT_TOO_SMALL; continue; }
+    size_t o = 0;
+    for (uint32_t k = 0; k < sp.n_shard; k++) {
+      const ShardD& sh = job.shards[sp.first_shard + k];
+      uint32_t b = ctx->h_shard_bytes[sp.first_shard + k];
+      CK(cudaMemcpyAsync(out[dst] + o, ctx->out.as<uint8_t>() + sh.out_off, b, cudaMemcpyDeviceToHost, st));
+      o += b;
+    }
+  }
+  CK(cudaStreamSynchronize(st));
+  return rc;
+}
+
+int check_quality(const EncParams& P) { return (P.quality >= 1 && P.quality <= 4) ? BGPU_E_UNSUPPORTED : 0; }
+int check_quality_hq(const EncParams& P) { return P.quality >= 10 ? BGPU_E_UNSUPPORTED : 0; }  // q10/11 land in zopfli.cu
+
+}  // namespace
+
+extern "C" {
+
+int bgpu_ctx_create(int device_id, bgpu_ctx** out) {
+  if (!out) return BGPU_E_INVALID;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0) { g_cuda_err = e != cudaSuccess ? cudaGetErrorString(e) : "no CUDA device"; return BGPU_E_NO_DEVICE; }
+  bgpu_ctx* c = new bgpu_ctx();
+  if (device_id >= 0) { CK(cudaSetDevice(device_id)); c->device = device_id; } else { CK(cudaGetDevice(&c->device)); }
+  CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  c->ev_ok = true;
+  for (int i = 0; i <= bgpu_ctx::kMaxStages; i++) if (cudaEventCreate(&c->ev[i]) != cudaSuccess) c->ev_ok = false;
+  *out = c;
+  return 0;
+}
+
+void bgpu_ctx_destroy(bgpu_ctx* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  DBuf* all[] = {&c->in, &c->link, &c->best, &c->role, &c->ins, &c->cmds, &c->out, &c->shards, &c->mbs, &c->segs, &c->tile_seg, &c->seg_ncmd,
+                 &c->seg_trail, &c->hist, &c->codes, &c->tree_bits, &c->tree_nbits, &c->tile_bits, &c->tile_off, &c->shard_bytes, &c->huff_meta};
+  for (DBuf* b : all) b->release();
+  if (c->ev_ok) for (int i = 0; i <= bgpu_ctx::kMaxStages; i++) cudaEventDestroy(c->ev[i]);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+int bgpu_ctx_set_tuning(bgpu_ctx* c, const bgpu_tuning* t) {
+  if (!c || !t) return BGPU_E_INVALID;
+  c->tune = *t;
+  return 0;
+}
+
+size_t bgpu_max_compressed_size(size_t n) { return 2 * n + 8192 + ((n >> 16) + 1) * 2048; }
+
+int bgpu_encode_batch(bgpu_ctx* c, int count, const uint8_t* const* in, const size_t* n, int quality, int lgwin, int mode,
+                      uint8_t* const* out, const size_t* out_cap, size_t* out_len) {
+  if (!c || count < 0 || (count && (!in || !n || !out || !out_cap || !out_len))) return BGPU_E_INVALID;
+  EncParams P = make_params(quality, lgwin, mode);
+  int rc;
+  if ((rc = check_quality(P))) return rc;
+  CK(cudaSetDevice(c->device));
+  // host-only special cases first; the rest goes to the device in one job
+  std::vector<int> map; std::vector<size_t> lens; std::vector<const uint8_t*> ptrs;
+  int result = 0;
+  for (int i = 0; i < count; i++) {
+    if (n[i] && !in[i]) return BGPU_E_INVALID;
+    std::vector<uint8_t> v;
+    if (host_special_case(in[i], n[i], P, v)) {
+      out_len[i] = v.size();
+      if (v.size() > out_cap[i] || !out[i]) result = BGPU_E_OUTPUT_TOO_SMALL; else memcpy(out[i], v.data(), v.size());
+    } else { map.push_back(i); lens.push_back(n[i]); ptrs.push_back(in[i]); }
+  }
+  if (map.empty()) return result;
+  if ((rc = check_quality_hq(P))) return rc;
+  Job job; plan_job(c, P, lens.data(), (int)lens.size(), job);
+  if ((rc = c->in.reserve(job.in_bytes + IN_PAD))) return rc;
+  timing_begin(c);
+  for (size_t s = 0; s < lens.size(); s++) {
+    CK(cudaMemcpyAsync(c->in.as<uint8_t>() + job.streams[s].in_off, ptrs[s], lens[s], cudaMemcpyHostToDevice, c->stream));
+    size_t padded = ((lens[s] + 255) & ~(size_t)255) + (s + 1 == lens.size() ? IN_PAD : 0);
+    CK(cudaMemsetAsync(c->in.as<uint8_t>() + job.streams[s].in_off + lens[s], 0, padded - lens[s], c->stream));
+  }
+  stage_mark(c, "h2d");
+  if ((rc = upload_plan(c, job))) return rc;
+  if ((rc = run_frontend(c, job, P, c->in.as<uint8_t>()))) return rc;
+  if ((rc = run_backend(c, job, P, c->in.as<uint8_t>()))) return rc;
+  rc = collect(c, job, out, out_cap, out_len, map.data(), (int)map.size());
+  timing_end(c);
+  return rc ? rc : result;
+}
+
+int bgpu_encode(bgpu_ctx* c, const uint8_t* in, size_t n, int quality, int lgwin, int mode, uint8_t* out, size_t out_cap, size_t* out_len) {
+  if (!out_len) return BGPU_E_INVALID;
+  const uint8_t* ins[1] = {in}; size_t ns[1] = {n}; uint8_t* outs[1] = {out}; size_t caps[1] = {out_cap};
+  return bgpu_encode_batch(c, 1, ins, ns, quality, lgwin, mode, outs, caps, out_len);
+}
+
+int bgpu_encode_device(bgpu_ctx* c, const void* d_in, size_t n, int quality, int lgwin, int mode, uint8_t* out, size_t out_cap,
+                       size_t* out_len, float* kernel_ms) {
+  if (!c || !d_in || !out_len || n < 64) return BGPU_E_INVALID;
+  EncParams P = make_params(quality, lgwin, mode);
+  int rc;
+  if (P.quality == 0) return BGPU_E_INVALID;
+  if ((rc = check_quality(P))) return rc;
+  if ((rc = check_quality_hq(P))) return rc;
+  CK(cudaSetDevice(c->device));
+  Job job; size_t lens[1] = {n}; plan_job(c, P, lens, 1, job);
+  timing_begin(c);
+  if ((rc = upload_plan(c, job))) return rc;
+  if ((rc = run_frontend(c, job, P, (const uint8_t*)d_in))) return rc;
+  if ((rc = run_backend(c, job, P, (const uint8_t*)d_in))) return rc;
+  if (out) {
+    uint8_t* outs[1] = {out}; size_t caps[1] = {out_cap};
+    rc = collect(c, job, outs, caps, out_len, nullptr, 1);
+  } else {
+    c->h_shard_bytes.resize(job.shards.size());
+    CK(cudaMemcpyAsync(c->h_shard_bytes.data(), c->shard_bytes.p, job.shards.size() * 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaStreamSynchronize(c->stream));
+    size_t total = 0;
+    for (uint32_t b : c->h_shard_bytes) total += b;
+    *out_len = total;
+  }
+  timing_end(c);
+  if (kernel_ms) { float t = 0; for (int i = 0; i < c->n_stage; i++) t += c->ms[i]; *kernel_ms = t; }
+  return rc;
+}
+
+// ------------------------------------------------------------------ streaming (encode.ts:290-409)
+}  // extern "C"
+
+struct bgpu_stream {
+  bgpu_ctx* ctx; int quality, lgwin, mode;
+  std::vector<uint8_t> pending;   // bytes not yet encoded (the reference copies each chunk, encode.ts:360-363)
+  std::vector<uint8_t> outbuf;
+  bool header_done = false, finished = false;
+  size_t total_in = 0;
+};
+
+extern "C" {
+
+int bgpu_stream_create(bgpu_ctx* c, int quality, int lgwin, int mode, bgpu_stream** s) {
+  if (!c || !s) return BGPU_E_INVALID;
+  EncParams P = make_params(quality, lgwin, mode);
+  if (P.quality < 5) return BGPU_E_UNSUPPORTED;   // streaming q0..4 uses SimpleHasher (encode.ts:343-344)
+  int rc; if ((rc = check_quality_hq(P))) return rc;
+  bgpu_stream* st = new bgpu_stream(); st->ctx = c; st->quality = P.quality; st->lgwin = P.lgwin; st->mode = mode;
+  *s = st;
+  return 0;
+}
+
+// Encodes `n` pending bytes as one shard of the stream (first: carries the window header; last: ISLAST).
+static int stream_flush_shard(bgpu_stream* s, size_t n, bool last) {
+  bgpu_ctx* c = s->ctx;
+  EncParams P = make_params(s->quality, s->lgwin, s->mode);
+  CK(cudaSetDevice(c->device));
+  Job job; size_t lens[1] = {n}; plan_job(c, P, lens, 1, job);
+  if (job.shards.size() != 1) return BGPU_E_INVALID;
+  ShardD& sh = job.shards[0];
+  sh.flags = (s->header_done ? 0u : 1u) | (last ? 2u : 0u);
+  for (MbD& mb : job.mbs) mb.is_last = 0;
+  if (last) job.mbs.back().is_last = 1;
+  if (s->header_done) for (SegD& sg : job.segs) sg.ring_known = 0;
+  int rc;
+  if ((rc = c->in.reserve(job.in_bytes + IN_PAD))) return rc;
+  timing_begin(c);
+  CK(cudaMemcpyAsync(c->in.p, s->pending.data(), n, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemsetAsync(c->in.as<uint8_t>() + n, 0, job.in_bytes + IN_PAD - n, c->stream));
+  if ((rc = upload_plan(c, job))) return rc;
+  if ((rc = run_frontend(c, job, P, c->in.as<uint8_t>()))) return rc;
+  if ((rc = run_backend(c, job, P, c->in.as<uint8_t>()))) return rc;
+  size_t cap = sh.out_cap, len = 0, old = s->outbuf.size();
+  s->outbuf.resize(old + cap);
+  uint8_t* outs[1] = {s->outbuf.data() + old}; size_t caps[1] = {cap};
+  rc = collect(c, job, outs, caps, &len, nullptr, 1);
+  s->outbuf.resize(old + (rc ? 0 : len));
+  timing_end(c);
+  s->header_done = true;
+  s->pending.erase(s->pending.begin(), s->pending.begin() + n);
+  return rc;
+}
+
+int bgpu_stream_update(bgpu_stream* s, const uint8_t* chunk, size_t n, const uint8_t** out, size_t* out_len) {
+  if (!s || (n && !chunk) || !out || !out_len) return BGPU_E_INVALID;
+  if (s->finished) return BGPU_E_STATE;
+  s->outbuf.clear();
+  s->pending.insert(s->pending.end(), chunk, chunk + n);
+  s->total_in += n;
+  EncParams P = make_params(s->quality, s->lgwin, s->mode);
+  size_t shard = std::min<size_t>((size_t)1 << 22, P.lgwin < 22 ? ((((size_t)1 << P.lgwin) - 16) & ~(size_t)3) : ((size_t)1 << 22));
+  if (s->ctx->tune.shard_bytes) shard = std::min<size_t>(shard, std::max<uint32_t>(s->ctx->tune.shard_bytes & ~3u, 64));
+  // keep at least one byte pending so that finish() can mark the final metablock ISLAST
+  while (s->pending.size() > shard) { int rc = stream_flush_shard(s, shard, false); if (rc) return rc; }
+  *out = s->outbuf.data(); *out_len = s->outbuf.size();
+  return 0;
+}
+
+int bgpu_stream_finish(bgpu_stream* s, const uint8_t** out, size_t* out_len) {
+  if (!s || !out || !out_len) return BGPU_E_INVALID;
+  if (s->finished) return BGPU_E_STATE;
+  s->outbuf.clear();
+  if (!s->pending.empty()) {
+    int rc = stream_flush_shard(s, s->pending.size(), true);
+    if (rc) return rc;
+  } else {
+    // encode.ts:399-405: ISLAST + ISEMPTY (after the window header if nothing was written yet)
+    HostBits w;
+    if (!s->header_done) { uint32_t wn, wv; window_bits(s->lgwin, &wn, &wv); w.put(wn, wv); }
+    w.put(1, 1); w.put(1, 1);
+    s->outbuf = w.b;
+  }
+  s->finished = true;
+  *out = s->outbuf.data(); *out_len = s->outbuf.size();
+  return 0;
+}
+
+void bgpu_stream_destroy(bgpu_stream* s) { delete s; }
+
+// ------------------------------------------------------------------ stage entry points
+int bgpu_stage_match_candidates(bgpu_ctx* c, const uint8_t* in, size_t n, int quality, int lgwin, uint32_t* len, uint32_t* dist) {
+  if (!c || !in || !len || !dist || n == 0 || n > ((size_t)1 << 22)) return BGPU_E_INVALID;
+  EncParams P = make_params(quality, lgwin, 0);
+  CK(cudaSetDevice(c->device));
+  bgpu_tuning saved = c->tune; c->tune.shard_bytes = 1u << 22;
+  Job job; size_t lens[1] = {n}; plan_job(c, P, lens, 1, job);
+  c->tune = saved;
+  int rc;
+  if ((rc = c->in.reserve(job.in_bytes + IN_PAD))) return rc;
+  timing_begin(c);
+  CK(cudaMemcpyAsync(c->in.p, in, n, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemsetAsync(c->in.as<uint8_t>() + n, 0, job.in_bytes + IN_PAD - n, c->stream));
+  if ((rc = upload_plan(c, job))) return rc;
+  if ((rc = run_frontend(c, job, P, c->in.as<uint8_t>()))) return rc;
+  std::vector<uint32_t> b(n);
+  CK(cudaMemcpyAsync(b.data(), c->best.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  timing_end(c);
+  for (size_t i = 0; i < n; i++) { len[i] = b[i] >> 24; dist[i] = (b[i] >> 24) ? (b[i] & 0xFFFFFF) : 0; }
+  return 0;
+}
+
+// Rebuilds the command list from role / ins / cmds (test path; the production path never needs it).
+static void rebuild_commands(const std::vector<uint8_t>& role, const std::vector<uint32_t>& ins, const std::vector<Cmd>& cmds, size_t n, int sh,
+                             std::vector<Cmd>& out) {
+  for (size_t p = 0; p < n; p++) {
+    if (!(role[p] & 4)) continue;
+    uint32_t il = ins[p >> sh];
+    if (role[p] & 8) out.push_back(make_insert_cmd(il));
+    else out.push_back(cmds[(p + il) >> sh]);
+  }
+}
+
+int bgpu_stage_commands(bgpu_ctx* c, const uint8_t* in, size_t n, int quality, int lgwin, int mode, void* cmds_out, size_t cmd_cap, size_t* ncmd) {
+  if (!c || !in || !ncmd || n == 0 || n > ((size_t)1 << 22)) return BGPU_E_INVALID;
+  EncParams P = make_params(quality, lgwin, mode);
+  int rc; if ((rc = check_quality_hq(P))) return rc;
+  CK(cudaSetDevice(c->device));
+  Job job; size_t lens[1] = {n}; plan_job(c, P, lens, 1, job);
+  if (job.shards.size() != 1) return BGPU_E_INVALID;
+  if ((rc = c->in.reserve(job.in_bytes + IN_PAD))) return rc;
+  timing_begin(c);
+  CK(cudaMemcpyAsync(c->in.p, in, n, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemsetAsync(c->in.as<uint8_t>() + n, 0, job.in_bytes + IN_PAD - n, c->stream));
+  if ((rc = upload_plan(c, job))) return rc;
+  if ((rc = run_frontend(c, job, P, c->in.as<uint8_t>()))) return rc;
+  size_t slots = (n >> P.k.sh) + 2;
+  std::vector<uint8_t> role(n); std::vector<uint32_t> ins(slots); std::vector<Cmd> cm(slots);
+  CK(cudaMemcpyAsync(role.data(), c->role.p, n, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(ins.data(), c->ins.p, slots * 4, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(cm.data(), c->cmds.p, slots * sizeof(Cmd), cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  timing_end(c);
+  std::vector<Cmd> list; rebuild_commands(role, ins, cm, n, P.k.sh, list);
+  *ncmd = list.size();
+  if (list.size() > cmd_cap || !cmds_out) return BGPU_E_OUTPUT_TOO_SMALL;
+  memcpy(cmds_out, list.data(), list.size() * sizeof(Cmd));
+  return 0;
+}
+
+int bgpu_stage_store_trivial(bgpu_ctx* c, const uint8_t* in, size_t n, const void* cmds_in, size_t ncmd, int is_last, int mode,
+                             unsigned start_nbits, unsigned start_value, uint8_t* out, size_t out_cap, size_t* out_len, uint64_t* out_bits,
+                             void* tables) {
+  if (!c || !in || !cmds_in || !out_len || n == 0 || n > ((size_t)1 << 24) || ncmd == 0) return BGPU_E_INVALID;
+  EncParams P = make_params(9, 24, mode);
+  P.k.sh = 1;  // caller-supplied commands may hold 2- and 3-byte copies (Zopfli)
+  CK(cudaSetDevice(c->device));
+  // one shard, one metablock, one segment covering the whole input
+  bgpu_tuning saved = c->tune; c->tune.shard_bytes = 1u << 22; c->tune.segment_bytes = 0xFFFFFFFFu; c->tune.metablock_bytes = 0;
+  Job job; size_t lens[1] = {std::min<size_t>(n, (size_t)1 << 22)}; plan_job(c, P, lens, 1, job);
+  c->tune = saved;
+  if (n > ((size_t)1 << 22)) return BGPU_E_INVALID;
+  ShardD& sh = job.shards[0];
+  sh.flags = (start_nbits ? 1u : 0u) | 2u;   // never append the padding block here
+  sh.start_nbits = start_nbits; sh.start_value = start_value;
+  job.mbs[0].is_last = is_last ? 1 : 0;
+  // roles / ins / cmds from the caller's command list
+  const Cmd* cl = (const Cmd*)cmds_in;
+  size_t slots = (n >> P.k.sh) + 2;
+  std::vector<uint8_t> role(n + IN_PAD, 0); std::vector<uint32_t> ins(slots, 0); std::vector<Cmd> cm(slots);
+  memset(cm.data(), 0, slots * sizeof(Cmd));
+  size_t pos = 0;
+  for (size_t i = 0; i < ncmd; i++) {
+    const Cmd& k = cl[i];
+    uint32_t copyLen = k.copyLen & 0x1FFFFFF;
+    if (pos + k.insertLen + copyLen > n) return BGPU_E_INVALID;
+    size_t start = pos;
+    for (uint32_t j = 0; j < k.insertLen; j++) role[pos + j] = 1;
+    pos += k.insertLen;
+    if (copyLen) { role[pos] |= 2; cm[pos >> P.k.sh] = k; }
+    else if (i + 1 != ncmd) return BGPU_E_INVALID;  // an insert-only command must be last
+    role[start] |= 4 | (copyLen ? 0 : 8);
+    ins[start >> P.k.sh] = k.insertLen;
+    pos += copyLen;
+  }
+  if (pos != n) return BGPU_E_INVALID;
+  int rc;
+  if ((rc = c->in.reserve(job.in_bytes + IN_PAD))) return rc;
+  if ((rc = reserve_front(c, job, P))) return rc;
+  timing_begin(c);
+  CK(cudaMemcpyAsync(c->in.p, in, n, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemsetAsync(c->in.as<uint8_t>() + n, 0, job.in_bytes + IN_PAD - n, c->stream));
+  CK(cudaMemcpyAsync(c->role.p, role.data(), n + IN_PAD, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(c->ins.p, ins.data(), slots * 4, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(c->cmds.p, cm.data(), slots * sizeof(Cmd), cudaMemcpyHostToDevice, c->stream));
+  if ((rc = upload_plan(c, job))) return rc;
+  if ((rc = run_backend(c, job, P, c->in.as<uint8_t>()))) return rc;
+  uint8_t* outs[1] = {out}; size_t caps[1] = {out_cap};
+  rc = collect(c, job, outs, caps, out_len, nullptr, 1);
+  timing_end(c);
+  if (out_bits) *out_bits = (uint64_t)*out_len * 8;
+  if (tables) {
+    // layout of oracle::TrivialTables: 3 histograms (256, 704, 544 u32), 3 depth arrays, 3 code arrays
+    std::vector<uint32_t> h(CODE_STRIDE), cd(CODE_STRIDE);
+    CK(cudaMemcpy(h.data(), c->hist.p, CODE_STRIDE * 4, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(cd.data(), c->codes.p, CODE_STRIDE * 4, cudaMemcpyDeviceToHost));
+    uint8_t* t = (uint8_t*)tables;
+    uint32_t* th = (uint32_t*)t; uint8_t* td = t + (256 + 704 + 544) * 4; uint16_t* tb = (uint16_t*)(td + 256 + 704 + 544);
+    memset(t, 0, (256 + 704 + 544) * 7);
+    const int srcOff[3] = {0, ALPHA_LIT, ALPHA_LIT + ALPHA_CMD}, dstOff[3] = {0, 256, 960}, cnt[3] = {256, 704, (int)P.k.dist_alphabet};
+    for (int a = 0; a < 3; a++)
+      for (int i = 0; i < cnt[a]; i++) {
+        th[dstOff[a] + i] = h[srcOff[a] + i];
+        td[dstOff[a] + i] = (uint8_t)(cd[srcOff[a] + i] & 0xFF);
+        tb[dstOff[a] + i] = (uint16_t)(cd[srcOff[a] + i] >> 8);
+      }
+  }
+  return rc;
+}
+
+int bgpu_stage_huffman(bgpu_ctx* c, const uint32_t* hist, int count, int alphabet, uint8_t* depths, uint16_t* bits, uint8_t* tree_bits,
+                       uint32_t* tree_nbits) {
+  if (!c || !hist || count <= 0 || alphabet < 2 || alphabet > ALPHA_CMD) return BGPU_E_INVALID;
+  CK(cudaSetDevice(c->device));
+  int rc; size_t total = (size_t)count * alphabet;
+  DBuf dh, dc, dt, dn, dm;
+  auto done = [&](int r) { dh.release(); dc.release(); dt.release(); dn.release(); dm.release(); return r; };
+  if ((rc = dh.reserve(total * 4)) || (rc = dc.reserve(total * 4)) || (rc = dt.reserve((size_t)count * TREE_WORDS * 4)) ||
+      (rc = dn.reserve((size_t)count * 4)) || (rc = dm.reserve(16)))
+    return done(rc);
+  int meta[2] = {alphabet, 0};
+  cudaError_t e = cudaMemcpy(dh.p, hist, total * 4, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpy(dm.p, meta, sizeof meta, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) {
+    k_huff<<<count, 128, 0, c->stream>>>(dh.as<uint32_t>(), alphabet, 1, dm.as<int>(), dm.as<int>() + 1, dc.as<uint32_t>(), dt.as<uint32_t>(), dn.as<uint32_t>());
+    e = cudaStreamSynchronize(c->stream);
+  }
+  std::vector<uint32_t> cd(total);
+  if (e == cudaSuccess) e = cudaMemcpy(cd.data(), dc.p, total * 4, cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess && tree_bits) e = cudaMemcpy(tree_bits, dt.p, (size_t)count * TREE_WORDS * 4, cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess && tree_nbits) e = cudaMemcpy(tree_nbits, dn.p, (size_t)count * 4, cudaMemcpyDeviceToHost);
+  if (e != cudaSuccess) { g_cuda_err = cudaGetErrorString(e); return done(BGPU_E_CUDA); }
+  for (size_t i = 0; i < total; i++) { if (depths) depths[i] = (uint8_t)(cd[i] & 0xFF); if (bits) bits[i] = (uint16_t)(cd[i] >> 8); }
+  return done(0);
+}
+
+int bgpu_stage_timings(bgpu_ctx* c, const char** names, float* ms, int cap) {
+  if (!c) return 0;
+  for (int i = 0; i < c->n_stage && i < cap; i++) { if (names) names[i] = c->names[i]; if (ms) ms[i] = c->ms[i]; }
+  return c->n_stage;
+}
+int bgpu_last_launch_count(bgpu_ctx* c) { return c ? c->launches : 0; }
+
+const char* bgpu_strerror(int code) {
+  switch (code) {
+    case 0: return "ok";
+    case BGPU_E_INVALID: return "invalid argument";
+    case BGPU_E_OUTPUT_TOO_SMALL: return "output buffer too small";
+    case BGPU_E_UNSUPPORTED: return "quality not supported by the GPU hot path";
+    case BGPU_E_NO_DEVICE: return "no CUDA device";
+    case BGPU_E_CUDA: return "CUDA error";
+    case BGPU_E_NOMEM: return "out of device memory";
+    case BGPU_E_STATE: return "stream already finished";
+    default: return "unknown error";
+  }
+}
+const char* bgpu_last_cuda_error(void) { return g_cuda_err.c_str(); }
+int bgpu_version(void) { return 0x000100; }
+
+}  // extern "C"

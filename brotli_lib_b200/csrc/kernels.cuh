@@ -1,0 +1,621 @@
+// sm_100a kernels of the Brotli encoder hot path (q5..q9 greedy path; K-numbers follow SURVEY.md §2).
+//
+//   K2  k_link      hash-chain links          hash-chains.ts:51-60,117-119 + match.ts:162-172
+//   K3  k_probe     per-position chain best   hash-chains.ts:121-152 (+ match.ts:20-77)
+//   K5  k_parse     greedy parse              backward-references.ts:14-158
+//       k_stitch    joins parse segments into whole-metablock command streams (no TS counterpart)
+//   K7  k_hist      BuildHistograms           metablock.ts:305-325
+//   K10 k_huff      Huffman + tree store      entropy-encode.ts:24-258, context-map.ts:215-520
+//   K11 k_tilebits / k_offsets / k_write      metablock.ts:233-255, 300-388; bit-writer.ts:32-56
+//
+// Data layout in HBM (all indexed by absolute byte position in the staged input buffer):
+//   in    u8 [N+pad]  input, every stream starts 256-byte aligned
+//   link  u32[N]      shard-relative previous position with the same hash key (NONE if first)
+//   best  u32[N]      chain-best match: len << 24 | distance   (len <= 128, distance < 2^22)
+//   role  u8 [N]      1 literal | 2 copy start | 4 command start | 8 insert-only command
+//   ins   u32[N>>sh]  insert length of the command starting at position p, slot p >> sh
+//   cmds  Cmd[N>>sh]  command record, slot = (copy-start position) >> sh    (sh = 2: copies >= 4 bytes)
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include "codec_common.cuh"
+
+namespace bgpu {
+
+constexpr uint32_t NONE = 0xFFFFFFFFu;
+constexpr uint32_t TILE = 1024;                 // positions per bit-writer tile
+constexpr uint32_t MAX_BACKWARD = (1u << 22) - 16;  // backward-references.ts:31
+constexpr int TREE_WORDS = 256;                 // serialised prefix code, u32 words per tree
+constexpr int ALPHA_LIT = 256, ALPHA_CMD = 704, ALPHA_DIST_MAX = 128;
+constexpr int CODE_STRIDE = ALPHA_LIT + ALPHA_CMD + ALPHA_DIST_MAX;  // per-metablock code table
+
+struct ShardD {
+  uint64_t in_off;    // absolute offset of the shard's first byte (multiple of 4)
+  uint32_t len;
+  uint32_t flags;     // 1 first shard of its stream, 2 last shard of its stream
+  uint64_t out_off;   // byte offset of the shard's output region (multiple of 4)
+  uint32_t out_cap;
+  uint32_t first_mb, n_mb;
+  uint32_t start_nbits, start_value;  // stream header bits (encodeWindowBits) for the first shard
+  uint32_t pad;
+};
+struct MbD { uint32_t shard, rel_pos, len, first_seg, n_seg, first_tile, n_tile, is_last; };
+struct SegD { uint32_t shard, rel_pos, len, mb, first_tile, ring_known, pad0, pad1; };
+
+struct Params {
+  int bucket_bits, depth, num_last;
+  uint32_t npostfix, ndirect, dist_alphabet;
+  int sh;  // command slot shift
+};
+
+// ---------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t ld32u(const uint8_t* base, uint64_t off) {
+  // unaligned little-endian u32 from a 4-byte-aligned base (reads up to 7 bytes past off)
+  const uint32_t* w = reinterpret_cast<const uint32_t*>(base) + (off >> 2);
+  uint32_t lo = __ldg(w), hi = __ldg(w + 1);
+  return __funnelshift_r(lo, hi, (uint32_t)(off & 3) * 8);
+}
+__device__ __forceinline__ uint32_t hash4(uint32_t v, int bits) { return (v * 0x1E35A7BDu) >> (32 - bits); }
+
+// common prefix length of in[a..] and in[b..], limit-capped (match.ts:42-77)
+__device__ __forceinline__ uint32_t match_len(const uint8_t* in, uint64_t a, uint64_t b, uint32_t limit) {
+  uint32_t k = 0;
+  while (k < limit) {
+    uint32_t x = ld32u(in, a + k) ^ ld32u(in, b + k);
+    if (x) { k += (__ffs((int)x) - 1) >> 3; break; }
+    k += 4;
+  }
+  return k < limit ? k : limit;
+}
+
+// ---------------------------------------------------------------------------------------
+// K2.  One warp per shard walks the shard in position order; the per-key "last position" table
+// lives in shared memory (4 << bucket_bits bytes).  32 positions per step: lanes with equal keys
+// are linked to each other through __match_any_sync, the lowest lane of each group reads the
+// table, the highest lane writes it back.
+__global__ void __launch_bounds__(32) k_link(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
+                                             uint32_t* __restrict__ link, int bucket_bits) {
+  extern __shared__ uint32_t s_table[];
+  const ShardD sh = shards[blockIdx.x];
+  const uint32_t lane = threadIdx.x;
+  for (uint32_t i = lane; i < (1u << bucket_bits); i += 32) s_table[i] = NONE;
+  __syncwarp();
+  const uint32_t npos = sh.len >= 4 ? sh.len - 3 : 0;
+  const uint32_t* in32 = reinterpret_cast<const uint32_t*>(in + sh.in_off);
+  uint32_t* lk = link + sh.in_off;
+  // 128 positions per outer iteration: lane L holds word base/4 + L; 33rd word fetched by lane 0.
+  uint32_t w = 0, wx = 0;
+  if (npos) { w = __ldg(in32 + lane); wx = __ldg(in32 + 32); }
+  for (uint32_t base = 0; base < npos; base += 128) {
+    uint32_t nw = 0, nwx = 0;
+    if (base + 128 < npos) { nw = __ldg(in32 + (base >> 2) + 32 + lane); nwx = __ldg(in32 + (base >> 2) + 64); }
+    wx = __shfl_sync(0xffffffffu, wx, 0);
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      uint32_t src = 8 * j + (lane >> 2);
+      uint32_t lo = __shfl_sync(0xffffffffu, w, src);
+      uint32_t hi = __shfl_sync(0xffffffffu, w, (src + 1) & 31);
+      if (src == 31) hi = wx;
+      uint32_t p = base + 32 * j + lane;
+      bool active = p < npos;
+      uint32_t v = __funnelshift_r(lo, hi, (lane & 3) * 8);
+      uint32_t key = active ? hash4(v, bucket_bits) : (0x80000000u | lane);
+      uint32_t peers = __match_any_sync(0xffffffffu, key);
+      uint32_t lower = peers & ((1u << lane) - 1);
+      uint32_t prev = NONE;
+      if (lower) prev = base + 32 * j + (31 - __clz((int)lower));
+      else if (active) prev = s_table[key];
+      __syncwarp();
+      if (active && (peers >> lane) == 1u) s_table[key] = p;
+      __syncwarp();
+      if (active) lk[p] = prev;
+    }
+    w = nw; wx = nwx;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// K3.  One thread per position: walk <= depth links, keep the first strict maximum of
+// backwardReferenceScore (match.ts:26-30).  256 threads cover one 1024-position tile.
+__global__ void __launch_bounds__(256) k_probe(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
+                                               const SegD* __restrict__ segs, const uint32_t* __restrict__ tile_seg,
+                                               const uint32_t* __restrict__ link, uint32_t* __restrict__ best, int depth) {
+  const uint32_t tile = blockIdx.x;
+  const SegD sg = segs[tile_seg[tile]];
+  const ShardD sh = shards[sg.shard];
+  const uint32_t tile_rel = sg.rel_pos + (tile - sg.first_tile) * TILE;
+  const uint32_t tile_end = min(sg.rel_pos + sg.len, tile_rel + TILE);
+  const uint8_t* sin = in + sh.in_off;
+  const uint32_t* lk = link + sh.in_off;
+  for (uint32_t rel = tile_rel + threadIdx.x; rel < tile_end; rel += 256) {
+    uint32_t out = 0;
+    if (rel + 4 <= sh.len) {
+      const uint32_t maxLen = min(sh.len - rel, 128u);
+      const uint32_t maxBackward = min(rel, MAX_BACKWARD);
+      const uint32_t v = ld32u(sin, rel);
+      uint32_t bestLen = 0, bestDist = 0; int bestScore = 0;
+      uint32_t c = lk[rel];
+      for (int d = 0; d < depth && c != NONE; d++) {
+        uint32_t backward = rel - c;
+        if (backward > maxBackward) break;
+        uint32_t nxt = lk[c];
+        // hash-chains.ts:132-135 quick check on the byte at bestLen (prunes only candidates that
+        // cannot win: they would need len > bestLen), then the full compare.
+        if (ld32u(sin, c) == v && (bestLen < 4 || sin[c + bestLen] == sin[rel + bestLen])) {
+          uint32_t len = 4 + match_len(sin, rel + 4, c + 4, maxLen - 4);
+          int score = 135 * (int)len + 960 - 30 * log2_floor(backward);
+          if (score > bestScore) { bestScore = score; bestLen = len; bestDist = backward; }
+          if (bestLen == maxLen) break;
+        }
+        c = nxt;
+      }
+      out = (bestLen << 24) | bestDist;
+    }
+    best[sh.in_off + rel] = out;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// K5.  One warp per parse segment.  32 consecutive positions are evaluated speculatively with the
+// current distance ring; the first lane holding an acceptable match is the reference's next
+// command (the ring only changes at accepted matches, so the speculation is exact).
+__device__ __forceinline__ uint32_t distance_to_code(uint32_t distance, const int* ring) {
+  // backward-references.ts:146-158, plus a guard so that ring entries not yet learned in this
+  // segment (0) are never referenced.
+  const int8_t off[16] = {0, 0, 0, 0, -1, 1, -2, 2, -3, 3, -1, 1, -2, 2, -3, 3};
+#pragma unroll
+  for (int i = 0; i < 16; i++) {
+    int base = i < 4 ? ring[i] : (i < 10 ? ring[0] : ring[1]);
+    int cached = base + off[i];
+    if (base > 0 && cached > 0 && (int)distance == cached) return i;
+  }
+  return distance + 15;
+}
+
+__global__ void __launch_bounds__(128) k_parse(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
+                                               const SegD* __restrict__ segs, uint32_t n_seg,
+                                               const uint32_t* __restrict__ best, uint8_t* __restrict__ role,
+                                               uint32_t* __restrict__ ins_at, Cmd* __restrict__ cmds,
+                                               uint32_t* __restrict__ seg_ncmd, uint32_t* __restrict__ seg_trail, Params P) {
+  const uint32_t seg = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (seg >= n_seg) return;
+  const uint32_t lane = threadIdx.x & 31;
+  const SegD sg = segs[seg];
+  const ShardD sh = shards[sg.shard];
+  const uint8_t* sin = in + sh.in_off;
+  const uint32_t* sbest = best + sh.in_off;
+  uint8_t* srole = role + sh.in_off;
+  const uint32_t seg_end = sg.rel_pos + sg.len;
+  int ring[4];
+  if (sg.ring_known) { ring[0] = 4; ring[1] = 11; ring[2] = 15; ring[3] = 16; }
+  else { ring[0] = ring[1] = ring[2] = ring[3] = 0; }
+  uint32_t pos = sg.rel_pos, ins_start = sg.rel_pos, ncmd = 0;
+  while (pos < seg_end) {
+    const uint32_t q = pos + lane;
+    uint32_t blen = 0, bdist = 0; int bscore = 0;
+    if (q + 4 <= seg_end) {
+      const uint32_t maxLen = min(seg_end - q, 128u);
+      const uint32_t maxBackward = min(q, MAX_BACKWARD);
+      const uint32_t v = ld32u(sin, q);
+      // hash-chains.ts:86-115: distance-cache candidates, all scored with the last-distance bonus
+#pragma unroll
+      for (int i = 0; i < 16; i++) {
+        if (i >= P.num_last) break;
+        // match.ts:128-148 prepareDistanceCache: ring[0] -+ 1,2,3 then ring[1] -+ 1,2,3
+        const int base = i < 4 ? ring[i & 3] : (i < 10 ? ring[0] : ring[1]);
+        const int d = i < 4 ? base : base + ((i & 1) ? 1 : -1) * (((i - 4) % 6) / 2 + 1);
+        if (base <= 0 || d <= 0 || (uint32_t)d > maxBackward) continue;
+        if (ld32u(sin, q - d) != v) continue;
+        uint32_t len = 4 + match_len(sin, q + 4, q - d + 4, maxLen - 4);
+        int score = 135 * (int)len + 975;
+        if (score > bscore) { bscore = score; blen = len; bdist = (uint32_t)d; }
+      }
+      // chain best from K3 (truncated at the segment end)
+      uint32_t b = sbest[q];
+      uint32_t clen = min(b >> 24, maxLen), cdist = b & 0xFFFFFFu;
+      if (clen >= 4) {
+        int score = 135 * (int)clen + 960 - 30 * log2_floor(cdist);
+        if (score > bscore) { bscore = score; blen = clen; bdist = cdist; }
+      }
+    }
+    const uint32_t ballot = __ballot_sync(0xffffffffu, blen >= 4);
+    const uint32_t f = ballot ? (uint32_t)__ffs((int)ballot) - 1 : 32u;
+    if (lane < f && q < seg_end) srole[q] = 1 | (q == ins_start ? 4 : 0);
+    if (f == 32u) { pos += 32; continue; }
+    const uint32_t mlen = __shfl_sync(0xffffffffu, blen, f);
+    const uint32_t mdist = __shfl_sync(0xffffffffu, bdist, f);
+    const uint32_t qf = pos + f;
+    const uint32_t code = distance_to_code(mdist, ring);
+    if (lane == 0) {
+      Cmd c = make_cmd(qf - ins_start, mlen, code, P.ndirect, P.npostfix);
+      srole[qf] = 2 | (qf == ins_start ? 4 : 0);
+      ins_at[(sh.in_off + ins_start) >> P.sh] = qf - ins_start;
+      *reinterpret_cast<uint4*>(&cmds[(sh.in_off + qf) >> P.sh]) = *reinterpret_cast<uint4*>(&c);
+    }
+    if (code > 0) { ring[3] = ring[2]; ring[2] = ring[1]; ring[1] = ring[0]; ring[0] = (int)mdist; }
+    pos = qf + mlen; ins_start = pos; ncmd++;
+  }
+  if (lane == 0) { seg_ncmd[seg] = ncmd; seg_trail[seg] = ins_start; }
+}
+
+// Joins the segments of a metablock: literals left over at the end of a segment become part of the
+// next segment's first command; what remains at the metablock end is the insert-only command of
+// encode.ts:253-267 / command.ts:183-208.
+__global__ void k_stitch(const ShardD* __restrict__ shards, const MbD* __restrict__ mbs, const SegD* __restrict__ segs,
+                         uint32_t n_mb, uint8_t* __restrict__ role, uint32_t* __restrict__ ins_at, Cmd* __restrict__ cmds,
+                         const uint32_t* __restrict__ seg_ncmd, const uint32_t* __restrict__ seg_trail, Params P) {
+  const uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= n_mb) return;
+  const MbD mb = mbs[m];
+  const ShardD sh = shards[mb.shard];
+  uint8_t* srole = role + sh.in_off;
+  int64_t carry = -1;  // start of the pending (not yet terminated) literal run, shard-relative
+  for (uint32_t s = mb.first_seg; s < mb.first_seg + mb.n_seg; s++) {
+    const SegD sg = segs[s];
+    const uint32_t seg_end = sg.rel_pos + sg.len;
+    const uint32_t nc = seg_ncmd[s], trail = seg_trail[s];
+    if (carry >= 0) {
+      srole[sg.rel_pos] &= ~4;
+      if (nc > 0) {
+        uint32_t ins_old = ins_at[(sh.in_off + sg.rel_pos) >> P.sh];
+        uint32_t ins_new = ins_old + (sg.rel_pos - (uint32_t)carry);
+        Cmd* c = &cmds[(sh.in_off + sg.rel_pos + ins_old) >> P.sh];
+        c->insertLen = ins_new;
+        c->cmdPrefix = (uint16_t)combine_codes(ins_code(ins_new), copy_code(c->copyLen & 0x1FFFFFF), (c->distPrefix & 0x3FF) == 0);
+        ins_at[(sh.in_off + (uint32_t)carry) >> P.sh] = ins_new;
+        carry = -1;
+      }
+    }
+    if (nc > 0 || carry < 0) carry = trail < seg_end ? (int64_t)trail : -1;
+  }
+  if (carry >= 0) {
+    srole[carry] |= 8;
+    ins_at[(sh.in_off + (uint32_t)carry) >> P.sh] = mb.rel_pos + mb.len - (uint32_t)carry;
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// K7.  Literal / command / distance histograms of every metablock (metablock.ts:305-325) plus the
+// per-tile command-independent bookkeeping.  One CTA per 8 tiles; shared-memory histograms are
+// flushed with global atomics whenever the metablock changes.
+struct MbHist { uint32_t lit[ALPHA_LIT]; uint32_t cmd[ALPHA_CMD]; uint32_t dist[ALPHA_DIST_MAX]; };
+
+__global__ void __launch_bounds__(256) k_hist(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
+                                              const SegD* __restrict__ segs, const uint32_t* __restrict__ tile_seg, uint32_t n_tile,
+                                              const uint8_t* __restrict__ role, const uint32_t* __restrict__ ins_at,
+                                              const Cmd* __restrict__ cmds, MbHist* __restrict__ hist, Params P) {
+  __shared__ uint32_t s_h[CODE_STRIDE];
+  for (uint32_t i = threadIdx.x; i < CODE_STRIDE; i += 256) s_h[i] = 0;
+  __syncthreads();
+  uint32_t cur_mb = NONE;
+  const uint32_t t0 = blockIdx.x * 8, t1 = min(t0 + 8, n_tile);
+  for (uint32_t tile = t0; tile < t1; tile++) {
+    const SegD sg = segs[tile_seg[tile]];
+    if (sg.mb != cur_mb) {
+      if (cur_mb != NONE) {
+        __syncthreads();
+        uint32_t* g = reinterpret_cast<uint32_t*>(&hist[cur_mb]);
+        for (uint32_t i = threadIdx.x; i < CODE_STRIDE; i += 256) { uint32_t v = s_h[i]; if (v) atomicAdd(&g[i], v); s_h[i] = 0; }
+        __syncthreads();
+      }
+      cur_mb = sg.mb;
+    }
+    const ShardD sh = shards[sg.shard];
+    const uint32_t tile_rel = sg.rel_pos + (tile - sg.first_tile) * TILE;
+    const uint32_t tile_end = min(sg.rel_pos + sg.len, tile_rel + TILE);
+    for (uint32_t rel = tile_rel + threadIdx.x; rel < tile_end; rel += 256) {
+      const uint64_t p = sh.in_off + rel;
+      const uint32_t r = role[p];
+      if (r & 1) atomicAdd(&s_h[in[p]], 1u);
+      if (r & 4) {
+        uint32_t ins = ins_at[p >> P.sh];
+        uint32_t prefix = (r & 8) ? insert_only_prefix(ins) : cmds[(p + ins) >> P.sh].cmdPrefix;
+        atomicAdd(&s_h[ALPHA_LIT + prefix], 1u);
+      }
+      if (r & 2) {
+        const Cmd c = cmds[p >> P.sh];
+        if (c.cmdPrefix >= 128) atomicAdd(&s_h[ALPHA_LIT + ALPHA_CMD + (c.distPrefix & 0x3FF)], 1u);
+      }
+    }
+  }
+  __syncthreads();
+  if (cur_mb != NONE) {
+    uint32_t* g = reinterpret_cast<uint32_t*>(&hist[cur_mb]);
+    for (uint32_t i = threadIdx.x; i < CODE_STRIDE; i += 256) { uint32_t v = s_h[i]; if (v) atomicAdd(&g[i], v); }
+  }
+}
+
+// ---------------------------------------------------------------------------------------
+// K10.  One CTA (128 threads) per prefix code.  Histogram -> depths (<= 15) -> canonical codes ->
+// serialised tree bits.  The sort is a parallel rank-by-counting over the total order
+// (count asc, symbol desc); the two-queue merge and the serialisation are run by thread 0.
+// code table entry: bits << 8 | depth.
+__global__ void __launch_bounds__(128) k_huff(const uint32_t* __restrict__ hists, int hist_stride, int n_codes,
+                                              const int* __restrict__ alphabets, const int* __restrict__ hist_offsets,
+                                              uint32_t* __restrict__ codes, uint32_t* __restrict__ tree_bits,
+                                              uint32_t* __restrict__ tree_nbits) {
+  // code c of problem (blockIdx.x / n_codes) ; alphabets[c], hist_offsets[c] give its slice.
+  const int prob = blockIdx.x / n_codes, which = blockIdx.x % n_codes;
+  const int alphabet = alphabets[which];
+  const uint32_t* hist = hists + (size_t)prob * hist_stride + hist_offsets[which];
+  uint32_t* code_out = codes + (size_t)prob * hist_stride + hist_offsets[which];
+  __shared__ uint32_t s_hist[ALPHA_CMD];
+  __shared__ uint16_t s_sorted[ALPHA_CMD];
+  __shared__ uint32_t s_cnt[2 * ALPHA_CMD + 2];
+  __shared__ uint16_t s_lt[2 * ALPHA_CMD + 2], s_rt[2 * ALPHA_CMD + 2];
+  __shared__ uint8_t s_nd[2 * ALPHA_CMD + 2];
+  __shared__ uint8_t s_depth[ALPHA_CMD];
+  __shared__ uint16_t s_bits[ALPHA_CMD];
+  __shared__ uint8_t s_rle_sym[ALPHA_CMD + 8], s_rle_extra[ALPHA_CMD + 8];
+  __shared__ uint32_t s_tree[TREE_WORDS];
+  __shared__ int s_n, s_ok;
+  __shared__ uint32_t s_limit;
+  __shared__ uint16_t s_s4[4];
+  const int tid = threadIdx.x;
+  for (int i = tid; i < alphabet; i += 128) { s_hist[i] = hist[i]; s_depth[i] = 0; s_bits[i] = 0; }
+  for (int i = tid; i < TREE_WORDS; i += 128) s_tree[i] = 0;
+  __syncthreads();
+  if (tid == 0) {
+    int n = 0;
+    for (int i = 0; i < alphabet; i++) if (s_hist[i]) { if (n < 4) s_s4[n] = (uint16_t)i; n++; }
+    if (n == 0) s_s4[0] = 0;
+    s_n = n; s_limit = 1; s_ok = 0;
+  }
+  __syncthreads();
+  const int n = s_n;
+  if (n >= 2) {
+    for (;;) {
+      const uint32_t limit = s_limit;
+      for (int s = tid; s < alphabet; s += 128) {
+        uint32_t hs = s_hist[s];
+        if (!hs) continue;
+        uint32_t cs = max(hs, limit);
+        int rank = 0;
+        for (int t = 0; t < alphabet; t++) {
+          uint32_t ht = s_hist[t];
+          if (!ht || t == s) continue;
+          uint32_t ct = max(ht, limit);
+          rank += (ct < cs || (ct == cs && t > s)) ? 1 : 0;
+        }
+        s_sorted[rank] = (uint16_t)s;
+      }
+      __syncthreads();
+      if (tid == 0) {
+        s_ok = huff_depths_from_sorted(s_hist, s_sorted, n, limit, 15, s_cnt, s_lt, s_rt, s_nd, s_depth) ? 1 : 0;
+        if (!s_ok) s_limit = limit * 2;
+      }
+      __syncthreads();
+      if (s_ok) break;
+    }
+  }
+  if (tid == 0) {
+    BitSink w{s_tree, 0};
+    if (n <= 1) {
+      // context-map.ts:236-243: depth stays 0 (the single symbol costs no bits)
+      tree_store_single(w, alphabet, s_s4[0]);
+    } else {
+      huff_codes(s_depth, alphabet, s_bits);
+      tree_store(w, s_depth, alphabet, n, s_s4, s_rle_sym, s_rle_extra);
+    }
+    tree_nbits[blockIdx.x] = w.pos;
+  }
+  __syncthreads();
+  for (int i = tid; i < alphabet; i += 128) code_out[i] = ((uint32_t)s_bits[i] << 8) | s_depth[i];
+  for (int i = tid; i < TREE_WORDS; i += 128) tree_bits[(size_t)blockIdx.x * TREE_WORDS + i] = s_tree[i];
+}
+
+// ---------------------------------------------------------------------------------------
+// K11.  Tokens of one input position, in stream order (metablock.ts:355-383):
+//   [command symbol + insert/copy extra bits]  if a command starts here
+//   [literal symbol]                           if the byte is a literal
+//   [distance symbol + extra bits]             if a copy starts here and the command codes a distance
+struct Tok { uint32_t n0; uint64_t v0; uint32_t n1; uint64_t v1; };  // two fields of <= 63 bits
+
+__device__ __forceinline__ Tok position_tokens(const uint8_t* __restrict__ in, uint64_t p, uint32_t r,
+                                               const uint32_t* __restrict__ ins_at, const Cmd* __restrict__ cmds,
+                                               const uint32_t* __restrict__ code /* shared-memory table of the metablock */, int sh) {
+  Tok t; t.n0 = 0; t.v0 = 0; t.n1 = 0; t.v1 = 0;
+  if (r & 4) {
+    uint32_t ins = ins_at[p >> sh];
+    uint32_t prefix, copyField;
+    if (r & 8) { prefix = insert_only_prefix(ins); copyField = 2u << 25; }
+    else { const Cmd c = cmds[(p + ins) >> sh]; prefix = c.cmdPrefix; copyField = c.copyLen; }
+    uint32_t e = code[ALPHA_LIT + prefix];
+    uint64_t xv; uint32_t xn = cmd_extra(ins, copyField, &xv);
+    t.n0 = (e & 0xFF) + xn;
+    t.v0 = (uint64_t)(e >> 8) | (xv << (e & 0xFF));
+  }
+  if (r & 1) {
+    uint32_t e = code[in[p]];
+    t.n1 = e & 0xFF; t.v1 = e >> 8;
+  } else if (r & 2) {
+    const Cmd c = cmds[p >> sh];
+    if (c.cmdPrefix >= 128) {
+      uint32_t e = code[ALPHA_LIT + ALPHA_CMD + (c.distPrefix & 0x3FF)];
+      t.n1 = (e & 0xFF) + (c.distPrefix >> 10);
+      t.v1 = (uint64_t)(e >> 8) | ((uint64_t)c.distExtra << (e & 0xFF));
+    }
+  }
+  return t;
+}
+
+// per-tile bit totals
+__global__ void __launch_bounds__(256) k_tilebits(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
+                                                  const SegD* __restrict__ segs, const uint32_t* __restrict__ tile_seg,
+                                                  const uint8_t* __restrict__ role, const uint32_t* __restrict__ ins_at,
+                                                  const Cmd* __restrict__ cmds, const uint32_t* __restrict__ codes,
+                                                  uint32_t* __restrict__ tile_bits, Params P) {
+  __shared__ uint32_t s_code[CODE_STRIDE];
+  __shared__ uint32_t s_sum[8];
+  const uint32_t tile = blockIdx.x;
+  const SegD sg = segs[tile_seg[tile]];
+  const ShardD sh = shards[sg.shard];
+  for (uint32_t i = threadIdx.x; i < CODE_STRIDE; i += 256) s_code[i] = codes[(size_t)sg.mb * CODE_STRIDE + i];
+  __syncthreads();
+  const uint32_t tile_rel = sg.rel_pos + (tile - sg.first_tile) * TILE;
+  const uint32_t tile_end = min(sg.rel_pos + sg.len, tile_rel + TILE);
+  uint32_t bits = 0;
+  for (uint32_t rel = tile_rel + threadIdx.x; rel < tile_end; rel += 256) {
+    const uint64_t p = sh.in_off + rel;
+    const uint32_t r = role[p];
+    if (r) { Tok t = position_tokens(in, p, r, ins_at, cmds, s_code, P.sh); bits += t.n0 + t.n1; }
+  }
+  for (int o = 16; o; o >>= 1) bits += __shfl_xor_sync(0xffffffffu, bits, o);
+  if ((threadIdx.x & 31) == 0) s_sum[threadIdx.x >> 5] = bits;
+  __syncthreads();
+  if (threadIdx.x == 0) { uint32_t s = 0; for (int i = 0; i < 8; i++) s += s_sum[i]; tile_bits[tile] = s; }
+}
+
+__device__ __forceinline__ void gput(uint32_t* w, uint64_t& pos, uint32_t nbits, uint32_t value) {
+  if (!nbits) return;
+  uint64_t i = pos >> 5; uint32_t o = (uint32_t)pos & 31;
+  atomicOr(&w[i], value << o);
+  if (o + nbits > 32) atomicOr(&w[i + 1], value >> (32 - o));
+  pos += nbits;
+}
+
+// One CTA per shard: metablock headers + prefix codes, bit offset of every tile, shard byte length.
+// Header layout: metablock.ts:233-255 (ISLAST, [ISEMPTY], MNIBBLES, MLEN-1, [ISUNCOMPRESSED]) then
+// metablock.ts:327-343 (three NBLTYPES = 1, NPOSTFIX/NDIRECT, NTREESL = 1 + context mode LSB6,
+// NTREESD = 1), then the three prefix codes (literal, command, distance).
+__global__ void __launch_bounds__(256) k_offsets(const ShardD* __restrict__ shards, const MbD* __restrict__ mbs,
+                                                 const uint32_t* __restrict__ tile_bits, uint32_t* __restrict__ tile_off,
+                                                 const uint32_t* __restrict__ tree_bits, const uint32_t* __restrict__ tree_nbits,
+                                                 uint8_t* __restrict__ out, uint32_t* __restrict__ shard_bytes, Params P) {
+  __shared__ uint32_t s_part[256];
+  __shared__ uint64_t s_pos;
+  const ShardD sh = shards[blockIdx.x];
+  uint32_t* w = reinterpret_cast<uint32_t*>(out + sh.out_off);
+  const int tid = threadIdx.x;
+  if (tid == 0) {
+    uint64_t pos = 0;
+    if (sh.flags & 1) gput(w, pos, sh.start_nbits, sh.start_value);
+    s_pos = pos;
+  }
+  __syncthreads();
+  for (uint32_t m = sh.first_mb; m < sh.first_mb + sh.n_mb; m++) {
+    const MbD mb = mbs[m];
+    if (tid == 0) {
+      uint64_t pos = s_pos;
+      const bool isLast = mb.is_last != 0;
+      gput(w, pos, 1, isLast ? 1 : 0);
+      if (isLast) gput(w, pos, 1, 0);
+      int lg = mb.len == 1 ? 1 : log2_floor(mb.len - 1) + 1;
+      int mnibbles = (lg < 16 ? 16 : lg + 3) / 4;
+      gput(w, pos, 2, mnibbles - 4);
+      gput(w, pos, mnibbles * 4, mb.len - 1);
+      if (!isLast) gput(w, pos, 1, 0);
+      gput(w, pos, 3, 0);                                              // NBLTYPESL/I/D = 1
+      gput(w, pos, 6, P.npostfix | ((P.ndirect >> P.npostfix) << 2));  // NPOSTFIX, NDIRECT
+      gput(w, pos, 4, 0);                                              // NTREESL=1, mode LSB6, NTREESD=1
+      for (int t = 0; t < 3; t++) {
+        const uint32_t* tb = tree_bits + ((size_t)m * 3 + t) * TREE_WORDS;
+        uint32_t nb = tree_nbits[m * 3 + t];
+        for (uint32_t k = 0; k < nb; k += 32) gput(w, pos, min(32u, nb - k), nb - k >= 32 ? tb[k >> 5] : (tb[k >> 5] & ((1u << (nb - k)) - 1)));
+      }
+      s_pos = pos;
+    }
+    __syncthreads();
+    // exclusive scan of the metablock's tile bit counts, 256 tiles per round
+    for (uint32_t t0 = 0; t0 < mb.n_tile; t0 += 256) {
+      uint32_t v = (t0 + tid < mb.n_tile) ? tile_bits[mb.first_tile + t0 + tid] : 0;
+      s_part[tid] = v;
+      __syncthreads();
+      for (int o = 1; o < 256; o <<= 1) {
+        uint32_t add = tid >= o ? s_part[tid - o] : 0;
+        __syncthreads();
+        s_part[tid] += add;
+        __syncthreads();
+      }
+      uint32_t incl = s_part[tid];
+      if (t0 + tid < mb.n_tile) tile_off[mb.first_tile + t0 + tid] = (uint32_t)s_pos + incl - v;
+      __syncthreads();
+      if (tid == 255) s_pos += incl;
+      __syncthreads();
+    }
+  }
+  if (tid == 0) {
+    uint64_t pos = s_pos;
+    if (!(sh.flags & 2)) gput(w, pos, 6, 6);  // empty metadata block: ISLAST=0, MNIBBLES=3 (11), reserved 0, MSKIPBYTES=0 (00)
+    shard_bytes[blockIdx.x] = (uint32_t)((pos + 7) >> 3);
+  }
+}
+
+// One CTA per tile: recompute the tokens, scan their lengths, assemble the tile's bit span in
+// shared memory and store it (interior words with plain stores, the two boundary words with atomicOr).
+constexpr uint32_t STAGE_WORDS = 4096;
+__device__ __forceinline__ void sput(uint32_t* w, uint32_t pos, uint32_t nbits, uint64_t value) {
+  if (!nbits) return;
+  uint32_t i = pos >> 5, o = pos & 31;
+  unsigned long long lo = (unsigned long long)value << o;   // bits [0,64) of value << o
+  atomicOr(&w[i], (uint32_t)lo);
+  if (o + nbits > 32) atomicOr(&w[i + 1], (uint32_t)(lo >> 32));
+  if (o + nbits > 64) atomicOr(&w[i + 2], (uint32_t)(value >> (64 - o)));
+}
+
+__global__ void __launch_bounds__(256) k_write(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
+                                               const SegD* __restrict__ segs, const uint32_t* __restrict__ tile_seg,
+                                               const uint8_t* __restrict__ role, const uint32_t* __restrict__ ins_at,
+                                               const Cmd* __restrict__ cmds, const uint32_t* __restrict__ codes,
+                                               const uint32_t* __restrict__ tile_bits, const uint32_t* __restrict__ tile_off,
+                                               uint8_t* __restrict__ out, Params P) {
+  __shared__ uint32_t s_code[CODE_STRIDE];
+  __shared__ uint32_t s_stage[STAGE_WORDS];
+  __shared__ uint32_t s_warp[8];
+  const uint32_t tile = blockIdx.x;
+  const uint32_t total = tile_bits[tile];
+  if (total == 0) return;
+  const SegD sg = segs[tile_seg[tile]];
+  const ShardD sh = shards[sg.shard];
+  const int tid = threadIdx.x;
+  for (uint32_t i = tid; i < CODE_STRIDE; i += 256) s_code[i] = codes[(size_t)sg.mb * CODE_STRIDE + i];
+  const uint32_t off = tile_off[tile];
+  const uint32_t head = off & 31;
+  const uint32_t nwords = (head + total + 31) >> 5;
+  const bool staged = nwords + 2 <= STAGE_WORDS;
+  if (staged) for (uint32_t i = tid; i < nwords + 2; i += 256) s_stage[i] = 0;
+  __syncthreads();
+  const uint32_t tile_rel = sg.rel_pos + (tile - sg.first_tile) * TILE;
+  const uint32_t tile_end = min(sg.rel_pos + sg.len, tile_rel + TILE);
+  // thread t owns positions tile_rel + 4t .. +3
+  Tok tk[4]; uint32_t mine = 0;
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    uint32_t rel = tile_rel + 4 * tid + k;
+    tk[k].n0 = tk[k].n1 = 0; tk[k].v0 = tk[k].v1 = 0;
+    if (rel < tile_end) {
+      const uint64_t p = sh.in_off + rel;
+      const uint32_t r = role[p];
+      if (r) tk[k] = position_tokens(in, p, r, ins_at, cmds, s_code, P.sh);
+    }
+    mine += tk[k].n0 + tk[k].n1;
+  }
+  // block exclusive scan of `mine`
+  uint32_t incl = mine;
+  for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, incl, o); if ((tid & 31) >= o) incl += y; }
+  if ((tid & 31) == 31) s_warp[tid >> 5] = incl;
+  __syncthreads();
+  uint32_t wbase = 0;
+  for (int i = 0; i < (tid >> 5); i++) wbase += s_warp[i];
+  uint32_t bitpos = head + wbase + incl - mine;
+  uint32_t* gw = reinterpret_cast<uint32_t*>(out + sh.out_off) + (off >> 5);
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    if (staged) {
+      sput(s_stage, bitpos, tk[k].n0, tk[k].v0); bitpos += tk[k].n0;
+      sput(s_stage, bitpos, tk[k].n1, tk[k].v1); bitpos += tk[k].n1;
+    } else {
+      sput(gw, bitpos, tk[k].n0, tk[k].v0); bitpos += tk[k].n0;
+      sput(gw, bitpos, tk[k].n1, tk[k].v1); bitpos += tk[k].n1;
+    }
+  }
+  if (!staged) return;
+  __syncthreads();
+  for (uint32_t i = tid; i < nwords; i += 256) {
+    uint32_t v = s_stage[i];
+    if (i == 0 || i == nwords - 1) { if (v) atomicOr(&gw[i], v); }
+    else gw[i] = v;
+  }
+}
+
+}  // namespace bgpu

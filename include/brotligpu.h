@@ -1,0 +1,131 @@
+/* brotligpu.h — C ABI of the B200 Brotli encoder hot path (libbrotligpu.so).
+ *
+ * The reference (countertype/brotli-lib) has no FFI layer; its only boundary is the TypeScript
+ * API.  Every entry point below names the reference interface it stands in for (paths relative
+ * to the reference tree).  A Node-API addon (node/addon.cc) binds these 1:1; tests bind them
+ * with ctypes.  Plain C, no exceptions cross the boundary, every int-returning function yields
+ * 0 or a negative BGPU_E_* code.  There is NO CPU fallback: without a usable CUDA device the
+ * calls fail with BGPU_E_NO_DEVICE / BGPU_E_CUDA.
+ */
+#ifndef BROTLIGPU_H_
+#define BROTLIGPU_H_
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BGPU_OK 0
+#define BGPU_E_INVALID (-1)          /* NULL pointer / bad argument */
+#define BGPU_E_OUTPUT_TOO_SMALL (-2) /* *out_len is set to the size needed */
+#define BGPU_E_UNSUPPORTED (-3)      /* quality 1..4 (SimpleHasher / encodeFast: outside the hot path) */
+#define BGPU_E_NO_DEVICE (-4)
+#define BGPU_E_CUDA (-5)             /* bgpu_last_cuda_error() has the text */
+#define BGPU_E_NOMEM (-6)
+#define BGPU_E_STATE (-7)            /* stream used after finish */
+
+/* src/encode/enc-constants.ts:56-60  const enum EncoderMode */
+#define BGPU_MODE_GENERIC 0
+#define BGPU_MODE_TEXT 1
+#define BGPU_MODE_FONT 2
+
+typedef struct bgpu_ctx bgpu_ctx;
+typedef struct bgpu_stream bgpu_stream;
+
+/* Tunables that have no counterpart in the reference (it is single-threaded and serial).
+ * 0 selects the default.  segment_bytes = 0xFFFFFFFF selects the exact serial parse (one
+ * parse unit per shard, bit-identical commands to src/encode/backward-references.ts:14-134). */
+typedef struct bgpu_tuning {
+  uint32_t shard_bytes;     /* independent window, <= 4 MiB (default 4 MiB)      */
+  uint32_t segment_bytes;   /* greedy-parse unit inside a shard (default 64 KiB)                  */
+  uint32_t metablock_bytes; /* metablock size inside a shard (default = shard)                    */
+  uint32_t flags;           /* BGPU_F_*                                                           */
+} bgpu_tuning;
+#define BGPU_F_KEEP_DEVICE_OUTPUT 1u /* bench: skip the device->host gather (device-resident timing) */
+
+/* Context: owns the CUDA device, stream, scratch arenas.  Not thread-safe; one per thread.
+ * device_id < 0 selects the current device. */
+int bgpu_ctx_create(int device_id, bgpu_ctx** out);
+void bgpu_ctx_destroy(bgpu_ctx* ctx);
+int bgpu_ctx_set_tuning(bgpu_ctx* ctx, const bgpu_tuning* t);
+
+/* Upper bound of the stream size for n input bytes (any quality/mode). */
+size_t bgpu_max_compressed_size(size_t n);
+
+/* brotliEncode(input, {quality, lgwin, mode})            src/encode/encode.ts:50-90
+ * Options are clamped, never rejected (encode.ts:57-62); TEXT == GENERIC; FONT sets
+ * npostfix=1/ndirect=12 at quality >= 4 (enc-constants.ts:121-126).  n == 0 -> A1 01
+ * (encode.ts:92-103); quality 0 or n < 64 -> uncompressed metablocks (encode.ts:105-138); both
+ * are produced on the host (no kernel).  quality 1..4 -> BGPU_E_UNSUPPORTED.
+ * `in`/`out` are host buffers owned by the caller. */
+int bgpu_encode(bgpu_ctx* ctx, const uint8_t* in, size_t n, int quality, int lgwin, int mode,
+                uint8_t* out, size_t out_cap, size_t* out_len);
+
+/* Batch of independent streams (BASELINE config 5): item i is brotliEncode(in[i], ...). */
+int bgpu_encode_batch(bgpu_ctx* ctx, int count, const uint8_t* const* in, const size_t* n,
+                      int quality, int lgwin, int mode, uint8_t* const* out, const size_t* out_cap,
+                      size_t* out_len);
+
+/* Same pipeline with the input already resident in device memory (d_in: device pointer, 256-byte
+ * aligned, n + 64 bytes readable).  The compressed stream stays on the device unless `out` is
+ * non-NULL.  Used by bench.py for the device-resident `value`; the timed CUDA-event duration of
+ * the kernels is returned in *kernel_ms when non-NULL. */
+int bgpu_encode_device(bgpu_ctx* ctx, const void* d_in, size_t n, int quality, int lgwin, int mode,
+                       uint8_t* out, size_t out_cap, size_t* out_len, float* kernel_ms);
+
+/* new BrotliEncoder(opts) / update(chunk) / finish()     src/encode/encode.ts:290-409
+ * update copies the chunk (encode.ts:360-363) and returns the bytes completed so far (possibly
+ * none); *out stays valid until the next call on the same stream. */
+int bgpu_stream_create(bgpu_ctx* ctx, int quality, int lgwin, int mode, bgpu_stream** s);
+int bgpu_stream_update(bgpu_stream* s, const uint8_t* chunk, size_t n, const uint8_t** out, size_t* out_len);
+int bgpu_stream_finish(bgpu_stream* s, const uint8_t** out, size_t* out_len);
+void bgpu_stream_destroy(bgpu_stream* s);
+
+/* ---- stage entry points for parity tests (device does the work; host buffers in/out) ---- */
+
+/* HashChainHasher.findLongestMatch, chain part            src/encode/hash-chains.ts:117-152
+ * For every position p with p + 4 <= n: best match over the <= 1<<(quality-1) most recent
+ * positions with the same hashBytes4 key (match.ts:162-172), maxLength = min(n-p, 128),
+ * maxBackward = min(p, 4 MiB - 16).  len[p] == 0 when none.  n <= 4 MiB. */
+int bgpu_stage_match_candidates(bgpu_ctx* ctx, const uint8_t* in, size_t n, int quality, int lgwin,
+                                uint32_t* len, uint32_t* dist);
+
+/* createBackwardReferences + trailing-insert merge        src/encode/backward-references.ts:14-134,
+ * encode.ts:250-267.  Commands use the reference's 16-byte layout (src/encode/command.ts:138-144:
+ * insertLen u32, copyLen u32, distExtra u32, cmdPrefix u16, distPrefix u16).  Honors the context's
+ * segment_bytes (exact serial parse when 0xFFFFFFFF). n <= 4 MiB. */
+int bgpu_stage_commands(bgpu_ctx* ctx, const uint8_t* in, size_t n, int quality, int lgwin, int mode,
+                        void* cmds, size_t cmd_cap, size_t* ncmd);
+
+/* storeMetaBlockTrivial on caller-supplied commands       src/encode/metablock.ts:290-389
+ * (histograms :305-325, createHuffmanTree entropy-encode.ts:24-131, convertBitDepthsToSymbols
+ * :234-258, buildAndStoreHuffmanTree context-map.ts:215-347, emit loop :355-383).
+ * start_nbits/start_value: bits already in the stream (the window header).  tables (optional,
+ * 3 x (u32 hist, u8 depth, u16 bits) laid out as oracle's TrivialTables) receives the histograms
+ * and codes. */
+int bgpu_stage_store_trivial(bgpu_ctx* ctx, const uint8_t* in, size_t n, const void* cmds, size_t ncmd,
+                             int is_last, int mode, unsigned start_nbits, unsigned start_value,
+                             uint8_t* out, size_t out_cap, size_t* out_len, uint64_t* out_bits, void* tables);
+
+/* createHuffmanTree + convertBitDepthsToSymbols           src/encode/entropy-encode.ts:24-131, 234-258
+ * and buildAndStoreHuffmanTree                            src/encode/context-map.ts:215-347
+ * count histograms of `alphabet` symbols each (<= 704).  tree_bits: 1 KiB per histogram of
+ * serialised prefix-code bits, tree_nbits their lengths (either may be NULL). */
+int bgpu_stage_huffman(bgpu_ctx* ctx, const uint32_t* hist, int count, int alphabet,
+                       uint8_t* depths, uint16_t* bits, uint8_t* tree_bits, uint32_t* tree_nbits);
+
+/* Per-kernel CUDA-event milliseconds of the last encode call on this context.  names/ms receive up
+ * to cap entries; returns the number of stages. */
+int bgpu_stage_timings(bgpu_ctx* ctx, const char** names, float* ms, int cap);
+/* Number of kernel launches issued by the last encode call. */
+int bgpu_last_launch_count(bgpu_ctx* ctx);
+
+const char* bgpu_strerror(int code);
+const char* bgpu_last_cuda_error(void);
+int bgpu_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BROTLIGPU_H_ */

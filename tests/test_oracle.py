@@ -1,0 +1,137 @@
+"""CPU tier: the oracle (C++ restatement of brotli-lib's encoder) against everything the
+reference's own tests pin for the encode path and against the committed goldens."""
+import hashlib
+import json
+import os
+import re
+
+import numpy as np
+import pytest
+
+import _oracle as O
+from conftest import CORPUS, SYNTH, FUZZ_SIZES, Xorshift32, fuzz_inputs, load_input, ROOT
+
+QUALITIES = [5, 9, 10, 11]
+
+
+def _roundtrip(stream, data):
+    assert O.decode(stream, len(data), "system") == data
+    if O.have_ref_decoder():
+        assert O.decode(stream, len(data), "ref") == data
+
+
+def test_decoder_harness_on_reference_vectors():
+    # test/brotli.test.ts:88-101: canonical decoder vectors validate the independent decoder itself
+    vec = os.path.join(ROOT, "tests", "golden", "vectors")
+    data = os.path.join(ROOT, "tests", "golden", "data")
+    for name in ["alice29.txt", "monkey", "x", "10x10y"]:
+        comp = open(os.path.join(vec, name + ".compressed"), "rb").read()
+        plain = open(os.path.join(data, name), "rb").read()
+        assert O.decode(comp, len(plain)) == plain
+    assert O.decode(open(os.path.join(vec, "empty.compressed"), "rb").read(), 0) == b""
+
+
+@pytest.mark.parametrize("name", CORPUS + SYNTH)
+def test_roundtrip_corpus(name):
+    data = load_input(name)
+    for q in QUALITIES:
+        for mode in (0, 2):
+            _roundtrip(O.encode(data, q, 22, mode), data)
+    _roundtrip(O.encode(data, 5, 24, 1), data)
+    _roundtrip(O.encode(data, 11, 24, 1), data)
+    _roundtrip(O.encode(data, 5, 22, 0, force_trivial=True), data)
+
+
+def test_empty_input_is_a1_01():
+    # encode.ts:92-103, test/brotli.test.ts:105-110
+    for q in (0, 5, 11):
+        assert O.encode(b"", q) == bytes([0xA1, 0x01])
+
+
+def test_ratio_assertion_abcdefghij():
+    # test/brotli.test.ts:225-233: the only ratio assertion in the reference
+    data = load_input("abc1000")
+    s = O.encode(data, 5)
+    assert len(s) < 0.2 * len(data)
+    _roundtrip(s, data)
+
+
+def test_fuzz_matrix():
+    # test/brotli.test.ts:264-281 (qualities 1..4 are outside the hot path: SimpleHasher)
+    for name, data in fuzz_inputs():
+        for q in (0, 5, 6, 7, 8, 9, 10, 11):
+            _roundtrip(O.encode(data, q), data)
+
+
+def test_font_vs_generic():
+    # test/brotli.test.ts:152-174
+    data = load_input("font4k")
+    _roundtrip(O.encode(data, 5, 22, 0), data)
+    _roundtrip(O.encode(data, 5, 22, 2), data)
+
+
+def test_streaming_matrix():
+    # test/brotli.test.ts:283-312: seed 0x12345678, 4096 random bytes, chunk sizes 1..257
+    for q in (5, 6, 7, 8, 9, 10, 11):
+        g = Xorshift32(0x12345678)
+        data = g.bytes(4096)
+        enc = O.StreamEncoder(q)
+        out, pos = [], 0
+        while pos < len(data):
+            k = 1 + (g.next() % 257)
+            out.append(enc.update(data[pos:pos + k]))
+            pos += k
+        out.append(enc.finish())
+        _roundtrip(b"".join(out), data)
+
+
+def test_streaming_multiblock_and_empty():
+    data = load_input("alice29.txt")
+    enc = O.StreamEncoder(5)
+    parts = [enc.update(data[i:i + 50000]) for i in range(0, len(data), 50000)] + [enc.finish()]
+    _roundtrip(b"".join(parts), data)
+    enc = O.StreamEncoder(5)
+    _roundtrip(enc.finish(), b"")
+
+
+def test_tables_against_reference_literals():
+    ref = "/root/reference/src/encode"
+    if not os.path.isdir(ref):
+        pytest.skip("reference tree not present on this machine")
+    src = open(os.path.join(ref, "context.ts")).read()
+    m = re.search(r"CONTEXT_LOOKUP_TABLE = new Uint8Array\(\[(.*?)\]\)", src, re.S)
+    nums = [int(x) for x in re.findall(r"\d+", re.sub(r"//.*", "", m.group(1)))]
+    lut = np.ctypeslib.as_array(O.lib().oracle_context_lut(), shape=(2048,))
+    assert nums == lut.tolist()
+    src = open(os.path.join(ref, "fast-log.ts")).read()
+    m = re.search(r"kLog2Table = new Float64Array\(\[(.*?)\]\)", src, re.S)
+    vals = [float(x) for x in re.findall(r"[0-9]+\.[0-9]+", m.group(1))]
+    tab = np.ctypeslib.as_array(O.lib().oracle_log2_table(), shape=(256,))
+    assert len(vals) == 256
+    assert np.max(np.abs(np.array(vals) - tab)) < 1e-14
+
+
+def test_golden_streams():
+    """Pins the oracle against regressions: sizes and SHA-256 of its streams, written by
+    tests/golden/make_golden.py in the build container."""
+    path = os.path.join(ROOT, "tests", "golden", "oracle_streams.json")
+    gold = json.load(open(path))
+    for key, (size, sha) in gold.items():
+        name, q, lgwin, mode = key.split("|")
+        s = O.encode(load_input(name), int(q), int(lgwin), int(mode))
+        assert len(s) == size, key
+        assert hashlib.sha256(s).hexdigest() == sha, key
+
+
+def test_stage_functions_consistent():
+    """oracle stage entry points agree with the one-shot encoder (trivial store of its own commands)."""
+    data = load_input("alice29.txt")
+    for q, mode in ((5, 0), (9, 2), (11, 0)):
+        cm = O.commands(data, q, 22, mode)
+        s, nbits, tab = O.store_trivial(data, cm, True, mode == 2, 4, 0b1011)
+        assert s == O.encode(data, q, 22, mode, force_trivial=True)
+        assert int(tab["litHisto"].sum()) == int(cm["insertLen"].sum())
+        d, b = O.huffman(tab["cmdHisto"])
+        assert np.array_equal(d, tab["cmdDepths"]) and np.array_equal(b, tab["cmdBits"])
+    ln, ds = O.h5_chain_best(data[:20000], 5)
+    assert ln.max() <= 128 and (ds[ln > 0] > 0).all()
