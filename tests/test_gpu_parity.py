@@ -1,0 +1,205 @@
+"""GPU tier (-m gpu): the CUDA path, called through the C ABI, against the oracle.
+
+Bit-exact: match candidates, greedy commands (exact parse mode), histograms, Huffman depths and
+codes, serialised prefix codes, and the packed stream given the same commands.  Every stream
+round-trips through Google's C decoder; sizes are compared with the oracle's."""
+import numpy as np
+import pytest
+
+import _oracle as O
+from conftest import CORPUS, SYNTH, Xorshift32, fuzz_inputs, load_input
+
+pytestmark = pytest.mark.gpu
+
+EXACT = 0xFFFFFFFF
+
+
+def _rt(stream, data):
+    assert O.decode(stream, len(data), "system") == data
+    if O.have_ref_decoder():
+        assert O.decode(stream, len(data), "ref") == data
+
+
+@pytest.mark.parametrize("name", ["alice29.txt", "enc-ttf.bin", "zeros", "quickfox_repeated", "backward65536", "random_org_10k.bin", "monkey"])
+@pytest.mark.parametrize("quality", [5, 7, 9])
+def test_match_candidates_bit_exact(gpu_ctx, name, quality):
+    data = load_input(name)
+    ln, ds = gpu_ctx.stage_match_candidates(data, quality, 22)
+    oln, ods = O.h5_chain_best(data, quality, 22)
+    assert np.array_equal(ln, oln)
+    assert np.array_equal(ds, ods)
+
+
+@pytest.mark.parametrize("name", ["alice29.txt", "enc-ttf.bin", "zeros", "quickfox_repeated", "html-content.bin", "mapsdatazrh", "abc1000", "font4k"])
+@pytest.mark.parametrize("quality,mode", [(5, 0), (5, 2), (6, 0), (7, 0), (9, 2)])
+def test_commands_bit_exact_in_exact_parse_mode(gpu_ctx, name, quality, mode):
+    data = load_input(name)
+    gpu_ctx.set_tuning(segment_bytes=EXACT)
+    try:
+        cm = gpu_ctx.stage_commands(data, quality, 22, mode)
+    finally:
+        gpu_ctx.set_tuning()
+    ocm = O.commands(data, quality, 22, mode)
+    assert len(cm) == len(ocm)
+    assert cm.tobytes() == ocm.tobytes()
+
+
+def test_huffman_bit_exact(gpu_ctx):
+    rng = np.random.default_rng(7)
+    for alphabet in (256, 704, 64, 124, 18, 26):
+        hs = []
+        for kind in range(8):
+            if kind == 0:
+                h = rng.integers(0, 1000, alphabet)
+            elif kind == 1:
+                h = (rng.random(alphabet) < 0.1) * rng.integers(1, 100000, alphabet)
+            elif kind == 2:
+                h = np.zeros(alphabet, dtype=np.int64)
+                h[rng.choice(alphabet, 3, replace=False)] = [5, 9, 1]
+            elif kind == 3:
+                h = 2 ** rng.integers(0, 31, alphabet)
+            elif kind == 4:
+                h = np.ones(alphabet, dtype=np.int64)
+            elif kind == 5:
+                h = np.zeros(alphabet, dtype=np.int64)
+                h[alphabet // 2] = 17
+            elif kind == 6:
+                h = np.zeros(alphabet, dtype=np.int64)
+            else:
+                h = np.array([int(1.6 ** i) % (2 ** 32 - 1) + 1 for i in range(alphabet)])
+            hs.append(np.asarray(h, dtype=np.uint32))
+        d, b, tb, tn = gpu_ctx.stage_huffman(np.stack(hs))
+        for i, h in enumerate(hs):
+            od, ob, obytes, onb = O.build_store_tree(h)
+            assert int(tn[i]) == onb, (alphabet, i)
+            assert tb[i].tobytes()[: (onb + 7) // 8] == obytes, (alphabet, i)
+            assert np.array_equal(d[i], od) and np.array_equal(b[i], ob), (alphabet, i)
+
+
+@pytest.mark.parametrize("name", ["alice29.txt", "enc-ttf.bin", "zeros", "html-content.bin", "random_org_10k.bin", "monkey", "ramp"])
+@pytest.mark.parametrize("quality,mode", [(5, 0), (9, 2), (11, 0)])
+def test_store_trivial_bit_exact_given_oracle_commands(gpu_ctx, name, quality, mode):
+    """K7 + K10 + K11 fed with the oracle's commands (q11: Zopfli commands with 2/3-byte copies)."""
+    data = load_input(name)
+    ocm = O.commands(data, quality, 22, mode)
+    ostream, obits, otab = O.store_trivial(data, ocm, True, mode == 2, 4, 0b1011)
+    stream, tab = gpu_ctx.stage_store_trivial(data, ocm, True, mode, 4, 0b1011)
+    for f in ("litHisto", "cmdHisto", "distHisto", "litDepths", "cmdDepths", "distDepths", "litBits", "cmdBits", "distBits"):
+        assert np.array_equal(tab[f], otab[f]), f
+    assert stream == ostream
+    _rt(stream, data)
+
+
+@pytest.mark.parametrize("name", CORPUS + SYNTH)
+def test_end_to_end_exact_mode_equals_oracle_trivial(gpu_ctx, name):
+    """Whole GPU pipeline in exact parse mode == oracle encode with trivial metablocks, byte for byte."""
+    data = load_input(name)
+    if len(data) < 64:
+        pytest.skip("host-only path")
+    gpu_ctx.set_tuning(segment_bytes=EXACT)
+    try:
+        for q, mode in ((5, 0), (6, 2), (9, 0)):
+            s = gpu_ctx.encode(data, q, 22, mode)
+            assert s == O.encode(data, q, 22, mode, force_trivial=True), (q, mode)
+    finally:
+        gpu_ctx.set_tuning()
+
+
+@pytest.mark.parametrize("name", CORPUS + SYNTH)
+def test_end_to_end_default_roundtrip_and_size(gpu_ctx, name):
+    data = load_input(name)
+    for q in (5, 9):
+        for mode in (0, 1, 2):
+            s = gpu_ctx.encode(data, q, 22, mode)
+            _rt(s, data)
+            ref = len(O.encode(data, q, 22, mode))
+            # trivial metablocks for now: report-only bound, the 0.5 % gate is tracked in DESIGN.md
+            assert len(s) <= ref * 1.15 + 64, (name, q, mode, len(s), ref)
+
+
+def test_fuzz_matrix_all_supported_qualities(gpu_ctx):
+    # test/brotli.test.ts:264-281
+    for name, data in fuzz_inputs():
+        for q in (0, 5, 6, 7, 8, 9):
+            s = gpu_ctx.encode(data, q)
+            _rt(s, data)
+            if len(data) < 64 or q == 0:
+                assert s == O.encode(data, q)   # host-only paths are byte-identical
+
+
+def test_unsupported_qualities_fail_loudly(gpu_ctx):
+    import brotli_lib_b200._lib as L
+    for q in (1, 2, 3, 4):
+        with pytest.raises(L.BgpuError):
+            gpu_ctx.encode(bytes(1000), q)
+
+
+@pytest.mark.parametrize("shard,seg,mb", [(65536, 16384, 0), (100000, 4096, 8192), (1 << 20, 65536, 131072), (4096, 1024, 1024)])
+def test_stitched_shards_segments_metablocks(gpu_ctx, shard, seg, mb):
+    """>= 3 shards, ragged tail, matches/literals/zero runs at the boundaries."""
+    parts = [load_input("alice29.txt"), bytes(70001), load_input("enc-ttf.bin")[:150003], load_input("quickfox_repeated")[:50000],
+             load_input("random_org_10k.bin")]
+    data = b"".join(parts)
+    gpu_ctx.set_tuning(shard_bytes=shard, segment_bytes=seg, metablock_bytes=mb)
+    try:
+        for q, mode in ((5, 0), (9, 2)):
+            _rt(gpu_ctx.encode(data, q, 22, mode), data)
+    finally:
+        gpu_ctx.set_tuning()
+
+
+@pytest.mark.parametrize("lgwin", [10, 12, 16, 17, 18, 24])
+def test_small_windows(gpu_ctx, lgwin):
+    data = load_input("alice29.txt")[:40000]
+    _rt(gpu_ctx.encode(data, 5, lgwin), data)
+
+
+def test_batch_of_independent_streams(gpu_ctx):
+    g = Xorshift32(0xF0470001)
+    base = load_input("enc-ttf.bin")
+    items = [b"", b"x", base[:63], base[:64], base[1000:1000 + 4096], base[:300000], load_input("alice29.txt"), bytes(5000), g.bytes(3000)]
+    outs = gpu_ctx.encode_batch(items, 5, 22, 2)
+    assert len(outs) == len(items)
+    for d, s in zip(items, outs):
+        _rt(s, d)
+        assert s == gpu_ctx.encode(d, 5, 22, 2)
+
+
+def test_streaming_api(gpu_ctx):
+    import brotli_lib_b200 as B
+    # test/brotli.test.ts:283-312
+    for q in (5, 9):
+        g = Xorshift32(0x12345678)
+        data = g.bytes(4096)
+        enc = B.BrotliEncoder({"quality": q}, context=gpu_ctx)
+        out, pos = [], 0
+        while pos < len(data):
+            k = 1 + (g.next() % 257)
+            out.append(enc.update(data[pos:pos + k]))
+            pos += k
+        out.append(enc.finish())
+        _rt(b"".join(out), data)
+    # multi-shard stream (small shards) and the empty stream
+    data = load_input("alice29.txt")
+    gpu_ctx.set_tuning(shard_bytes=32768)
+    try:
+        enc = B.BrotliEncoder(quality=5, context=gpu_ctx)
+        parts = [enc.update(data[i:i + 10000]) for i in range(0, len(data), 10000)] + [enc.finish()]
+        assert sum(1 for p in parts[:-1] if p) >= 3
+        _rt(b"".join(parts), data)
+    finally:
+        gpu_ctx.set_tuning()
+    enc = B.BrotliEncoder(quality=5, context=gpu_ctx)
+    _rt(enc.finish(), b"")
+
+
+def test_full_size_shard_properties(gpu_ctx):
+    """4 MiB shards (BASELINE config 2 shape, 3 shards): round trip + size-independent properties."""
+    g = np.random.default_rng(5)
+    text = load_input("alice29.txt")
+    blob = (text * 40)[: (1 << 22) + 12345] + g.integers(0, 256, 1 << 21, dtype=np.uint8).tobytes() + bytes(1 << 21) + load_input("enc-ttf.bin") * 3
+    s = gpu_ctx.encode(blob, 5, 22, 0)
+    _rt(s, blob)
+    assert len(s) < len(blob)
+    # idempotence: same input, same stream
+    assert s == gpu_ctx.encode(blob, 5, 22, 0)

@@ -1,0 +1,100 @@
+"""CPU tier: the __host__ __device__ format code the kernels run (brotli_lib_b200/csrc/codec_common.cuh),
+compiled for the host, against the oracle; plus the C-ABI surface check (no compute without a GPU)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+
+import _oracle as O
+from conftest import ROOT, load_input
+
+
+def _hosttest():
+    from brotli_lib_b200 import build
+    return C.CDLL(build.build_hosttest())
+
+
+def test_huffman_and_tree_serialisation_match_oracle():
+    H = _hosttest()
+    rng = np.random.default_rng(1)
+    for trial in range(300):
+        alpha = int(rng.choice([256, 704, 64, 124, 18, 26, 272, 10]))
+        kind = trial % 6
+        if kind == 0:
+            h = rng.integers(0, 1000, alpha)
+        elif kind == 1:
+            h = (rng.random(alpha) < 0.1) * rng.integers(1, 100000, alpha)
+        elif kind == 2:
+            h = np.zeros(alpha, dtype=np.int64)
+            idx = rng.choice(alpha, size=min(alpha, int(rng.integers(0, 6))), replace=False)
+            h[idx] = rng.integers(1, 50, len(idx))
+        elif kind == 3:
+            h = 2 ** rng.integers(0, 31, alpha)
+        elif kind == 4:
+            h = np.ones(alpha, dtype=np.int64)
+        else:
+            h = np.array([int(1.6 ** i) % (2 ** 32 - 1) + 1 for i in range(alpha)])
+        h = np.ascontiguousarray(h, dtype=np.uint32)
+        d = np.zeros(alpha, np.uint8)
+        b = np.zeros(alpha, np.uint16)
+        tw = np.zeros(256, np.uint32)
+        nb = H.bgpu_hosttest_huffman(h.ctypes.data, alpha, d.ctypes.data, b.ctypes.data, tw.ctypes.data)
+        od, ob, obytes, onb = O.build_store_tree(h)
+        assert nb == onb and tw.tobytes()[: (nb + 7) // 8] == obytes
+        assert np.array_equal(d, od) and np.array_equal(b, ob)
+
+
+def test_command_coding_matches_oracle_commands():
+    H = _hosttest()
+    out = np.zeros(1, dtype=O.CMD_DTYPE)
+    val = C.c_uint64(0)
+    H.bgpu_hosttest_cmd_extra.restype = C.c_uint32
+    for name, q, mode in (("alice29.txt", 5, 0), ("enc-ttf.bin", 9, 2), ("enc-ttf.bin", 11, 0)):
+        data = load_input(name)
+        cm = O.commands(data, q, 22, mode)
+        npostfix, ndirect = (1, 12) if mode == 2 else (0, 0)
+        for c in cm[:: max(1, len(cm) // 3000)]:
+            copy_len = int(c["copyLen"]) & 0x1FFFFFF
+            if copy_len == 0:
+                H.bgpu_hosttest_make_insert_cmd(int(c["insertLen"]), out.ctypes.data)
+                assert out[0] == c
+                continue
+            # invert the distance prefix code (command.ts:225-248) to recover the distance code
+            dcode = int(c["distPrefix"]) & 0x3FF
+            if dcode < 16 + ndirect:
+                code = dcode
+            else:
+                nbits = int(c["distPrefix"]) >> 10
+                h = (dcode - ndirect - 16) >> npostfix
+                lo = (dcode - ndirect - 16) & ((1 << npostfix) - 1)
+                offset = ((2 + (h & 1)) << nbits) - 4
+                code = ((offset + int(c["distExtra"])) << npostfix) + lo + ndirect + 16
+            H.bgpu_hosttest_make_cmd(int(c["insertLen"]), copy_len, code, ndirect, npostfix, out.ctypes.data)
+            assert out[0] == c
+            assert H.bgpu_hosttest_cmd_extra(int(c["insertLen"]), int(c["copyLen"]), C.byref(val)) <= 48
+
+
+def test_c_abi_library_exports_every_declared_symbol():
+    from brotli_lib_b200 import _lib
+    header = open(os.path.join(ROOT, "include", "brotligpu.h")).read()
+    declared = sorted(set(re.findall(r"\b(bgpu_[a-z_]+)\s*\(", header)))
+    assert set(declared) == set(_lib.SYMBOLS)
+    assert os.path.exists(_lib.LIB_PATH), "run python -m brotli_lib_b200.build"
+    L = C.CDLL(_lib.LIB_PATH)
+    for sym in declared:
+        assert hasattr(L, sym), sym
+    L.bgpu_max_compressed_size.restype = C.c_size_t
+    L.bgpu_max_compressed_size.argtypes = [C.c_size_t]
+    assert L.bgpu_max_compressed_size(1 << 20) >= (1 << 20) + 1024
+    L.bgpu_strerror.restype = C.c_char_p
+    assert b"quality" in L.bgpu_strerror(-3)
+
+
+def test_product_does_not_reference_the_oracle():
+    pkg = os.path.join(ROOT, "brotli_lib_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cc", ".h")):
+                text = open(os.path.join(dirpath, f), errors="ignore").read()
+                assert "liboracle" not in text and "_oracle" not in text and "oracle/" not in text.replace("the oracle", ""), f
