@@ -109,18 +109,21 @@ def time_oracle(sample, quality, lgwin, mode, threads):
     return sample.size / dt / 1e9, total, dt
 
 
-# Algorithmic (compulsory) HBM bytes per input byte of each kernel, command-record traffic left out
-# (lower bound; DESIGN.md "Kernels and rooflines").  M = output bytes per input byte.
+# ALGORITHMIC (compulsory) HBM bytes per input byte of each stage: SURVEY.md §8(d) / DESIGN.md
+# "Kernels and rooflines".  M = output bytes per input byte.  Command-record terms (16 C) are left
+# out (C is not known on the host), so the figures are lower bounds.  The match-finding stage
+# (K1+K2+K3 = both sort passes + the probe) is judged as ONE unit, as §8(d) defines it:
+# N (input) + 8 N (best {len, dist} per position) = 9 B per input byte; the sorted (position, bytes)
+# arrays in between are overhead, not algorithmic bytes.
+STAGE_OF = {"k_sort_pass0": "match_finding", "k_sort_pass1": "match_finding", "k_probe": "match_finding",
+            "k_parse": "parse", "k_stitch": "parse", "k_hist": "histograms", "k_huff": "huffman",
+            "k_tilebits": "bit_writer", "k_offsets": "bit_writer", "k_write": "bit_writer"}
 ALGO_BYTES = {
-    "k_link": lambda M: 1 + 4,          # read input, write u32 link
-    "k_probe": lambda M: 1 + 4 + 4,     # read input + link, write u32 best
-    "k_parse": lambda M: 1 + 4 + 1,     # read input + best, write role
-    "k_stitch": lambda M: 0,
-    "k_hist": lambda M: 1 + 1,          # read input + role
-    "k_huff": lambda M: 0,
-    "k_tilebits": lambda M: 1 + 1,
-    "k_offsets": lambda M: 0,
-    "k_write": lambda M: 1 + 1 + M,     # read input + role, write stream
+    "match_finding": lambda M: 9.0,        # §8(d) K1+K2+K3
+    "parse": lambda M: 9.0,                # §8(d) K5: N + 8N (+16C)
+    "histograms": lambda M: 1.0,           # §8(d) K7: L (+16C + 4AH), L <= N
+    "huffman": lambda M: 0.0,              # 7 A H bytes: negligible
+    "bit_writer": lambda M: 1.0 + M,       # §8(d) K11: L + M (+16C + 3AH)
 }
 
 
@@ -201,31 +204,37 @@ def run_gpu(args, rank, world, local_rank):
             raise RuntimeError(f"bgpu_encode rc={rc}")
         return ln.value
 
-    # ---- device-resident timing
+    # all work of the context goes to torch's current stream so that torch.cuda.Event brackets it
+    stream = torch.cuda.current_stream()
+    ctx.set_stream(stream.cuda_stream)
+    # ---- device-resident timing (CUDA events on the launching stream)
     for _ in range(max(args.warmup, 3)):
         step_device()
     sampler = ClockSampler(local_rank)
     stage_ms = {}
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     sampler.start()
-    t0 = time.perf_counter()
+    ev0.record(stream)
     out_size = 0
     for _ in range(args.steps):
         out_size, kms, _ = step_device()
         for name, ms in ctx.timings():
             stage_ms[name] = stage_ms.get(name, 0.0) + ms
-    torch.cuda.synchronize()
-    t_dev = time.perf_counter() - t0
+    ev1.record(stream)
+    barrier()
+    t_dev = ev0.elapsed_time(ev1) * 1e-3
     clocks = sampler.stop()
     launches = ctx.launch_count() * args.steps
-    # ---- end to end (host buffers)
+    # ---- end to end (pinned host buffers; H2D + kernels + D2H + stitch inside the timed region)
     step_e2e()
     barrier()
-    t0 = time.perf_counter()
+    ev0.record(stream)
     for _ in range(args.steps):
         e2e_size = step_e2e()
-    torch.cuda.synchronize()
-    t_e2e = time.perf_counter() - t0
+    ev1.record(stream)
+    barrier()
+    t_e2e = ev0.elapsed_time(ev1) * 1e-3
     times = torch.tensor([t_dev, t_e2e], dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
@@ -240,26 +249,35 @@ def run_gpu(args, rank, world, local_rank):
     if rank == 0:
         M = out_size / n
         peak, which = peaks()
-        per_kernel = {}
+        per_kernel, per_stage = {}, {}
         for name, ms in stage_ms.items():
             avg = ms / args.steps
-            ab = ALGO_BYTES.get(name, lambda M: 0)(M) * n
-            per_kernel[name] = {"ms": round(avg, 3), "algo_GBps": round(ab / (avg * 1e-3) / 1e9, 1) if avg > 0 else None}
-        top = max((k for k in per_kernel if k.startswith("k_")), key=lambda k: per_kernel[k]["ms"])
-        achieved = per_kernel[top]["algo_GBps"] or 0.0
+            per_kernel[name] = round(avg, 3)
+            st = STAGE_OF.get(name)
+            if st:
+                per_stage[st] = per_stage.get(st, 0.0) + avg
+        stages = {}
+        for st, avg in per_stage.items():
+            ab = ALGO_BYTES[st](M) * n
+            stages[st] = {"ms": round(avg, 3), "algo_bytes": int(ab), "algo_GBps": round(ab / (avg * 1e-3) / 1e9, 1) if avg > 0 else None,
+                          "frac": round(ab / (avg * 1e-3) / 1e9 / peak, 4) if avg > 0 else None}
+        top = max(stages, key=lambda k: stages[k]["ms"])
+        achieved = stages[top]["algo_GBps"] or 0.0
         line = {
             "metric": METRIC, "value": n * world * args.steps / t_dev / 1e9, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": t_dev / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u8", "data": "synthetic",
             "config": {"workload": f"q{args.quality} GENERIC lgwin{args.lgwin}, {args.size_mb} MiB synthetic mixed text/binary per GPU (BASELINE config 2), "
                                    f"{(n + (1 << 22) - 1) >> 22} independent 4 MiB shards, H5 hash-chain matcher depth {1 << (args.quality - 1)}",
+                       "timing": "CUDA events on the launching stream, max over ranks",
                        "l2": "input (1 GiB) and every intermediate array exceed the 126 MB L2; no flush needed",
                        "compressed_ratio": round(M, 4), "verified_roundtrip": verified, "datagen_s": round(t_gen, 1)},
             "e2e": {"value": n * world * args.steps / t_e2e / 1e9, "unit": UNIT, "h2d_bytes_per_step": n, "d2h_bytes_per_step": int(e2e_size)},
             "gpu_launches": launches,
             "clocks": clocks,
             "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
-                         "traffic": None, "peak_source": which, "per_kernel": per_kernel},
+                         "traffic": None, "peak_source": which, "whole_step_frac": round((1 + M) * n * args.steps / t_dev / 1e9 / peak, 4),
+                         "stages": stages, "launch_ms": per_kernel},
         }
         if world == 1 and not args.no_cpu:
             sample = cpu_reference_sample(args.quality)

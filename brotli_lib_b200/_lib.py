@@ -10,7 +10,7 @@ E_OUTPUT_TOO_SMALL = -2
 E_UNSUPPORTED = -3
 
 SYMBOLS = [
-    "bgpu_ctx_create", "bgpu_ctx_destroy", "bgpu_ctx_set_tuning", "bgpu_max_compressed_size", "bgpu_encode",
+    "bgpu_ctx_create", "bgpu_ctx_destroy", "bgpu_ctx_set_tuning", "bgpu_ctx_set_stream", "bgpu_max_compressed_size", "bgpu_encode",
     "bgpu_encode_batch", "bgpu_encode_device", "bgpu_stream_create", "bgpu_stream_update", "bgpu_stream_finish",
     "bgpu_stream_destroy", "bgpu_stage_match_candidates", "bgpu_stage_commands", "bgpu_stage_store_trivial",
     "bgpu_stage_huffman", "bgpu_stage_timings", "bgpu_last_launch_count", "bgpu_strerror", "bgpu_last_cuda_error",
@@ -39,6 +39,7 @@ def load():
     L.bgpu_ctx_destroy.argtypes = [vp]
     L.bgpu_ctx_destroy.restype = None
     L.bgpu_ctx_set_tuning.argtypes = [vp, C.POINTER(Tuning)]
+    L.bgpu_ctx_set_stream.argtypes = [vp, vp]
     L.bgpu_max_compressed_size.argtypes = [sz]
     L.bgpu_max_compressed_size.restype = sz
     L.bgpu_encode.argtypes = [vp, vp, sz, i, i, i, vp, sz, szp]

@@ -76,17 +76,19 @@ struct Job {
   std::vector<ShardD> shards; std::vector<MbD> mbs; std::vector<SegD> segs; std::vector<uint32_t> tile_seg;
   std::vector<StreamPlan> streams;
   size_t in_bytes = 0, out_bytes = 0;
+  uint32_t n_stile = 0, max_shard_len = 0;
 };
 
 constexpr size_t IN_PAD = 1024;
+constexpr int PARSE_G = 8;   // lanes per parse segment (kernels.cuh k_parse)
 
 }  // namespace
 
 struct bgpu_ctx {
   int device = 0;
-  cudaStream_t stream = nullptr;
+  cudaStream_t stream = nullptr, own_stream = nullptr;
   bgpu_tuning tune{0, 0, 0, 0};
-  DBuf in, link, best, role, ins, cmds, out, shards, mbs, segs, tile_seg, seg_ncmd, seg_trail, hist, codes, tree_bits, tree_nbits,
+  DBuf in, sa_pos, sa_v, sb_pos, sb_v, sort_hist, role, ins, cmds, out, shards, mbs, segs, tile_seg, seg_ncmd, seg_trail, hist, codes, tree_bits, tree_nbits,
       tile_bits, tile_off, shard_bytes, huff_meta;
   std::vector<uint32_t> h_shard_bytes;
   // timings
@@ -104,7 +106,7 @@ void plan_job(const bgpu_ctx* ctx, const EncParams& P, const size_t* lens, int c
   uint32_t shard_bytes = std::min<uint32_t>(eff(ctx->tune.shard_bytes, 1u << 22), 1u << 22);
   if (P.lgwin < 22) shard_bytes = std::min<uint32_t>(shard_bytes, ((1u << P.lgwin) - 16) & ~3u);
   shard_bytes = std::max<uint32_t>(shard_bytes & ~3u, 64);
-  uint32_t seg_bytes = eff(ctx->tune.segment_bytes, 1u << 16);
+  uint32_t seg_bytes = eff(ctx->tune.segment_bytes, 1u << 14);
   seg_bytes = seg_bytes >= shard_bytes ? shard_bytes : std::max<uint32_t>(seg_bytes & ~(TILE - 1), TILE);
   uint32_t mb_bytes = eff(ctx->tune.metablock_bytes, shard_bytes);
   mb_bytes = mb_bytes >= shard_bytes ? shard_bytes : std::max<uint32_t>((mb_bytes / seg_bytes) * seg_bytes, seg_bytes);
@@ -119,6 +121,9 @@ void plan_job(const bgpu_ctx* ctx, const EncParams& P, const size_t* lens, int c
       sh.flags = (so == 0 ? 1u : 0u) | (so + shard_bytes >= n ? 2u : 0u);
       sh.start_nbits = wb_n; sh.start_value = wb_v;
       sh.first_mb = (uint32_t)job.mbs.size();
+      sh.first_stile = job.n_stile;
+      job.n_stile += sh.len >= 4 ? (sh.len - 3 + SORT_TILE - 1) / SORT_TILE : 0;
+      job.max_shard_len = std::max(job.max_shard_len, sh.len);
       uint32_t shard_idx = (uint32_t)job.shards.size();
       for (uint32_t mo = 0; mo < sh.len; mo += mb_bytes) {
         MbD mb; memset(&mb, 0, sizeof mb);
@@ -228,21 +233,38 @@ int run_frontend(bgpu_ctx* ctx, const Job& job, const EncParams& P, const uint8_
   int rc; size_t N = job.in_bytes + IN_PAD;
   const uint32_t n_tile = (uint32_t)job.tile_seg.size(), n_mb = (uint32_t)job.mbs.size(), n_shard = (uint32_t)job.shards.size(),
                  n_seg = (uint32_t)job.segs.size();
-  if ((rc = ctx->link.reserve(N * 4))) return rc;
-  if ((rc = ctx->best.reserve(N * 4))) return rc;
+  if ((rc = ctx->sa_pos.reserve(N * 4))) return rc;   // pass-0 output, later `best`
+  if ((rc = ctx->sa_v.reserve(N * 4))) return rc;
+  if ((rc = ctx->sb_pos.reserve(N * 4))) return rc;
+  if ((rc = ctx->sb_v.reserve(N * 4))) return rc;
+  if ((rc = ctx->sort_hist.reserve(((size_t)job.n_stile + 1) * SORT_BINS * 4))) return rc;
   if ((rc = reserve_front(ctx, job, P))) return rc;
   if ((rc = ctx->seg_ncmd.reserve((size_t)n_seg * 4))) return rc;
   if ((rc = ctx->seg_trail.reserve((size_t)n_seg * 4))) return rc;
   const ShardD* d_sh = ctx->shards.as<ShardD>(); const MbD* d_mb = ctx->mbs.as<MbD>(); const SegD* d_sg = ctx->segs.as<SegD>();
-  const uint32_t* d_ts = ctx->tile_seg.as<uint32_t>();
-  size_t smem = (size_t)4 << P.k.bucket_bits;
-  CK(cudaFuncSetAttribute(k_link, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  k_link<<<n_shard, 32, smem, st>>>(d_in, d_sh, ctx->link.as<uint32_t>(), P.k.bucket_bits);
-  ctx->launches++; stage_mark(ctx, "k_link");
-  k_probe<<<n_tile, 256, 0, st>>>(d_in, d_sh, d_sg, d_ts, ctx->link.as<uint32_t>(), ctx->best.as<uint32_t>(), P.k.depth);
-  ctx->launches++; stage_mark(ctx, "k_probe");
+  uint32_t* sa_pos = ctx->sa_pos.as<uint32_t>(); uint32_t* sa_v = ctx->sa_v.as<uint32_t>();
+  uint32_t* sb_pos = ctx->sb_pos.as<uint32_t>(); uint32_t* sb_v = ctx->sb_v.as<uint32_t>();
+  uint32_t* sh_hist = ctx->sort_hist.as<uint32_t>();
+  uint32_t* best = sa_pos;
+  if (job.max_shard_len >= 4) {
+    const uint32_t max_npos = job.max_shard_len - 3;
+    const dim3 gs((max_npos + SORT_TILE - 1) / SORT_TILE, n_shard), gp((max_npos + PROBE_TILE - 1) / PROBE_TILE, n_shard);
+    const int bb = P.k.bucket_bits, nb0 = 1 << SORT_LOW_BITS, nb1 = 1 << (bb - SORT_LOW_BITS);
+    k_sort_hist<0><<<gs, 256, 0, st>>>(d_in, nullptr, d_sh, sh_hist, bb);
+    k_sort_scan<<<n_shard, 1024, 0, st>>>(d_sh, sh_hist, nb0);
+    k_sort_scatter<0><<<gs, 256, 0, st>>>(d_in, nullptr, nullptr, d_sh, sh_hist, sa_pos, sa_v, bb);
+    ctx->launches += 3; stage_mark(ctx, "k_sort_pass0");
+    k_sort_hist<1><<<gs, 256, 0, st>>>(d_in, sa_v, d_sh, sh_hist, bb);
+    k_sort_scan<<<n_shard, 1024, 0, st>>>(d_sh, sh_hist, nb1);
+    k_sort_scatter<1><<<gs, 256, 0, st>>>(d_in, sa_pos, sa_v, d_sh, sh_hist, sb_pos, sb_v, bb);
+    ctx->launches += 3; stage_mark(ctx, "k_sort_pass1");
+    k_probe_sorted<<<gp, 256, 0, st>>>(d_in, d_sh, sb_pos, sb_v, best, P.k.depth, bb);
+    ctx->launches++; stage_mark(ctx, "k_probe");
+  } else {
+    CK(cudaMemsetAsync(best, 0, N * 4, st));
+  }
   CK(cudaMemsetAsync(ctx->role.p, 0, N, st));
-  k_parse<<<(n_seg + 3) / 4, 128, 0, st>>>(d_in, d_sh, d_sg, n_seg, ctx->best.as<uint32_t>(), ctx->role.as<uint8_t>(), ctx->ins.as<uint32_t>(),
+  k_parse<PARSE_G><<<(n_seg * PARSE_G + 127) / 128, 128, 0, st>>>(d_in, d_sh, d_sg, n_seg, best, ctx->role.as<uint8_t>(), ctx->ins.as<uint32_t>(),
                                            ctx->cmds.as<Cmd>(), ctx->seg_ncmd.as<uint32_t>(), ctx->seg_trail.as<uint32_t>(), P.k);
   ctx->launches++; stage_mark(ctx, "k_parse");
   k_stitch<<<(n_mb + 63) / 64, 64, 0, st>>>(d_sh, d_mb, d_sg, n_mb, ctx->role.as<uint8_t>(), ctx->ins.as<uint32_t>(), ctx->cmds.as<Cmd>(),
@@ -349,7 +371,8 @@ int bgpu_ctx_create(int device_id, bgpu_ctx** out) {
   if (e != cudaSuccess || n == 0) { g_cuda_err = e != cudaSuccess ? cudaGetErrorString(e) : "no CUDA device"; return BGPU_E_NO_DEVICE; }
   bgpu_ctx* c = new bgpu_ctx();
   if (device_id >= 0) { CK(cudaSetDevice(device_id)); c->device = device_id; } else { CK(cudaGetDevice(&c->device)); }
-  CK(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  CK(cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking));
+  c->stream = c->own_stream;
   c->ev_ok = true;
   for (int i = 0; i <= bgpu_ctx::kMaxStages; i++) if (cudaEventCreate(&c->ev[i]) != cudaSuccess) c->ev_ok = false;
   *out = c;
@@ -359,17 +382,23 @@ int bgpu_ctx_create(int device_id, bgpu_ctx** out) {
 void bgpu_ctx_destroy(bgpu_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
-  DBuf* all[] = {&c->in, &c->link, &c->best, &c->role, &c->ins, &c->cmds, &c->out, &c->shards, &c->mbs, &c->segs, &c->tile_seg, &c->seg_ncmd,
+  DBuf* all[] = {&c->in, &c->sa_pos, &c->sa_v, &c->sb_pos, &c->sb_v, &c->sort_hist, &c->role, &c->ins, &c->cmds, &c->out, &c->shards, &c->mbs, &c->segs, &c->tile_seg, &c->seg_ncmd,
                  &c->seg_trail, &c->hist, &c->codes, &c->tree_bits, &c->tree_nbits, &c->tile_bits, &c->tile_off, &c->shard_bytes, &c->huff_meta};
   for (DBuf* b : all) b->release();
   if (c->ev_ok) for (int i = 0; i <= bgpu_ctx::kMaxStages; i++) cudaEventDestroy(c->ev[i]);
-  if (c->stream) cudaStreamDestroy(c->stream);
+  if (c->own_stream) cudaStreamDestroy(c->own_stream);
   delete c;
 }
 
 int bgpu_ctx_set_tuning(bgpu_ctx* c, const bgpu_tuning* t) {
   if (!c || !t) return BGPU_E_INVALID;
   c->tune = *t;
+  return 0;
+}
+
+int bgpu_ctx_set_stream(bgpu_ctx* c, void* cuda_stream) {
+  if (!c) return BGPU_E_INVALID;
+  c->stream = cuda_stream ? (cudaStream_t)cuda_stream : c->own_stream;
   return 0;
 }
 
@@ -554,7 +583,7 @@ int bgpu_stage_match_candidates(bgpu_ctx* c, const uint8_t* in, size_t n, int qu
   if ((rc = upload_plan(c, job))) return rc;
   if ((rc = run_frontend(c, job, P, c->in.as<uint8_t>()))) return rc;
   std::vector<uint32_t> b(n);
-  CK(cudaMemcpyAsync(b.data(), c->best.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(b.data(), c->sa_pos.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
   timing_end(c);
   for (size_t i = 0; i < n; i++) { len[i] = b[i] >> 24; dist[i] = (b[i] >> 24) ? (b[i] & 0xFFFFFF) : 0; }

@@ -1,7 +1,7 @@
 // sm_100a kernels of the Brotli encoder hot path (q5..q9 greedy path; K-numbers follow SURVEY.md §2).
 //
-//   K2  k_link      hash-chain links          hash-chains.ts:51-60,117-119 + match.ts:162-172
-//   K3  k_probe     per-position chain best   hash-chains.ts:121-152 (+ match.ts:20-77)
+//   K1-K3 match_h5.cuh  key sort (k_sort_*) + window probe (k_probe_sorted)
+//                       hash-chains.ts:51-60,117-152 + match.ts:20-77,162-172
 //   K5  k_parse     greedy parse              backward-references.ts:14-158
 //       k_stitch    joins parse segments into whole-metablock command streams (no TS counterpart)
 //   K7  k_hist      BuildHistograms           metablock.ts:305-325
@@ -10,8 +10,8 @@
 //
 // Data layout in HBM (all indexed by absolute byte position in the staged input buffer):
 //   in    u8 [N+pad]  input, every stream starts 256-byte aligned
-//   link  u32[N]      shard-relative previous position with the same hash key (NONE if first)
-//   best  u32[N]      chain-best match: len << 24 | distance   (len <= 128, distance < 2^22)
+//   sa/sb u32[N] x 4  key-sorted (position, 4 input bytes) entries, ping-pong of the two sort passes
+//   best  u32[N]      chain-best match: len << 24 | distance   (len <= 128, distance < 2^22); aliases sa_pos
 //   role  u8 [N]      1 literal | 2 copy start | 4 command start | 8 insert-only command
 //   ins   u32[N>>sh]  insert length of the command starting at position p, slot p >> sh
 //   cmds  Cmd[N>>sh]  command record, slot = (copy-start position) >> sh    (sh = 2: copies >= 4 bytes)
@@ -37,7 +37,7 @@ struct ShardD {
   uint32_t out_cap;
   uint32_t first_mb, n_mb;
   uint32_t start_nbits, start_value;  // stream header bits (encodeWindowBits) for the first shard
-  uint32_t pad;
+  uint32_t first_stile;  // index of the shard's first sort tile (match_h5.cuh)
 };
 struct MbD { uint32_t shard, rel_pos, len, first_seg, n_seg, first_tile, n_tile, is_last; };
 struct SegD { uint32_t shard, rel_pos, len, mb, first_tile, ring_known, pad0, pad1; };
@@ -68,92 +68,9 @@ __device__ __forceinline__ uint32_t match_len(const uint8_t* in, uint64_t a, uin
   return k < limit ? k : limit;
 }
 
-// ---------------------------------------------------------------------------------------
-// K2.  One warp per shard walks the shard in position order; the per-key "last position" table
-// lives in shared memory (4 << bucket_bits bytes).  32 positions per step: lanes with equal keys
-// are linked to each other through __match_any_sync, the lowest lane of each group reads the
-// table, the highest lane writes it back.
-__global__ void __launch_bounds__(32) k_link(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
-                                             uint32_t* __restrict__ link, int bucket_bits) {
-  extern __shared__ uint32_t s_table[];
-  const ShardD sh = shards[blockIdx.x];
-  const uint32_t lane = threadIdx.x;
-  for (uint32_t i = lane; i < (1u << bucket_bits); i += 32) s_table[i] = NONE;
-  __syncwarp();
-  const uint32_t npos = sh.len >= 4 ? sh.len - 3 : 0;
-  const uint32_t* in32 = reinterpret_cast<const uint32_t*>(in + sh.in_off);
-  uint32_t* lk = link + sh.in_off;
-  // 128 positions per outer iteration: lane L holds word base/4 + L; 33rd word fetched by lane 0.
-  uint32_t w = 0, wx = 0;
-  if (npos) { w = __ldg(in32 + lane); wx = __ldg(in32 + 32); }
-  for (uint32_t base = 0; base < npos; base += 128) {
-    uint32_t nw = 0, nwx = 0;
-    if (base + 128 < npos) { nw = __ldg(in32 + (base >> 2) + 32 + lane); nwx = __ldg(in32 + (base >> 2) + 64); }
-    wx = __shfl_sync(0xffffffffu, wx, 0);
-#pragma unroll
-    for (int j = 0; j < 4; j++) {
-      uint32_t src = 8 * j + (lane >> 2);
-      uint32_t lo = __shfl_sync(0xffffffffu, w, src);
-      uint32_t hi = __shfl_sync(0xffffffffu, w, (src + 1) & 31);
-      if (src == 31) hi = wx;
-      uint32_t p = base + 32 * j + lane;
-      bool active = p < npos;
-      uint32_t v = __funnelshift_r(lo, hi, (lane & 3) * 8);
-      uint32_t key = active ? hash4(v, bucket_bits) : (0x80000000u | lane);
-      uint32_t peers = __match_any_sync(0xffffffffu, key);
-      uint32_t lower = peers & ((1u << lane) - 1);
-      uint32_t prev = NONE;
-      if (lower) prev = base + 32 * j + (31 - __clz((int)lower));
-      else if (active) prev = s_table[key];
-      __syncwarp();
-      if (active && (peers >> lane) == 1u) s_table[key] = p;
-      __syncwarp();
-      if (active) lk[p] = prev;
-    }
-    w = nw; wx = nwx;
-  }
-}
-
-// ---------------------------------------------------------------------------------------
-// K3.  One thread per position: walk <= depth links, keep the first strict maximum of
-// backwardReferenceScore (match.ts:26-30).  256 threads cover one 1024-position tile.
-__global__ void __launch_bounds__(256) k_probe(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
-                                               const SegD* __restrict__ segs, const uint32_t* __restrict__ tile_seg,
-                                               const uint32_t* __restrict__ link, uint32_t* __restrict__ best, int depth) {
-  const uint32_t tile = blockIdx.x;
-  const SegD sg = segs[tile_seg[tile]];
-  const ShardD sh = shards[sg.shard];
-  const uint32_t tile_rel = sg.rel_pos + (tile - sg.first_tile) * TILE;
-  const uint32_t tile_end = min(sg.rel_pos + sg.len, tile_rel + TILE);
-  const uint8_t* sin = in + sh.in_off;
-  const uint32_t* lk = link + sh.in_off;
-  for (uint32_t rel = tile_rel + threadIdx.x; rel < tile_end; rel += 256) {
-    uint32_t out = 0;
-    if (rel + 4 <= sh.len) {
-      const uint32_t maxLen = min(sh.len - rel, 128u);
-      const uint32_t maxBackward = min(rel, MAX_BACKWARD);
-      const uint32_t v = ld32u(sin, rel);
-      uint32_t bestLen = 0, bestDist = 0; int bestScore = 0;
-      uint32_t c = lk[rel];
-      for (int d = 0; d < depth && c != NONE; d++) {
-        uint32_t backward = rel - c;
-        if (backward > maxBackward) break;
-        uint32_t nxt = lk[c];
-        // hash-chains.ts:132-135 quick check on the byte at bestLen (prunes only candidates that
-        // cannot win: they would need len > bestLen), then the full compare.
-        if (ld32u(sin, c) == v && (bestLen < 4 || sin[c + bestLen] == sin[rel + bestLen])) {
-          uint32_t len = 4 + match_len(sin, rel + 4, c + 4, maxLen - 4);
-          int score = 135 * (int)len + 960 - 30 * log2_floor(backward);
-          if (score > bestScore) { bestScore = score; bestLen = len; bestDist = backward; }
-          if (bestLen == maxLen) break;
-        }
-        c = nxt;
-      }
-      out = (bestLen << 24) | bestDist;
-    }
-    best[sh.in_off + rel] = out;
-  }
-}
+}  // namespace bgpu
+#include "match_h5.cuh"   // K1-K3: key sort + window probe
+namespace bgpu {
 
 // ---------------------------------------------------------------------------------------
 // K5.  One warp per parse segment.  32 consecutive positions are evaluated speculatively with the
@@ -172,14 +89,22 @@ __device__ __forceinline__ uint32_t distance_to_code(uint32_t distance, const in
   return distance + 15;
 }
 
+// G lanes (a power of two <= 32) work on one segment; a warp carries 32 / G segments.  The parse of
+// a segment is latency bound (a dependent chain of L2 reads per accepted match), so throughput
+// comes from the number of segments in flight: G = 8 keeps one 32-byte sector of `best` and of the
+// input per group read while quadrupling the segments per warp.
+template <int G>
 __global__ void __launch_bounds__(128) k_parse(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
                                                const SegD* __restrict__ segs, uint32_t n_seg,
                                                const uint32_t* __restrict__ best, uint8_t* __restrict__ role,
                                                uint32_t* __restrict__ ins_at, Cmd* __restrict__ cmds,
                                                uint32_t* __restrict__ seg_ncmd, uint32_t* __restrict__ seg_trail, Params P) {
-  const uint32_t seg = blockIdx.x * 4 + (threadIdx.x >> 5);
+  const uint32_t seg = (blockIdx.x * 128 + threadIdx.x) / G;
   if (seg >= n_seg) return;
-  const uint32_t lane = threadIdx.x & 31;
+  const uint32_t wl = threadIdx.x & 31;
+  const uint32_t lane = wl & (G - 1);
+  const uint32_t gshift = wl & ~(uint32_t)(G - 1);
+  const uint32_t gmask = (G == 32 ? 0xffffffffu : ((1u << G) - 1u)) << gshift;
   const SegD sg = segs[seg];
   const ShardD sh = shards[sg.shard];
   const uint8_t* sin = in + sh.in_off;
@@ -197,6 +122,7 @@ __global__ void __launch_bounds__(128) k_parse(const uint8_t* __restrict__ in, c
       const uint32_t maxLen = min(seg_end - q, 128u);
       const uint32_t maxBackward = min(q, MAX_BACKWARD);
       const uint32_t v = ld32u(sin, q);
+      const uint32_t b = sbest[q];
       // hash-chains.ts:86-115: distance-cache candidates, all scored with the last-distance bonus
 #pragma unroll
       for (int i = 0; i < 16; i++) {
@@ -211,19 +137,18 @@ __global__ void __launch_bounds__(128) k_parse(const uint8_t* __restrict__ in, c
         if (score > bscore) { bscore = score; blen = len; bdist = (uint32_t)d; }
       }
       // chain best from K3 (truncated at the segment end)
-      uint32_t b = sbest[q];
       uint32_t clen = min(b >> 24, maxLen), cdist = b & 0xFFFFFFu;
       if (clen >= 4) {
         int score = 135 * (int)clen + 960 - 30 * log2_floor(cdist);
         if (score > bscore) { bscore = score; blen = clen; bdist = cdist; }
       }
     }
-    const uint32_t ballot = __ballot_sync(0xffffffffu, blen >= 4);
-    const uint32_t f = ballot ? (uint32_t)__ffs((int)ballot) - 1 : 32u;
+    const uint32_t ballot = (__ballot_sync(gmask, blen >= 4) & gmask) >> gshift;
+    const uint32_t f = ballot ? (uint32_t)__ffs((int)ballot) - 1 : (uint32_t)G;
     if (lane < f && q < seg_end) srole[q] = 1 | (q == ins_start ? 4 : 0);
-    if (f == 32u) { pos += 32; continue; }
-    const uint32_t mlen = __shfl_sync(0xffffffffu, blen, f);
-    const uint32_t mdist = __shfl_sync(0xffffffffu, bdist, f);
+    if (f == (uint32_t)G) { pos += G; continue; }
+    const uint32_t mlen = __shfl_sync(gmask, blen, gshift + f);
+    const uint32_t mdist = __shfl_sync(gmask, bdist, gshift + f);
     const uint32_t qf = pos + f;
     const uint32_t code = distance_to_code(mdist, ring);
     if (lane == 0) {

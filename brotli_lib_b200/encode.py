@@ -38,6 +38,10 @@ class Context:
         t = _lib.Tuning(shard_bytes, segment_bytes, metablock_bytes, flags)
         _lib.check(self._L.bgpu_ctx_set_tuning(self._h, C.byref(t)))
 
+    def set_stream(self, cuda_stream):
+        """Run on the caller's CUDA stream (an int handle, e.g. torch.cuda.current_stream().cuda_stream)."""
+        _lib.check(self._L.bgpu_ctx_set_stream(self._h, C.c_void_p(cuda_stream or None)))
+
     def close(self):
         if getattr(self, "_h", None):
             self._L.bgpu_ctx_destroy(self._h)

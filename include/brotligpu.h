@@ -38,7 +38,7 @@ typedef struct bgpu_stream bgpu_stream;
  * parse unit per shard, bit-identical commands to src/encode/backward-references.ts:14-134). */
 typedef struct bgpu_tuning {
   uint32_t shard_bytes;     /* independent window, <= 4 MiB (default 4 MiB)      */
-  uint32_t segment_bytes;   /* greedy-parse unit inside a shard (default 64 KiB)                  */
+  uint32_t segment_bytes;   /* greedy-parse unit inside a shard (default 16 KiB)                  */
   uint32_t metablock_bytes; /* metablock size inside a shard (default = shard)                    */
   uint32_t flags;           /* BGPU_F_*                                                           */
 } bgpu_tuning;
@@ -49,6 +49,9 @@ typedef struct bgpu_tuning {
 int bgpu_ctx_create(int device_id, bgpu_ctx** out);
 void bgpu_ctx_destroy(bgpu_ctx* ctx);
 int bgpu_ctx_set_tuning(bgpu_ctx* ctx, const bgpu_tuning* t);
+/* Runs all further work of the context on the caller's CUDA stream (a cudaStream_t passed as void*;
+ * NULL restores the context's own stream).  Lets a harness bracket calls with its own CUDA events. */
+int bgpu_ctx_set_stream(bgpu_ctx* ctx, void* cuda_stream);
 
 /* Upper bound of the stream size for n input bytes (any quality/mode). */
 size_t bgpu_max_compressed_size(size_t n);
