@@ -184,6 +184,8 @@ def run_gpu(args, rank, world, local_rank):
     d_in = torch.zeros(n + 4096, dtype=torch.uint8, device=dev)
     d_in[:n].copy_(h_in, non_blocking=False)
     ctx = B.Context(local_rank)
+    if args.segment_kb:
+        ctx.set_tuning(segment_bytes=args.segment_kb << 10)
     L = ctx._L
     cap = n + (n >> 3) + (1 << 20)
     h_out = torch.empty(cap, dtype=torch.uint8, pin_memory=True)
@@ -301,6 +303,7 @@ def main():
     ap.add_argument("--size-mb", type=int, default=1024)
     ap.add_argument("--quality", type=int, default=5)
     ap.add_argument("--lgwin", type=int, default=22)
+    ap.add_argument("--segment-kb", type=int, default=0, help="parse segment size override (0 = library default)")
     ap.add_argument("--no-verify", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()

@@ -258,7 +258,8 @@ int run_frontend(bgpu_ctx* ctx, const Job& job, const EncParams& P, const uint8_
     k_sort_scan<<<n_shard, 1024, 0, st>>>(d_sh, sh_hist, nb1);
     k_sort_scatter<1><<<gs, 256, 0, st>>>(d_in, sa_pos, sa_v, d_sh, sh_hist, sb_pos, sb_v, bb);
     ctx->launches += 3; stage_mark(ctx, "k_sort_pass1");
-    k_probe_sorted<<<gp, 256, 0, st>>>(d_in, d_sh, sb_pos, sb_v, best, P.k.depth, bb);
+    CK(cudaFuncSetAttribute(k_probe_sorted, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PROBE_SMEM));
+    k_probe_sorted<<<gp, 256, PROBE_SMEM, st>>>(d_in, d_sh, sb_pos, sb_v, best, P.k.depth, bb);
     ctx->launches++; stage_mark(ctx, "k_probe");
   } else {
     CK(cudaMemsetAsync(best, 0, N * 4, st));

@@ -180,11 +180,59 @@ __global__ void __launch_bounds__(256) k_sort_scatter(const uint8_t* __restrict_
   }
 }
 
-// Window probe over the key-sorted entries of a shard.  grid (ceil(4Mi / PROBE_TILE), shards).
+// Window probe over the key-sorted entries of a shard.  grid (ceil(max npos / PROBE_TILE), shards).
+// Every entry of the tile (and of the halo of `depth` entries before it) first fetches the 16 input
+// bytes that follow its 4 key bytes into shared memory — the only random input reads of the common
+// case.  Candidates are then confirmed (4 equal bytes) and extended to 20 bytes entirely in shared
+// memory; only matches of >= 20 bytes go back to the (L2-resident) input.
+__device__ __forceinline__ uint4 ld128u(const uint8_t* base, uint64_t off) {
+  const uint32_t* w = reinterpret_cast<const uint32_t*>(base) + (off >> 2);
+  const uint32_t sh = (uint32_t)(off & 3) * 8;
+  const uint32_t a = __ldg(w), b = __ldg(w + 1), c = __ldg(w + 2), d = __ldg(w + 3), e = __ldg(w + 4);
+  return make_uint4(__funnelshift_r(a, b, sh), __funnelshift_r(b, c, sh), __funnelshift_r(c, d, sh), __funnelshift_r(d, e, sh));
+}
+// number of equal leading bytes of two 16-byte blocks (16 if identical)
+__device__ __forceinline__ uint32_t prefix16(const uint4& x, const uint4& y) {
+  uint32_t d;
+  if ((d = x.x ^ y.x)) return (uint32_t)(__ffs((int)d) - 1) >> 3;
+  if ((d = x.y ^ y.y)) return 4 + ((uint32_t)(__ffs((int)d) - 1) >> 3);
+  if ((d = x.z ^ y.z)) return 8 + ((uint32_t)(__ffs((int)d) - 1) >> 3);
+  if ((d = x.w ^ y.w)) return 12 + ((uint32_t)(__ffs((int)d) - 1) >> 3);
+  return 16;
+}
+
+// Shared-memory plan of k_probe_sorted (dynamic, PROBE_SMEM bytes).
+//   s_x        (TILE + HALO) uint4 the 16 input bytes after the key bytes
+//   s_p, s_v   (TILE + HALO) u32   sorted positions / their 4 key bytes
+constexpr uint32_t PROBE_N = PROBE_TILE + PROBE_HALO;
+constexpr uint32_t PROBE_SMEM = PROBE_N * 16 + PROBE_N * 8;
+
+// common prefix of in[a..] and in[b..] in 16-byte steps, limit-capped
+__device__ __forceinline__ uint32_t match_len16(const uint8_t* in, uint64_t a, uint64_t b, uint32_t limit) {
+  uint32_t k = 0;
+  while (k < limit) {
+    const uint32_t n = prefix16(ld128u(in, a + k), ld128u(in, b + k));
+    k += n;
+    if (n < 16) break;
+  }
+  return k < limit ? k : limit;
+}
+
+// The chain walk of hash-chains.ts:121-152 keeps the FIRST strict maximum of the score over the
+// chain, newest candidate first.  One thread owns 4 consecutive sorted entries.  For each 16 chain
+// steps it first builds the mask of confirmed candidates (same 4 bytes => same key run) from a
+// register window over s_v, then visits only the set bits, so a warp iterates max-popcount times
+// instead of 16 (profiles/r1c: 80 % of the 16 steps had a confirmed candidate in some lane and the
+// whole warp paid for it).  Candidates that reach 20 bytes are deferred: their extension needs
+// input reads, is rare outside repetitive data, and runs afterwards with the reference's pruning
+// (a candidate that cannot beat the current best even at full length is skipped).
 __global__ void __launch_bounds__(256) k_probe_sorted(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
                                                       const uint32_t* __restrict__ srt_pos, const uint32_t* __restrict__ srt_v,
                                                       uint32_t* __restrict__ best, int depth, int bucket_bits) {
-  __shared__ uint32_t s_p[PROBE_TILE + PROBE_HALO], s_v[PROBE_TILE + PROBE_HALO];
+  extern __shared__ __align__(16) uint8_t smem[];
+  uint4* s_x = reinterpret_cast<uint4*>(smem);
+  uint32_t* s_p = reinterpret_cast<uint32_t*>(s_x + PROBE_N);
+  uint32_t* s_v = s_p + PROBE_N;
   const ShardD sh = shards[blockIdx.y];
   const uint32_t npos = shard_npos(sh);
   const uint32_t g0 = blockIdx.x * PROBE_TILE;
@@ -194,42 +242,96 @@ __global__ void __launch_bounds__(256) k_probe_sorted(const uint8_t* __restrict_
   if (blockIdx.x == 0 && tid < sh.len - npos) sbest[npos + tid] = 0;
   if (g0 >= npos) return;
   const uint32_t* sp = srt_pos + sh.in_off; const uint32_t* sv = srt_v + sh.in_off;
-  const uint32_t halo = (uint32_t)depth;  // <= PROBE_HALO
+  const uint8_t* sin = in + sh.in_off;
+  const uint32_t halo = (uint32_t)depth;  // multiple of 16, <= PROBE_HALO
   for (uint32_t i = tid; i < PROBE_TILE + halo; i += 256) {
     const int64_t g = (int64_t)g0 - halo + i;
     const bool ok = g >= 0 && g < (int64_t)npos;
-    s_p[i] = ok ? __ldg(sp + g) : 0;
+    const uint32_t p = ok ? __ldg(sp + g) : 0;
+    s_p[i] = p;
     s_v[i] = ok ? __ldg(sv + g) : 0;
+    s_x[i] = ok ? ld128u(sin, (uint64_t)p + 4) : make_uint4(0, 0, 0, 0);   // reads <= 24 bytes past p: inside the padded input
   }
   __syncthreads();
-  const uint8_t* sin = in + sh.in_off;
-#pragma unroll 1
-  for (uint32_t k = 0; k < PROBE_TILE / 256; k++) {
-    const uint32_t i = k * 256 + tid;
-    const uint32_t g = g0 + i;
-    if (g >= npos) break;
-    const uint32_t v = s_v[halo + i], p = s_p[halo + i];
-    const uint32_t key = hash4(v, bucket_bits);
-    const uint32_t maxLen = min(sh.len - p, 128u);
-    uint32_t bestLen = 0, bestDist = 0; int bestScore = 0;
-    const uint32_t jmax = min((uint32_t)depth, g);
-    for (uint32_t j = 1; j <= jmax; j++) {
-      const uint32_t u = s_v[halo + i - j];
-      if (u != v) {
-        if (hash4(u, bucket_bits) != key) break;   // left the key run: end of the chain
-        continue;                                  // hash collision: uses up one chain step
+  // lanes take entries 4 apart so that a warp's shared-memory reads stay spread over the banks
+  const uint32_t e0 = tid * 4;
+  uint32_t bLen[4], bDist[4]; int bScore[4]; uint32_t longm[4];
+#pragma unroll
+  for (int k = 0; k < 4; k++) { bLen[k] = 0; bDist[k] = 0; bScore[k] = 0; }
+  for (uint32_t jc = 0; jc < (uint32_t)depth; jc += 16) {
+    // ---- candidate masks.  Steps jc+1 .. jc+16 of entry e look at entries e-jc-1 .. e-jc-16.
+    uint32_t mask[4];
+    {
+      uint32_t win[20];   // s_v[halo + e0 - jc - 16 .. halo + e0 - jc + 3]
+      const uint32_t* src = s_v + halo + e0 - jc - 16;
+#pragma unroll
+      for (int q = 0; q < 5; q++) {
+        const uint4 t4 = *reinterpret_cast<const uint4*>(src + 4 * q);
+        win[4 * q] = t4.x; win[4 * q + 1] = t4.y; win[4 * q + 2] = t4.z; win[4 * q + 3] = t4.w;
       }
-      const uint32_t c = s_p[halo + i - j];
-      const uint32_t backward = p - c;
-      if (backward > MAX_BACKWARD) break;          // hash-chains.ts:124
-      // hash-chains.ts:132-135 quick check on the byte at bestLen (prunes only losers)
-      if (bestLen >= 4 && sin[c + bestLen] != sin[p + bestLen]) continue;
-      const uint32_t len = 4 + match_len(sin, p + 4, c + 4, maxLen - 4);
-      const int score = 135 * (int)len + 960 - 30 * log2_floor(backward);
-      if (score > bestScore) { bestScore = score; bestLen = len; bestDist = backward; }
-      if (bestLen == maxLen) break;
+#pragma unroll
+      for (int k = 0; k < 4; k++) {
+        const uint32_t v = s_v[halo + e0 + k];
+        uint32_t m = 0;
+#pragma unroll
+        for (int j = 1; j <= 16; j++) m |= (win[16 + k - j] == v ? 1u : 0u) << (j - 1);
+        // steps beyond the start of the shard / past the last entry do not exist
+        const uint32_t g = g0 + e0 + k;
+        if (g >= npos) m = 0;
+        else if (g < jc + 16) m &= g > jc ? ((1u << (g - jc)) - 1u) : 0u;
+        mask[k] = m;
+      }
     }
-    sbest[p] = (bestLen << 24) | bestDist;
+    // ---- confirmed candidates, newest first; up to 20 bytes from shared memory
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const uint32_t e = e0 + k;
+      const uint32_t p = s_p[halo + e];
+      const uint32_t maxLen = min(sh.len - p, 128u);
+      const uint4 x = s_x[halo + e];
+      uint32_t m = mask[k], lm = 0;
+      while (m) {
+        const uint32_t jj = __ffs((int)m) - 1; m &= m - 1;
+        const uint32_t ci = halo + e - jc - jj - 1;
+        const uint32_t backward = p - s_p[ci];
+        if (backward > MAX_BACKWARD) break;          // hash-chains.ts:124 (only within 16 bytes of a 4 MiB shard's end)
+        uint32_t len = 4 + prefix16(x, s_x[ci]);
+        if (len == 20 && maxLen > 20) { lm |= 1u << jj; continue; }
+        len = min(len, maxLen);
+        const int score = 135 * (int)len + 960 - 30 * log2_floor(backward);
+        // ties keep the earlier (nearer) candidate; a deferred long candidate is always nearer than
+        // the ones after it and longer than 20 bytes, so ordering against it is settled below
+        if (score > bScore[k]) { bScore[k] = score; bLen[k] = len; bDist[k] = backward; }
+      }
+      longm[k] = lm;
+    }
+    // ---- deferred candidates of >= 20 bytes (input reads), newest first
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      uint32_t lm = longm[k];
+      if (!lm) continue;
+      const uint32_t e = e0 + k;
+      const uint32_t p = s_p[halo + e];
+      const uint32_t maxLen = min(sh.len - p, 128u);
+      while (lm) {
+        const uint32_t jj = __ffs((int)lm) - 1; lm &= lm - 1;
+        const uint32_t c = s_p[halo + e - jc - jj - 1];
+        const uint32_t backward = p - c;
+        const int dcost = 960 - 30 * log2_floor(backward);
+        // Skip when even the full length cannot win.  Against an equal score the nearer candidate
+        // wins, so ">=" when the current best is nearer, ">" when it is farther.
+        const int ub = 135 * (int)maxLen + dcost;
+        if (ub < bScore[k] || (ub == bScore[k] && bDist[k] <= backward)) continue;
+        const uint32_t len = 20 + match_len16(sin, p + 20, c + 20, maxLen - 20);
+        const int score = 135 * (int)len + dcost;
+        if (score > bScore[k] || (score == bScore[k] && backward < bDist[k])) { bScore[k] = score; bLen[k] = len; bDist[k] = backward; }
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    const uint32_t e = e0 + k;
+    if (g0 + e < npos) sbest[s_p[halo + e]] = (bLen[k] << 24) | bDist[k];
   }
 }
 
