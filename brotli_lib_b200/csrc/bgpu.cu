@@ -2,7 +2,7 @@
 // The host side mirrors src/encode/encode.ts:50-287 of the reference: option clamping, the
 // empty/uncompressed special cases (host only), shard splitting and stitching.
 #include "../../include/brotligpu.h"
-#include "kernels.cuh"
+#include "metablock_write.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -89,10 +89,11 @@ struct bgpu_ctx {
   cudaStream_t stream = nullptr, own_stream = nullptr;
   bgpu_tuning tune{0, 0, 0, 0};
   DBuf in, sa_pos, sa_v, sb_pos, sb_v, sort_hist, role, ins, cmds, out, shards, mbs, segs, tile_seg, seg_ncmd, seg_trail, hist, codes, tree_bits, tree_nbits,
-      tile_bits, tile_off, shard_bytes, huff_meta;
+      tile_bits, tile_off, shard_bytes, huff_meta, model_arena, misc_arena, d_models, d_splits, d_cb, d_cx, d_bh_ptrs, d_bh_strides, d_cx_outs;
+  bool lut_ready = false;
   std::vector<uint32_t> h_shard_bytes;
   // timings
-  static const int kMaxStages = 16;
+  static const int kMaxStages = 24;
   cudaEvent_t ev[kMaxStages + 1]; const char* names[kMaxStages]; float ms[kMaxStages]; int n_stage = 0; int launches = 0;
   bool ev_ok = false;
 };
@@ -217,6 +218,14 @@ int upload_plan(bgpu_ctx* ctx, const Job& job) {
   if ((rc = upload(ctx, ctx->segs, job.segs.data(), job.segs.size() * sizeof(SegD)))) return rc;
   if ((rc = upload(ctx, ctx->tile_seg, job.tile_seg.data(), job.tile_seg.size() * 4))) return rc;
   return 0;
+}
+
+#include "model_host.inc"
+
+// storeMetaBlock (full modelling) unless the caller asked for storeMetaBlockTrivial everywhere.
+int run_backend_any(bgpu_ctx* ctx, const Job& job, const EncParams& P, const uint8_t* d_in) {
+  if (ctx->tune.flags & BGPU_F_TRIVIAL_METABLOCKS) return run_backend(ctx, job, P, d_in);
+  return run_backend_full(ctx, job, P, d_in);
 }
 
 int reserve_front(bgpu_ctx* ctx, const Job& job, const EncParams& P) {
@@ -384,7 +393,8 @@ void bgpu_ctx_destroy(bgpu_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   DBuf* all[] = {&c->in, &c->sa_pos, &c->sa_v, &c->sb_pos, &c->sb_v, &c->sort_hist, &c->role, &c->ins, &c->cmds, &c->out, &c->shards, &c->mbs, &c->segs, &c->tile_seg, &c->seg_ncmd,
-                 &c->seg_trail, &c->hist, &c->codes, &c->tree_bits, &c->tree_nbits, &c->tile_bits, &c->tile_off, &c->shard_bytes, &c->huff_meta};
+                 &c->seg_trail, &c->hist, &c->codes, &c->tree_bits, &c->tree_nbits, &c->tile_bits, &c->tile_off, &c->shard_bytes, &c->huff_meta,
+                 &c->model_arena, &c->misc_arena, &c->d_models, &c->d_splits, &c->d_cb, &c->d_cx, &c->d_bh_ptrs, &c->d_bh_strides, &c->d_cx_outs};
   for (DBuf* b : all) b->release();
   if (c->ev_ok) for (int i = 0; i <= bgpu_ctx::kMaxStages; i++) cudaEventDestroy(c->ev[i]);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -436,7 +446,7 @@ int bgpu_encode_batch(bgpu_ctx* c, int count, const uint8_t* const* in, const si
   stage_mark(c, "h2d");
   if ((rc = upload_plan(c, job))) return rc;
   if ((rc = run_frontend(c, job, P, c->in.as<uint8_t>()))) return rc;
-  if ((rc = run_backend(c, job, P, c->in.as<uint8_t>()))) return rc;
+  if ((rc = run_backend_any(c, job, P, c->in.as<uint8_t>()))) return rc;
   rc = collect(c, job, out, out_cap, out_len, map.data(), (int)map.size());
   timing_end(c);
   return rc ? rc : result;
@@ -461,7 +471,7 @@ int bgpu_encode_device(bgpu_ctx* c, const void* d_in, size_t n, int quality, int
   timing_begin(c);
   if ((rc = upload_plan(c, job))) return rc;
   if ((rc = run_frontend(c, job, P, (const uint8_t*)d_in))) return rc;
-  if ((rc = run_backend(c, job, P, (const uint8_t*)d_in))) return rc;
+  if ((rc = run_backend_any(c, job, P, (const uint8_t*)d_in))) return rc;
   if (out) {
     uint8_t* outs[1] = {out}; size_t caps[1] = {out_cap};
     rc = collect(c, job, outs, caps, out_len, nullptr, 1);

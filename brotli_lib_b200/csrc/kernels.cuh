@@ -255,15 +255,9 @@ __global__ void __launch_bounds__(256) k_hist(const uint8_t* __restrict__ in, co
 // serialised tree bits.  The sort is a parallel rank-by-counting over the total order
 // (count asc, symbol desc); the two-queue merge and the serialisation are run by thread 0.
 // code table entry: bits << 8 | depth.
-__global__ void __launch_bounds__(128) k_huff(const uint32_t* __restrict__ hists, int hist_stride, int n_codes,
-                                              const int* __restrict__ alphabets, const int* __restrict__ hist_offsets,
-                                              uint32_t* __restrict__ codes, uint32_t* __restrict__ tree_bits,
-                                              uint32_t* __restrict__ tree_nbits) {
-  // code c of problem (blockIdx.x / n_codes) ; alphabets[c], hist_offsets[c] give its slice.
-  const int prob = blockIdx.x / n_codes, which = blockIdx.x % n_codes;
-  const int alphabet = alphabets[which];
-  const uint32_t* hist = hists + (size_t)prob * hist_stride + hist_offsets[which];
-  uint32_t* code_out = codes + (size_t)prob * hist_stride + hist_offsets[which];
+// CTA-cooperative (128 threads) body shared by k_huff and k_huff_mb (metablock_model.cuh).
+__device__ __forceinline__ void huff_cta(const uint32_t* __restrict__ hist, const int alphabet, uint32_t* __restrict__ code_out,
+                                         uint32_t* __restrict__ tree_bits_out, uint32_t* __restrict__ tree_nbits_out) {
   __shared__ uint32_t s_hist[ALPHA_CMD];
   __shared__ uint16_t s_sorted[ALPHA_CMD];
   __shared__ uint32_t s_cnt[2 * ALPHA_CMD + 2];
@@ -322,11 +316,21 @@ __global__ void __launch_bounds__(128) k_huff(const uint32_t* __restrict__ hists
       huff_codes(s_depth, alphabet, s_bits);
       tree_store(w, s_depth, alphabet, n, s_s4, s_rle_sym, s_rle_extra);
     }
-    tree_nbits[blockIdx.x] = w.pos;
+    *tree_nbits_out = w.pos;
   }
   __syncthreads();
   for (int i = tid; i < alphabet; i += 128) code_out[i] = ((uint32_t)s_bits[i] << 8) | s_depth[i];
-  for (int i = tid; i < TREE_WORDS; i += 128) tree_bits[(size_t)blockIdx.x * TREE_WORDS + i] = s_tree[i];
+  for (int i = tid; i < TREE_WORDS; i += 128) tree_bits_out[i] = s_tree[i];
+}
+
+__global__ void __launch_bounds__(128) k_huff(const uint32_t* __restrict__ hists, int hist_stride, int n_codes,
+                                              const int* __restrict__ alphabets, const int* __restrict__ hist_offsets,
+                                              uint32_t* __restrict__ codes, uint32_t* __restrict__ tree_bits,
+                                              uint32_t* __restrict__ tree_nbits) {
+  // code c of problem (blockIdx.x / n_codes) ; alphabets[c], hist_offsets[c] give its slice.
+  const int prob = blockIdx.x / n_codes, which = blockIdx.x % n_codes;
+  huff_cta(hists + (size_t)prob * hist_stride + hist_offsets[which], alphabets[which],
+           codes + (size_t)prob * hist_stride + hist_offsets[which], tree_bits + (size_t)blockIdx.x * TREE_WORDS, tree_nbits + blockIdx.x);
 }
 
 // ---------------------------------------------------------------------------------------

@@ -1,0 +1,271 @@
+// Part E of the full metablock: the emit loop of storeMetaBlock (metablock.ts:714-756) as a
+// position-parallel bit writer.  Tokens of one input position, in stream order:
+//   [command block switch] [command symbol + insert/copy extra bits]     if a command starts here
+//   [literal block switch] [literal symbol, code chosen by block type and context]   if a literal
+//   [distance block switch] [distance symbol + extra bits]               if a copy with an explicit distance starts here
+#pragma once
+#include "metablock_header.cuh"
+
+namespace bgpu {
+
+struct Tok4 { uint32_t n[4]; uint64_t v[4]; };
+
+__device__ __forceinline__ void switch_token(const MbModel& M, int cat, uint32_t rank, uint32_t* type, uint32_t* n, uint64_t* v) {
+  const uint32_t b = M.sym_blk[cat][rank];
+  *type = M.blk_type[cat][b];
+  *n = 0; *v = 0;
+  if (b && M.blk_start[cat][b] == rank) { const uint64_t t = M.blk_tok[cat][b]; *n = (uint32_t)(t >> 56); *v = t & 0x00FFFFFFFFFFFFFFull; }
+}
+
+// il / ic / id: rank of this position's literal / command / distance symbol inside the metablock.
+__device__ __forceinline__ Tok4 position_tokens2(const uint8_t* __restrict__ in, uint64_t p, uint32_t r, const uint32_t* __restrict__ ins_at,
+                                                 const Cmd* __restrict__ cmds, const MbModel& M, uint32_t il, uint32_t ic, uint32_t id,
+                                                 int sh, bool trivial, const uint8_t* lut) {
+  Tok4 t;
+#pragma unroll
+  for (int k = 0; k < 4; k++) { t.n[k] = 0; t.v[k] = 0; }
+  if (r & 4) {
+    const uint32_t ins = ins_at[p >> sh];
+    uint32_t prefix, copyField;
+    if (r & 8) { prefix = insert_only_prefix(ins); copyField = 2u << 25; }
+    else { const Cmd c = cmds[(p + ins) >> sh]; prefix = c.cmdPrefix; copyField = c.copyLen; }
+    uint32_t type;
+    switch_token(M, CMD, ic, &type, &t.n[0], &t.v[0]);
+    const uint32_t e = M.codes[CMD][(size_t)type * ALPHA_CMD + prefix];
+    uint64_t xv; const uint32_t xn = cmd_extra(ins, copyField, &xv);
+    t.n[1] = (e & 0xFF) + xn;
+    t.v[1] = (uint64_t)(e >> 8) | (xv << (e & 0xFF));
+  }
+  if (r & 1) {
+    uint32_t type;
+    switch_token(M, LIT, il, &type, &t.n[2], &t.v[2]);
+    uint32_t ctx = 0;
+    if (!trivial) {
+      const bool s1 = M.stream_start && p == M.abs, s2 = M.stream_start && p <= M.abs + 1;
+      ctx = lut[s1 ? 0 : in[p - 1]] | lut[256 + (s2 ? 0 : in[p - 2])];
+    }
+    const uint32_t cl = M.cmap[LIT][type * 64 + ctx];
+    const uint32_t e = M.codes[LIT][cl * 256 + in[p]];
+    t.n[3] = e & 0xFF; t.v[3] = e >> 8;
+  } else if (r & 2) {
+    const Cmd c = cmds[p >> sh];
+    if (c.cmdPrefix >= 128) {
+      uint32_t type;
+      switch_token(M, DIST, id, &type, &t.n[2], &t.v[2]);
+      const uint32_t copyLen = c.copyLen & 0x1FFFFFF;
+      const uint32_t dctx = trivial ? 0 : (copyLen > 4 ? 3 : copyLen - 2);
+      const uint32_t cl = M.cmap[DIST][type * 4 + dctx];
+      const uint32_t e = M.codes[DIST][cl * ALPHA_DIST_MAX + (c.distPrefix & 0x3FF)];
+      t.n[3] = (e & 0xFF) + (c.distPrefix >> 10);
+      t.v[3] = (uint64_t)(e >> 8) | ((uint64_t)c.distExtra << (e & 0xFF));
+    }
+  }
+  return t;
+}
+
+// Shared by k_tilebits2 and k_write2: roles of the thread's 4 positions and their symbol ranks.
+struct TileRanks { uint32_t r[4]; uint32_t il, ic, id; };
+__device__ __forceinline__ TileRanks tile_ranks(const MbModel& M, uint32_t tile, const ShardD& sh, uint32_t tile_rel, uint32_t tile_end,
+                                                const uint8_t* __restrict__ role, const Cmd* __restrict__ cmds, int shft,
+                                                uint32_t (*s_w)[3]) {
+  const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  TileRanks R; uint32_t nl = 0, nc = 0, nd = 0;
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    const uint32_t rel = tile_rel + 4 * tid + k;
+    R.r[k] = 0;
+    if (rel < tile_end) {
+      const uint64_t p = sh.in_off + rel;
+      R.r[k] = role[p];
+      if ((R.r[k] & 2) && !(R.r[k] & 1) && cmds[p >> shft].cmdPrefix >= 128) { nd++; R.r[k] |= 16; }   // bit 4: codes a distance
+    }
+    nl += R.r[k] & 1; nc += (R.r[k] >> 2) & 1;
+  }
+  const uint32_t packed = nl | (nc << 11) | (nd << 22);
+  uint32_t incl = packed;
+  for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= (uint32_t)o) incl += y; }
+  if (lane == 31) { s_w[w][0] = incl & 2047; s_w[w][1] = (incl >> 11) & 2047; s_w[w][2] = incl >> 22; }
+  __syncthreads();
+  uint32_t bl = 0, bc = 0, bd = 0;
+  for (uint32_t i = 0; i < w; i++) { bl += s_w[i][0]; bc += s_w[i][1]; bd += s_w[i][2]; }
+  const uint32_t ex = incl - packed;
+  const uint32_t* tb = M.tile_base + (tile - M.first_tile) * 3;
+  R.il = tb[0] + bl + (ex & 2047); R.ic = tb[1] + bc + ((ex >> 11) & 2047); R.id = tb[2] + bd + (ex >> 22);
+  return R;
+}
+
+__global__ void __launch_bounds__(256) k_tilebits2(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
+                                                   const SegD* __restrict__ segs, const uint32_t* __restrict__ tile_seg,
+                                                   const MbModel* __restrict__ models, const uint8_t* __restrict__ role,
+                                                   const uint32_t* __restrict__ ins_at, const Cmd* __restrict__ cmds,
+                                                   uint32_t* __restrict__ tile_bits, Params P) {
+  __shared__ uint32_t s_w[8][3];
+  __shared__ uint32_t s_sum[8];
+  const uint32_t tile = blockIdx.x;
+  const SegD sg = segs[tile_seg[tile]];
+  const ShardD sh = shards[sg.shard];
+  const MbModel& M = models[sg.mb];
+  const bool trivial = M.cnt[4] != 0;
+  const uint8_t* lut = c_ctx_lut + (M.cnt[3] << 9);
+  const uint32_t tile_rel = sg.rel_pos + (tile - sg.first_tile) * TILE;
+  const uint32_t tile_end = min(sg.rel_pos + sg.len, tile_rel + TILE);
+  TileRanks R = tile_ranks(M, tile, sh, tile_rel, tile_end, role, cmds, P.sh, s_w);
+  uint32_t bits = 0;
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    const uint32_t r = R.r[k];
+    if (!r) continue;
+    const uint64_t p = sh.in_off + tile_rel + 4 * threadIdx.x + k;
+    const Tok4 t = position_tokens2(in, p, r, ins_at, cmds, M, R.il, R.ic, R.id, P.sh, trivial, lut);
+    bits += t.n[0] + t.n[1] + t.n[2] + t.n[3];
+    R.il += r & 1; R.ic += (r >> 2) & 1; R.id += (r >> 4) & 1;
+  }
+  for (int o = 16; o; o >>= 1) bits += __shfl_xor_sync(0xffffffffu, bits, o);
+  if ((threadIdx.x & 31) == 0) s_sum[threadIdx.x >> 5] = bits;
+  __syncthreads();
+  if (threadIdx.x == 0) { uint32_t s = 0; for (int i = 0; i < 8; i++) s += s_sum[i]; tile_bits[tile] = s; }
+}
+
+// atomicOr-copy of `nbits` bits from src (bit 0 of word 0 first) to bit position `pos` of w.
+__device__ __forceinline__ void copy_bits(uint32_t* w, uint64_t pos, const uint32_t* __restrict__ src, uint32_t nbits, uint32_t tid, uint32_t nthr) {
+  const uint32_t nw = (nbits + 31) >> 5;
+  for (uint32_t k = tid; k < nw; k += nthr) {
+    uint32_t v = src[k];
+    const uint32_t rem = nbits - k * 32;
+    if (rem < 32) v &= (1u << rem) - 1u;
+    if (!v) continue;
+    const uint64_t bp = pos + (uint64_t)k * 32;
+    const uint64_t i = bp >> 5; const uint32_t o = (uint32_t)bp & 31;
+    atomicOr(&w[i], v << o);
+    if (o) atomicOr(&w[i + 1], v >> (32 - o));
+  }
+}
+
+// One CTA per shard: headers + prefix codes of its metablocks, bit offset of every tile, shard length.
+__global__ void __launch_bounds__(256) k_offsets2(const ShardD* __restrict__ shards, const MbD* __restrict__ mbs,
+                                                  const MbModel* __restrict__ models, const uint32_t* __restrict__ tile_bits,
+                                                  uint32_t* __restrict__ tile_off, uint8_t* __restrict__ out,
+                                                  uint32_t* __restrict__ shard_bytes) {
+  __shared__ uint32_t s_part[256];
+  __shared__ uint64_t s_pos;
+  __shared__ uint32_t s_toff[HDR_TREE_SLOTS]; __shared__ uint16_t s_tslot[HDR_TREE_SLOTS]; __shared__ uint32_t s_nt, s_ttot;
+  const ShardD sh = shards[blockIdx.x];
+  uint32_t* w = reinterpret_cast<uint32_t*>(out + sh.out_off);
+  const uint32_t tid = threadIdx.x;
+  if (tid == 0) {
+    uint64_t pos = 0;
+    if (sh.flags & 1) gput(w, pos, sh.start_nbits, sh.start_value);
+    s_pos = pos;
+  }
+  __syncthreads();
+  for (uint32_t m = sh.first_mb; m < sh.first_mb + sh.n_mb; m++) {
+    const MbD mb = mbs[m];
+    const MbModel& M = models[m];
+    const uint32_t misc_bits = M.cnt[5];
+    if (tid == 0) {
+      uint32_t n = 0, off = 0;
+      const uint32_t ncl_l = M.cnt[6], ntc = M.sstate[CMD][2], ncl_d = M.cnt[7];
+      for (uint32_t s = 0; s < ncl_l; s++) { s_tslot[n] = (uint16_t)s; s_toff[n] = off; off += M.tree_nbits[s]; n++; }
+      for (uint32_t s = 0; s < ntc; s++) { s_tslot[n] = (uint16_t)(64 + s); s_toff[n] = off; off += M.tree_nbits[64 + s]; n++; }
+      for (uint32_t s = 0; s < ncl_d; s++) { s_tslot[n] = (uint16_t)(320 + s); s_toff[n] = off; off += M.tree_nbits[320 + s]; n++; }
+      s_nt = n; s_ttot = off;
+    }
+    __syncthreads();
+    const uint64_t base = s_pos;
+    copy_bits(w, base, M.misc, misc_bits, tid, 256);
+    for (uint32_t t = tid >> 5; t < s_nt; t += 8) {
+      const uint32_t slot = s_tslot[t];
+      copy_bits(w, base + misc_bits + s_toff[t], M.tree_bits + (size_t)slot * TREE_WORDS, M.tree_nbits[slot], tid & 31, 32);
+    }
+    __syncthreads();
+    if (tid == 0) s_pos = base + misc_bits + s_ttot;
+    __syncthreads();
+    for (uint32_t t0 = 0; t0 < mb.n_tile; t0 += 256) {
+      const uint32_t v = (t0 + tid < mb.n_tile) ? tile_bits[mb.first_tile + t0 + tid] : 0;
+      s_part[tid] = v;
+      __syncthreads();
+      for (int o = 1; o < 256; o <<= 1) {
+        const uint32_t add = tid >= (uint32_t)o ? s_part[tid - o] : 0;
+        __syncthreads();
+        s_part[tid] += add;
+        __syncthreads();
+      }
+      const uint32_t incl = s_part[tid];
+      if (t0 + tid < mb.n_tile) tile_off[mb.first_tile + t0 + tid] = (uint32_t)s_pos + incl - v;
+      __syncthreads();
+      if (tid == 255) s_pos += incl;
+      __syncthreads();
+    }
+  }
+  if (tid == 0) {
+    uint64_t pos = s_pos;
+    if (!(sh.flags & 2)) gput(w, pos, 6, 6);  // empty metadata block (RFC 7932 §9.2): byte-aligns a non-final shard
+    shard_bytes[blockIdx.x] = (uint32_t)((pos + 7) >> 3);
+  }
+}
+
+__global__ void __launch_bounds__(256) k_write2(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
+                                                const SegD* __restrict__ segs, const uint32_t* __restrict__ tile_seg,
+                                                const MbModel* __restrict__ models, const uint8_t* __restrict__ role,
+                                                const uint32_t* __restrict__ ins_at, const Cmd* __restrict__ cmds,
+                                                const uint32_t* __restrict__ tile_bits, const uint32_t* __restrict__ tile_off,
+                                                uint8_t* __restrict__ out, Params P) {
+  __shared__ uint32_t s_stage[STAGE_WORDS];
+  __shared__ uint32_t s_w[8][3];
+  __shared__ uint32_t s_warp[8];
+  const uint32_t tile = blockIdx.x;
+  const uint32_t total = tile_bits[tile];
+  if (total == 0) return;
+  const SegD sg = segs[tile_seg[tile]];
+  const ShardD sh = shards[sg.shard];
+  const MbModel& M = models[sg.mb];
+  const bool trivial = M.cnt[4] != 0;
+  const uint8_t* lut = c_ctx_lut + (M.cnt[3] << 9);
+  const uint32_t tid = threadIdx.x;
+  const uint32_t off = tile_off[tile];
+  const uint32_t head = off & 31;
+  const uint32_t nwords = (head + total + 31) >> 5;
+  const bool staged = nwords + 2 <= STAGE_WORDS;
+  if (staged) for (uint32_t i = tid; i < nwords + 2; i += 256) s_stage[i] = 0;
+  const uint32_t tile_rel = sg.rel_pos + (tile - sg.first_tile) * TILE;
+  const uint32_t tile_end = min(sg.rel_pos + sg.len, tile_rel + TILE);
+  TileRanks R = tile_ranks(M, tile, sh, tile_rel, tile_end, role, cmds, P.sh, s_w);   // contains a __syncthreads
+  Tok4 tk[4]; uint32_t mine = 0;
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    const uint32_t r = R.r[k];
+#pragma unroll
+    for (int f = 0; f < 4; f++) { tk[k].n[f] = 0; tk[k].v[f] = 0; }
+    if (r) {
+      const uint64_t p = sh.in_off + tile_rel + 4 * tid + k;
+      tk[k] = position_tokens2(in, p, r, ins_at, cmds, M, R.il, R.ic, R.id, P.sh, trivial, lut);
+      R.il += r & 1; R.ic += (r >> 2) & 1; R.id += (r >> 4) & 1;
+    }
+    mine += tk[k].n[0] + tk[k].n[1] + tk[k].n[2] + tk[k].n[3];
+  }
+  uint32_t incl = mine;
+  for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o); if ((tid & 31) >= (uint32_t)o) incl += y; }
+  if ((tid & 31) == 31) s_warp[tid >> 5] = incl;
+  __syncthreads();
+  uint32_t wbase = 0;
+  for (uint32_t i = 0; i < (tid >> 5); i++) wbase += s_warp[i];
+  uint32_t bitpos = head + wbase + incl - mine;
+  uint32_t* gw = reinterpret_cast<uint32_t*>(out + sh.out_off) + (off >> 5);
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+#pragma unroll
+    for (int f = 0; f < 4; f++) {
+      if (staged) sput(s_stage, bitpos, tk[k].n[f], tk[k].v[f]); else sput(gw, bitpos, tk[k].n[f], tk[k].v[f]);
+      bitpos += tk[k].n[f];
+    }
+  }
+  if (!staged) return;
+  __syncthreads();
+  for (uint32_t i = tid; i < nwords; i += 256) {
+    const uint32_t v = s_stage[i];
+    if (i == 0 || i == nwords - 1) { if (v) atomicOr(&gw[i], v); }
+    else gw[i] = v;
+  }
+}
+
+}  // namespace bgpu

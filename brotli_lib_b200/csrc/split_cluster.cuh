@@ -222,12 +222,14 @@ __global__ void __launch_bounds__(32) k_cluster_gather(const ClusterProb* __rest
 // (cluster.ts:361-365), then remap every input to its cheapest cluster (cluster.ts:244-275 with a
 // sparse distance), rebuild the cluster histograms and reindex by first appearance (:278-314).
 // One CTA of 512 threads per problem; dynamic shared memory: 256 x 256 floats (pair matrix) + tables.
-constexpr uint32_t CL_FINAL_SMEM = CL_FINAL_MAX * CL_FINAL_MAX * 4 + CL_FINAL_MAX * (4 + 4 + 4 + 4 + 1) + 256;
+constexpr uint32_t CL_FINAL_PAIRS = CL_FINAL_MAX * (CL_FINAL_MAX - 1) / 2;   // pair (i < j) at j (j - 1) / 2 + i
+constexpr uint32_t CL_FINAL_SMEM = CL_FINAL_PAIRS * 4 + CL_FINAL_MAX * (4 + 4 + 4 + 4 + 1) + 256;
+__device__ __forceinline__ uint32_t tri(uint32_t i, uint32_t j) { return j * (j - 1) / 2 + i; }
 
 __global__ void __launch_bounds__(512) k_cluster_final(const ClusterProb* __restrict__ probs) {
   extern __shared__ __align__(16) uint8_t csm[];
-  float* s_d = reinterpret_cast<float*>(csm);                       // [n][n], pair (i < j) at i * n + j
-  uint32_t* s_idx = reinterpret_cast<uint32_t*>(s_d + CL_FINAL_MAX * CL_FINAL_MAX);
+  float* s_d = reinterpret_cast<float*>(csm);                       // triangular pair matrix
+  uint32_t* s_idx = reinterpret_cast<uint32_t*>(s_d + CL_FINAL_PAIRS);
   float* s_cost = reinterpret_cast<float*>(s_idx + CL_FINAL_MAX);
   uint32_t* s_tot = reinterpret_cast<uint32_t*>(s_cost + CL_FINAL_MAX);
   uint32_t* s_size = s_tot + CL_FINAL_MAX;
@@ -247,7 +249,7 @@ __global__ void __launch_bounds__(512) k_cluster_final(const ClusterProb* __rest
     if (s_tot[i] == 0) combo = s_cost[j];
     else if (s_tot[j] == 0) combo = s_cost[i];
     else combo = hist_cost(p.work + (size_t)s_idx[i] * p.stride, p.work + (size_t)s_idx[j] * p.stride, (int)p.alpha, nullptr);
-    if (lane == 0) s_d[i * n + j] = 0.5f * cluster_cost_diff((float)s_size[i], (float)s_size[j]) - s_cost[i] - s_cost[j] + combo;
+    if (lane == 0) s_d[tri(i, j)] = 0.5f * cluster_cost_diff((float)s_size[i], (float)s_size[j]) - s_cost[i] - s_cost[j] + combo;
     if (combo_out) *combo_out = combo;
   };
   if (n > 1) {
@@ -262,7 +264,7 @@ __global__ void __launch_bounds__(512) k_cluster_final(const ClusterProb* __rest
     float bv = 3.0e38f; int bi = -1;
     for (uint32_t pr = tid; pr < n * n; pr += 512) {
       const uint32_t i = pr / n, j = pr % n;
-      if (i < j && s_live[i] && s_live[j]) { const float d = s_d[pr]; if (d < bv) { bv = d; bi = (int)pr; } }
+      if (i < j && s_live[i] && s_live[j]) { const float d = s_d[tri(i, j)]; if (d < bv) { bv = d; bi = (int)pr; } }
     }
     for (int o = 16; o; o >>= 1) {
       const float ov = __shfl_xor_sync(0xffffffffu, bv, o); const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
@@ -382,6 +384,7 @@ struct SplitProb {
   uint8_t* blk_type;       // [MAX_BLOCKS]
   const uint32_t* n_ptr;   // number of symbols (device side)
   uint32_t alpha, gran, sym_per_hist, wide;   // wide: 1 = u16 symbols
+  uint32_t max_blocks;
   float switch_cost;
 };
 
@@ -535,7 +538,7 @@ __global__ void __launch_bounds__(256) k_split_begin(const SplitProb* __restrict
   if (threadIdx.x == 0) { p.state[0] = n < 128 ? 1 : split_k0(n, p.sym_per_hist); p.state[1] = 0; }
 }
 
-// Runs of equal granule ids -> blocks (at most MAX_BLOCKS; later runs are folded into the last
+// Runs of equal granule ids -> blocks (at most p.max_blocks; later runs are folded into the last
 // block).  One warp per problem.
 __global__ void __launch_bounds__(32) k_split_blocks(const SplitProb* __restrict__ probs) {
   const SplitProb p = probs[blockIdx.x];
@@ -553,27 +556,30 @@ __global__ void __launch_bounds__(32) k_split_blocks(const SplitProb* __restrict
     const bool start = g < G && (g == 0 || p.gid[g] != p.gid[g - 1]);
     const uint32_t m = __ballot_sync(0xffffffffu, start);
     const uint32_t idx = nb + __popc(m & ((1u << lane) - 1));
-    if (start && idx < MAX_BLOCKS) { p.blk_start[idx] = g * p.gran; p.blk_type[idx] = p.gid[g]; }
+    if (start && idx < p.max_blocks) { p.blk_start[idx] = g * p.gran; p.blk_type[idx] = p.gid[g]; }
     nb += __popc(m);
   }
-  nb = min(nb, (uint32_t)MAX_BLOCKS);
+  nb = min(nb, p.max_blocks);
   if (lane == 0) { p.state[1] = nb; p.blk_start[nb] = n; }
 }
 
-// Per-block histograms for clusterBlocks (:326-340).  grid (MAX_BLOCKS, problems).
+// Per-block histograms for clusterBlocks (:326-340).  grid (64, problems); CTA x takes blocks x, x + 64, ...
 __global__ void __launch_bounds__(256) k_block_hist(const SplitProb* __restrict__ probs, uint32_t* const* __restrict__ bh_ptrs,
                                                     const uint32_t* __restrict__ strides) {
   extern __shared__ uint32_t s_hh[];
   const SplitProb p = probs[blockIdx.y];
   const uint32_t nb = p.state[1];
-  if (blockIdx.x >= nb || nb <= 1) return;
-  for (uint32_t i = threadIdx.x; i < p.alpha; i += 256) s_hh[i] = 0;
-  __syncthreads();
-  const uint32_t b = p.blk_start[blockIdx.x], e = p.blk_start[blockIdx.x + 1];
-  for (uint32_t i = b + threadIdx.x; i < e; i += 256) atomicAdd(&s_hh[split_sym(p, i)], 1u);
-  __syncthreads();
-  uint32_t* out = bh_ptrs[blockIdx.y] + (size_t)blockIdx.x * strides[blockIdx.y];
-  for (uint32_t i = threadIdx.x; i < p.alpha; i += 256) out[i] = s_hh[i];
+  if (nb <= 1) return;
+  for (uint32_t blk = blockIdx.x; blk < nb; blk += gridDim.x) {
+    for (uint32_t i = threadIdx.x; i < p.alpha; i += 256) s_hh[i] = 0;
+    __syncthreads();
+    const uint32_t b = p.blk_start[blk], e = p.blk_start[blk + 1];
+    for (uint32_t i = b + threadIdx.x; i < e; i += 256) atomicAdd(&s_hh[split_sym(p, i)], 1u);
+    __syncthreads();
+    uint32_t* out = bh_ptrs[blockIdx.y] + (size_t)blk * strides[blockIdx.y];
+    for (uint32_t i = threadIdx.x; i < p.alpha; i += 256) out[i] = s_hh[i];
+    __syncthreads();
+  }
 }
 
 }  // namespace bgpu

@@ -43,6 +43,7 @@ typedef struct bgpu_tuning {
   uint32_t flags;           /* BGPU_F_*                                                           */
 } bgpu_tuning;
 #define BGPU_F_KEEP_DEVICE_OUTPUT 1u /* bench: skip the device->host gather (device-resident timing) */
+#define BGPU_F_TRIVIAL_METABLOCKS 2u /* storeMetaBlockTrivial for every metablock (metablock.ts:290-389): no block split, no context map */
 
 /* Context: owns the CUDA device, stream, scratch arenas.  Not thread-safe; one per thread.
  * device_id < 0 selects the current device. */

@@ -12,6 +12,7 @@ from conftest import CORPUS, SYNTH, Xorshift32, fuzz_inputs, load_input
 pytestmark = pytest.mark.gpu
 
 EXACT = 0xFFFFFFFF
+TRIVIAL = 2   # BGPU_F_TRIVIAL_METABLOCKS
 
 
 def _rt(stream, data):
@@ -96,7 +97,7 @@ def test_end_to_end_exact_mode_equals_oracle_trivial(gpu_ctx, name):
     data = load_input(name)
     if len(data) < 64:
         pytest.skip("host-only path")
-    gpu_ctx.set_tuning(segment_bytes=EXACT)
+    gpu_ctx.set_tuning(segment_bytes=EXACT, flags=TRIVIAL)
     try:
         for q, mode in ((5, 0), (6, 2), (9, 0)):
             s = gpu_ctx.encode(data, q, 22, mode)
