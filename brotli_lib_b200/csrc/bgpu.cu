@@ -3,6 +3,7 @@
 // empty/uncompressed special cases (host only), shard splitting and stitching.
 #include "../../include/brotligpu.h"
 #include "metablock_write.cuh"
+#include "h10.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -89,11 +90,13 @@ struct bgpu_ctx {
   cudaStream_t stream = nullptr, own_stream = nullptr;
   bgpu_tuning tune{0, 0, 0, 0};
   DBuf in, sa_pos, sa_v, sb_pos, sb_v, sort_hist, role, ins, cmds, out, shards, mbs, segs, tile_seg, seg_ncmd, seg_trail, hist, codes, tree_bits, tree_nbits,
-      tile_bits, tile_off, shard_bytes, huff_meta, model_arena, misc_arena, d_models, d_splits, d_cb, d_cx, d_bh_ptrs, d_bh_strides, d_cx_outs;
+      tile_bits, tile_off, shard_bytes, huff_meta, model_arena, misc_arena, d_models, d_splits, d_cb, d_cx, d_bh_ptrs, d_bh_strides, d_cx_outs,
+      h10_bstart, h10_bend, h10_short, h10_forest, h10_m, h10_off, h10_cnt, h10_cursor, h10_full;
+  uint32_t h10_cap = 0;
   bool lut_ready = false;
   std::vector<uint32_t> h_shard_bytes;
   // timings
-  static const int kMaxStages = 24;
+  static const int kMaxStages = 40;
   cudaEvent_t ev[kMaxStages + 1]; const char* names[kMaxStages]; float ms[kMaxStages]; int n_stage = 0; int launches = 0;
   bool ev_ok = false;
 };
@@ -259,13 +262,13 @@ int run_frontend(bgpu_ctx* ctx, const Job& job, const EncParams& P, const uint8_
     const uint32_t max_npos = job.max_shard_len - 3;
     const dim3 gs((max_npos + SORT_TILE - 1) / SORT_TILE, n_shard), gp((max_npos + PROBE_TILE - 1) / PROBE_TILE, n_shard);
     const int bb = P.k.bucket_bits, nb0 = 1 << SORT_LOW_BITS, nb1 = 1 << (bb - SORT_LOW_BITS);
-    k_sort_hist<0><<<gs, 256, 0, st>>>(d_in, nullptr, d_sh, sh_hist, bb);
+    k_sort_hist<0><<<gs, 256, 0, st>>>(d_in, nullptr, d_sh, sh_hist, bb, 0, SORT_LOW_BITS);
     k_sort_scan<<<n_shard, 1024, 0, st>>>(d_sh, sh_hist, nb0);
-    k_sort_scatter<0><<<gs, 256, 0, st>>>(d_in, nullptr, nullptr, d_sh, sh_hist, sa_pos, sa_v, bb);
+    k_sort_scatter<0><<<gs, 256, 0, st>>>(d_in, nullptr, nullptr, d_sh, sh_hist, sa_pos, sa_v, bb, 0, SORT_LOW_BITS);
     ctx->launches += 3; stage_mark(ctx, "k_sort_pass0");
-    k_sort_hist<1><<<gs, 256, 0, st>>>(d_in, sa_v, d_sh, sh_hist, bb);
+    k_sort_hist<1><<<gs, 256, 0, st>>>(d_in, sa_v, d_sh, sh_hist, bb, SORT_LOW_BITS, bb - SORT_LOW_BITS);
     k_sort_scan<<<n_shard, 1024, 0, st>>>(d_sh, sh_hist, nb1);
-    k_sort_scatter<1><<<gs, 256, 0, st>>>(d_in, sa_pos, sa_v, d_sh, sh_hist, sb_pos, sb_v, bb);
+    k_sort_scatter<1><<<gs, 256, 0, st>>>(d_in, sa_pos, sa_v, d_sh, sh_hist, sb_pos, sb_v, bb, SORT_LOW_BITS, bb - SORT_LOW_BITS);
     ctx->launches += 3; stage_mark(ctx, "k_sort_pass1");
     CK(cudaFuncSetAttribute(k_probe_sorted, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PROBE_SMEM));
     k_probe_sorted<<<gp, 256, PROBE_SMEM, st>>>(d_in, d_sh, sb_pos, sb_v, best, P.k.depth, bb);
@@ -283,6 +286,8 @@ int run_frontend(bgpu_ctx* ctx, const Job& job, const EncParams& P, const uint8_
   CK(cudaGetLastError());
   return 0;
 }
+
+#include "hq_host.inc"
 
 void timing_begin(bgpu_ctx* ctx) {
   ctx->n_stage = 0; ctx->launches = 0;
@@ -394,7 +399,8 @@ void bgpu_ctx_destroy(bgpu_ctx* c) {
   cudaSetDevice(c->device);
   DBuf* all[] = {&c->in, &c->sa_pos, &c->sa_v, &c->sb_pos, &c->sb_v, &c->sort_hist, &c->role, &c->ins, &c->cmds, &c->out, &c->shards, &c->mbs, &c->segs, &c->tile_seg, &c->seg_ncmd,
                  &c->seg_trail, &c->hist, &c->codes, &c->tree_bits, &c->tree_nbits, &c->tile_bits, &c->tile_off, &c->shard_bytes, &c->huff_meta,
-                 &c->model_arena, &c->misc_arena, &c->d_models, &c->d_splits, &c->d_cb, &c->d_cx, &c->d_bh_ptrs, &c->d_bh_strides, &c->d_cx_outs};
+                 &c->model_arena, &c->misc_arena, &c->d_models, &c->d_splits, &c->d_cb, &c->d_cx, &c->d_bh_ptrs, &c->d_bh_strides, &c->d_cx_outs,
+                 &c->h10_bstart, &c->h10_bend, &c->h10_short, &c->h10_forest, &c->h10_m, &c->h10_off, &c->h10_cnt, &c->h10_cursor, &c->h10_full};
   for (DBuf* b : all) b->release();
   if (c->ev_ok) for (int i = 0; i <= bgpu_ctx::kMaxStages; i++) cudaEventDestroy(c->ev[i]);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -733,6 +739,55 @@ int bgpu_stage_huffman(bgpu_ctx* c, const uint32_t* hist, int count, int alphabe
   if (e != cudaSuccess) { g_cuda_err = cudaGetErrorString(e); return done(BGPU_E_CUDA); }
   for (size_t i = 0; i < total; i++) { if (depths) depths[i] = (uint8_t)(cd[i] & 0xFF); if (bits) bits[i] = (uint16_t)(cd[i] >> 8); }
   return done(0);
+}
+
+int bgpu_stage_h10_matches(bgpu_ctx* c, const uint8_t* in, size_t n, int lgwin, uint32_t* offsets, uint32_t* dist, uint32_t* len, size_t cap,
+                           size_t* total) {
+  if (!c || !in || !offsets || !total || n == 0 || n > ((size_t)1 << 22)) return BGPU_E_INVALID;
+  EncParams P = make_params(11, lgwin, 0);
+  CK(cudaSetDevice(c->device));
+  bgpu_tuning saved = c->tune; c->tune.shard_bytes = 1u << 22;
+  Job job; size_t lens[1] = {n}; plan_job(c, P, lens, 1, job);
+  c->tune = saved;
+  if (job.shards.size() != 1) return BGPU_E_INVALID;
+  int rc;
+  if ((rc = c->in.reserve(job.in_bytes + IN_PAD))) return rc;
+  timing_begin(c);
+  CK(cudaMemcpyAsync(c->in.p, in, n, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemsetAsync(c->in.as<uint8_t>() + n, 0, job.in_bytes + IN_PAD - n, c->stream));
+  if ((rc = upload_plan(c, job))) return rc;
+  uint32_t capu = 0;
+  if ((rc = run_h10_retry(c, job, c->in.as<uint8_t>(), &capu))) return rc;
+  const size_t N = job.in_bytes + IN_PAD;
+  if ((rc = c->h10_full.reserve(N * 4 * capu))) return rc;
+  H10Out O{c->h10_m.as<uint32_t>(), c->h10_off.as<uint32_t>(), c->h10_cnt.as<uint8_t>(), c->h10_cursor.as<uint32_t>(), c->h10_cursor.as<uint32_t>() + 1, capu};
+  k_h10_extend<<<dim3((unsigned)((n + 255) / 256), 1), 256, 0, c->stream>>>(c->in.as<uint8_t>(), c->shards.as<ShardD>(), O, c->h10_full.as<uint32_t>());
+  c->launches++; stage_mark(c, "k_h10_extend");
+  uint32_t used = 0;
+  CK(cudaMemcpyAsync(&used, c->h10_cursor.p, 4, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  std::vector<uint32_t> m(used), fl(used), off(n); std::vector<uint8_t> cnt(n);
+  if (used) {
+    CK(cudaMemcpyAsync(m.data(), c->h10_m.p, (size_t)used * 4, cudaMemcpyDeviceToHost, c->stream));
+    CK(cudaMemcpyAsync(fl.data(), c->h10_full.p, (size_t)used * 4, cudaMemcpyDeviceToHost, c->stream));
+  }
+  CK(cudaMemcpyAsync(off.data(), c->h10_off.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(cnt.data(), c->h10_cnt.p, n, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  timing_end(c);
+  size_t k = 0;
+  for (size_t i = 0; i < n; i++) {
+    offsets[i] = (uint32_t)k;
+    for (uint32_t j = 0; j < cnt[i]; j++) {
+      const uint32_t e = m[off[i] + j], L = fl[off[i] + j];
+      if (!L) continue;
+      if (k < cap && dist && len) { dist[k] = e & 0xFFFFFFu; len[k] = L; }
+      k++;
+    }
+  }
+  offsets[n] = (uint32_t)k;
+  *total = k;
+  return k > cap ? BGPU_E_OUTPUT_TOO_SMALL : 0;
 }
 
 int bgpu_stage_timings(bgpu_ctx* c, const char** names, float* ms, int cap) {

@@ -33,9 +33,9 @@ constexpr int SORT_LOW_BITS = 7;
 constexpr uint32_t PROBE_TILE = 1024;     // sorted entries per probe CTA (256 threads x 4)
 constexpr uint32_t PROBE_HALO = 256;      // >= max depth (quality 9)
 
-__device__ __forceinline__ uint32_t sort_digit(uint32_t v, int bucket_bits, int pass) {
-  const uint32_t key = hash4(v, bucket_bits);
-  return pass == 0 ? (key & ((1u << SORT_LOW_BITS) - 1)) : (key >> SORT_LOW_BITS);
+// digit of one LSD pass: bits [shift, shift + nbits) of the bucket key
+__device__ __forceinline__ uint32_t sort_digit(uint32_t v, int bucket_bits, int shift, int nbits) {
+  return (hash4(v, bucket_bits) >> shift) & ((1u << nbits) - 1);
 }
 __device__ __forceinline__ uint32_t shard_npos(const ShardD& sh) { return sh.len >= 4 ? sh.len - 3 : 0; }
 __device__ __forceinline__ uint32_t shard_nstile(const ShardD& sh) { return (shard_npos(sh) + SORT_TILE - 1) / SORT_TILE; }
@@ -44,7 +44,7 @@ __device__ __forceinline__ uint32_t shard_nstile(const ShardD& sh) { return (sha
 // at hist + first_stile * SORT_BINS.
 template <int PASS>
 __global__ void __launch_bounds__(256) k_sort_hist(const uint8_t* __restrict__ in, const uint32_t* __restrict__ src_v,
-                                                   const ShardD* __restrict__ shards, uint32_t* __restrict__ hist, int bucket_bits) {
+                                                   const ShardD* __restrict__ shards, uint32_t* __restrict__ hist, int bucket_bits, int shift, int nbits) {
   __shared__ uint32_t s_h[SORT_BINS];
   const ShardD sh = shards[blockIdx.y];
   const uint32_t npos = shard_npos(sh), n_stile = shard_nstile(sh), tile = blockIdx.x;
@@ -59,11 +59,11 @@ __global__ void __launch_bounds__(256) k_sort_hist(const uint8_t* __restrict__ i
     const uint32_t e = base + k * 256 + threadIdx.x;
     if (e < npos) {
       const uint32_t v = PASS == 0 ? ld32u(sin, e) : __ldg(sv + e);
-      atomicAdd(&s_h[sort_digit(v, bucket_bits, PASS)], 1u);
+      atomicAdd(&s_h[sort_digit(v, bucket_bits, shift, nbits)], 1u);
     }
   }
   __syncthreads();
-  const uint32_t nb = PASS == 0 ? (1u << SORT_LOW_BITS) : (1u << (bucket_bits - SORT_LOW_BITS));
+  const uint32_t nb = 1u << nbits;
   if (threadIdx.x < nb) hist[(size_t)sh.first_stile * SORT_BINS + (size_t)threadIdx.x * n_stile + tile] = s_h[threadIdx.x];
 }
 
@@ -109,7 +109,7 @@ template <int PASS>
 __global__ void __launch_bounds__(256) k_sort_scatter(const uint8_t* __restrict__ in, const uint32_t* __restrict__ src_pos,
                                                       const uint32_t* __restrict__ src_v, const ShardD* __restrict__ shards,
                                                       const uint32_t* __restrict__ hist, uint32_t* __restrict__ dst_pos,
-                                                      uint32_t* __restrict__ dst_v, int bucket_bits) {
+                                                      uint32_t* __restrict__ dst_v, int bucket_bits, int shift, int nbits) {
   constexpr int ROUNDS = SORT_TILE / 256;  // 16
   __shared__ uint32_t s_cnt[8][SORT_BINS];
   __shared__ uint32_t s_base[SORT_BINS];   // tile-local exclusive offset of each digit
@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(256) k_sort_scatter(const uint8_t* __restrict_
   const uint32_t npos = shard_npos(sh), n_stile = shard_nstile(sh), tile = blockIdx.x;
   if (tile >= n_stile) return;
   const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-  const uint32_t nb = PASS == 0 ? (1u << SORT_LOW_BITS) : (1u << (bucket_bits - SORT_LOW_BITS));
+  const uint32_t nb = 1u << nbits;
   for (uint32_t i = tid; i < 8 * SORT_BINS; i += 256) (&s_cnt[0][0])[i] = 0;
   if (tid < nb) s_goff[tid] = hist[(size_t)sh.first_stile * SORT_BINS + (size_t)tid * n_stile + tile];
   __syncthreads();
@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(256) k_sort_scatter(const uint8_t* __restrict_
     const uint32_t e = base + w * (SORT_TILE / 8) + r * 32 + lane;
     const bool valid = e < npos;
     v[r] = valid ? (PASS == 0 ? ld32u(sin, e) : __ldg(src_v + sh.in_off + e)) : 0;
-    const uint32_t d = valid ? sort_digit(v[r], bucket_bits, PASS) : (0x10000u | lane);
+    const uint32_t d = valid ? sort_digit(v[r], bucket_bits, shift, nbits) : (0x10000u | lane);
     const uint32_t peers = __match_any_sync(0xffffffffu, d);
     const uint32_t before = __popc(peers & ((1u << lane) - 1));
     uint32_t b = 0;
@@ -162,7 +162,7 @@ __global__ void __launch_bounds__(256) k_sort_scatter(const uint8_t* __restrict_
     const uint32_t idx = w * (SORT_TILE / 8) + r * 32 + lane;
     const uint32_t e = base + idx;
     if (e < npos) {
-      const uint32_t d = sort_digit(v[r], bucket_bits, PASS);
+      const uint32_t d = sort_digit(v[r], bucket_bits, shift, nbits);
       const uint32_t lp = s_base[d] + s_cnt[w][d] + rk[r];
       s_v[lp] = v[r];
       s_pos[lp] = PASS == 0 ? e : __ldg(src_pos + sh.in_off + e);
@@ -174,7 +174,7 @@ __global__ void __launch_bounds__(256) k_sort_scatter(const uint8_t* __restrict_
 #pragma unroll 4
   for (uint32_t j = tid; j < nvalid; j += 256) {
     const uint32_t vv = s_v[j];
-    const uint32_t d = sort_digit(vv, bucket_bits, PASS);
+    const uint32_t d = sort_digit(vv, bucket_bits, shift, nbits);
     const uint32_t dest = s_goff[d] + (j - s_base[d]);
     dp[dest] = s_pos[j]; dv[dest] = vv;
   }

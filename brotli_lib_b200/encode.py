@@ -106,6 +106,17 @@ class Context:
         _lib.check(self._L.bgpu_stage_match_candidates(self._h, _ptr(a), a.size, quality, lgwin, ln.ctypes.data, ds.ctypes.data))
         return ln, ds
 
+    def stage_h10_matches(self, data, lgwin=22):
+        """(offsets[n+1], dist, len): hash-binary-tree.ts findAllMatches for every position."""
+        a = _as_u8(data)
+        cap = a.size * 24 + 64
+        off = np.zeros(a.size + 1, dtype=np.uint32)
+        ds = np.zeros(cap, dtype=np.uint32)
+        ln = np.zeros(cap, dtype=np.uint32)
+        n = C.c_size_t(0)
+        _lib.check(self._L.bgpu_stage_h10_matches(self._h, _ptr(a), a.size, lgwin, off.ctypes.data, ds.ctypes.data, ln.ctypes.data, cap, C.byref(n)))
+        return off, ds[: n.value].copy(), ln[: n.value].copy()
+
     def stage_commands(self, data, quality=5, lgwin=22, mode=0):
         a = _as_u8(data)
         cap = a.size // 2 + 16

@@ -119,6 +119,15 @@ int bgpu_stage_store_trivial(bgpu_ctx* ctx, const uint8_t* in, size_t n, const v
 int bgpu_stage_huffman(bgpu_ctx* ctx, const uint32_t* hist, int count, int alphabet,
                        uint8_t* depths, uint16_t* bits, uint8_t* tree_bits, uint32_t* tree_nbits);
 
+/* BinaryTreeHasher.findAllMatches for every position    src/encode/hash-binary-tree.ts:57-227
+ * (17-bit buckets, <= 64 tree levels, 128-byte tree compare, 63-position short scan), called in
+ * position order with maxLength = n - p and maxBackward = min(p, 4 MiB - 16) as pass 0 of
+ * createHqZopfliBackwardReferences does (backward-references-hq.ts:520-527), every position stored.
+ * offsets[p] .. offsets[p+1] index the (dist, len) entries of position p (strictly increasing
+ * length).  offsets has n + 1 entries; n <= 4 MiB. */
+int bgpu_stage_h10_matches(bgpu_ctx* ctx, const uint8_t* in, size_t n, int lgwin, uint32_t* offsets,
+                           uint32_t* dist, uint32_t* len, size_t cap, size_t* total);
+
 /* Per-kernel CUDA-event milliseconds of the last encode call on this context.  names/ms receive up
  * to cap entries; returns the number of stages. */
 int bgpu_stage_timings(bgpu_ctx* ctx, const char** names, float* ms, int cap);

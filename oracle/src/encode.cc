@@ -227,6 +227,24 @@ int oracle_h5_chain_best(const uint8_t* in, size_t n, int quality, int lgwin, ui
   return 0;
 }
 
+// hash-binary-tree.ts findAllMatches for EVERY position of a single-window input (no skipping of
+// positions covered by long matches — that is caller logic, backward-references-hq.ts:520-540):
+// offsets[i]..offsets[i+1] index (dist, len) of position i; maxLength = n - i, maxBackward = min(i, 4M-16).
+int oracle_h10_all_matches(const uint8_t* in, size_t n, int lgwin, uint32_t* offsets, uint32_t* dist, uint32_t* len, size_t cap, size_t* total) {
+  BinaryTreeHasher h(lgwin, n);
+  Bytes data{in, n}; size_t mask = ((size_t)1 << lgwin) - 1;
+  std::vector<BackwardMatch> m; size_t k = 0;
+  for (size_t i = 0; i < n; i++) {
+    offsets[i] = (uint32_t)k;
+    if (i + 3 >= n) continue;
+    h.findAllMatches(data, mask, i, n - i, std::min<size_t>(i, ((size_t)1 << 22) - 16), m);
+    for (const BackwardMatch& b : m) { if (k < cap) { dist[k] = b.distance; len[k] = b.length; } k++; }
+  }
+  offsets[n] = (uint32_t)k;
+  *total = k;
+  return k > cap ? -1 : 0;
+}
+
 // Commands of the one-shot encode of a single-metablock input (encode.ts:213-267).
 int oracle_commands(const uint8_t* in, size_t n, int quality, int lgwin, int mode, Command* cmds, size_t cap, size_t* ncmd) {
   EncoderParams p = MakeParams(quality, lgwin, mode);

@@ -296,8 +296,9 @@ static inline size_t UpdateNodes(size_t numBytes, size_t blockStart, size_t pos,
       uint32_t dist = matches[j].distance;
       bool isDict = dist > maxDistance;
       uint32_t distCode = dist + 16 - 1;
-      uint32_t nbits = distCode < 16 ? 0 : Log2FloorNonZero(dist) - 1;
-      double distCost = baseCost + nbits + model.getDistanceCost(distCode & 0x3FF);
+      // JS number arithmetic: log2FloorNonZero(1) - 1 == -1 for distance 1 (backward-references-hq.ts:356-357)
+      int nbits = distCode < 16 ? 0 : (int)Log2FloorNonZero(dist) - 1;
+      double distCost = baseCost + (double)nbits + model.getDistanceCost(distCode & 0x3FF);
       size_t maxMatchLen = matches[j].length;
       if (matchLen < maxMatchLen && (isDict || maxMatchLen > maxZopfliLen)) matchLen = maxMatchLen;
       for (; matchLen <= maxMatchLen; matchLen++) {

@@ -44,6 +44,7 @@ def lib():
         L.oracle_encode_stats.argtypes = [u8p, C.c_size_t, C.c_int, C.c_int, C.c_int, szp, C.POINTER(C.c_int)]
         L.oracle_encode_shards.argtypes = [u8p, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, szp]
         L.oracle_h5_chain_best.argtypes = [u8p, C.c_size_t, C.c_int, C.c_int, u8p, u8p]
+        L.oracle_h10_all_matches.argtypes = [u8p, C.c_size_t, C.c_int, u8p, u8p, u8p, C.c_size_t, szp]
         L.oracle_commands.argtypes = [u8p, C.c_size_t, C.c_int, C.c_int, C.c_int, u8p, C.c_size_t, szp]
         L.oracle_store_trivial.argtypes = [u8p, C.c_size_t, u8p, C.c_size_t, C.c_int, C.c_int, C.c_uint, C.c_uint,
                                            u8p, C.c_size_t, szp, C.POINTER(C.c_uint64), u8p]
@@ -101,6 +102,20 @@ def h5_chain_best(data, quality=5, lgwin=22):
     ds = np.zeros(a.size, dtype=np.uint32)
     lib().oracle_h5_chain_best(p, a.size, quality, lgwin, ln.ctypes.data, ds.ctypes.data)
     return ln, ds
+
+
+def h10_all_matches(data, lgwin=22):
+    """(offsets[n+1], dist, len) of BinaryTreeHasher.findAllMatches over every position."""
+    a, p = _buf(data)
+    cap = a.size * 24 + 64
+    off = np.zeros(a.size + 1, dtype=np.uint32)
+    ds = np.zeros(cap, dtype=np.uint32)
+    ln = np.zeros(cap, dtype=np.uint32)
+    n = C.c_size_t(0)
+    rc = lib().oracle_h10_all_matches(p, a.size, lgwin, off.ctypes.data, ds.ctypes.data, ln.ctypes.data, cap, C.byref(n))
+    if rc:
+        raise RuntimeError(f"oracle_h10_all_matches rc={rc}")
+    return off, ds[: n.value].copy(), ln[: n.value].copy()
 
 
 def commands(data, quality=5, lgwin=22, mode=0):

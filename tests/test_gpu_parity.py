@@ -45,6 +45,20 @@ def test_commands_bit_exact_in_exact_parse_mode(gpu_ctx, name, quality, mode):
     assert cm.tobytes() == ocm.tobytes()
 
 
+@pytest.mark.parametrize("name", ["alice29.txt", "enc-ttf.bin", "quickfox_repeated", "backward65536", "random_org_10k.bin", "monkey",
+                                  "html-content.bin", "abc1000", "zeros", "ukkonooa", "font4k"])
+def test_h10_all_matches_bit_exact(gpu_ctx, name):
+    """BinaryTreeHasher.findAllMatches (hash-binary-tree.ts:57-227) for every position: same lists."""
+    data = load_input(name)
+    if name == "zeros":
+        data = data[:20000]   # all-positions FindAllMatches is quadratic on a single run
+    off, ds, ln = gpu_ctx.stage_h10_matches(data, 22)
+    ooff, ods, oln = O.h10_all_matches(data, 22)
+    assert np.array_equal(off, ooff)
+    assert np.array_equal(ds, ods)
+    assert np.array_equal(ln, oln)
+
+
 def test_huffman_bit_exact(gpu_ctx):
     rng = np.random.default_rng(7)
     for alphabet in (256, 704, 64, 124, 18, 26):
