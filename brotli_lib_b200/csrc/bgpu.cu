@@ -4,6 +4,7 @@
 #include "../../include/brotligpu.h"
 #include "metablock_write.cuh"
 #include "h10.cuh"
+#include "zopfli.cuh"
 
 #include <algorithm>
 #include <cmath>
@@ -60,7 +61,7 @@ EncParams make_params(int quality, int lgwin, int mode) {
   p.k.bucket_bits = q < 7 ? 14 : 15;
   p.k.depth = 1 << (q - 1);
   p.k.num_last = q < 7 ? 4 : (q < 9 ? 10 : 16);
-  p.k.sh = 2;
+  p.k.sh = p.quality >= 10 ? 1 : 2;   // Zopfli emits 2- and 3-byte copies
   return p;
 }
 
@@ -91,7 +92,8 @@ struct bgpu_ctx {
   bgpu_tuning tune{0, 0, 0, 0};
   DBuf in, sa_pos, sa_v, sb_pos, sb_v, sort_hist, role, ins, cmds, out, shards, mbs, segs, tile_seg, seg_ncmd, seg_trail, hist, codes, tree_bits, tree_nbits,
       tile_bits, tile_off, shard_bytes, huff_meta, model_arena, misc_arena, d_models, d_splits, d_cb, d_cx, d_bh_ptrs, d_bh_strides, d_cx_outs,
-      h10_bstart, h10_bend, h10_short, h10_forest, h10_m, h10_off, h10_cnt, h10_cursor, h10_full;
+      h10_bstart, h10_bend, h10_short, h10_forest, h10_m, h10_off, h10_cnt, h10_cursor, h10_full,
+      zop_bytehist, zop_model, zop_lc, zop_nodes, zop_ring;
   uint32_t h10_cap = 0;
   bool lut_ready = false;
   std::vector<uint32_t> h_shard_bytes;
@@ -110,7 +112,7 @@ void plan_job(const bgpu_ctx* ctx, const EncParams& P, const size_t* lens, int c
   uint32_t shard_bytes = std::min<uint32_t>(eff(ctx->tune.shard_bytes, 1u << 22), 1u << 22);
   if (P.lgwin < 22) shard_bytes = std::min<uint32_t>(shard_bytes, ((1u << P.lgwin) - 16) & ~3u);
   shard_bytes = std::max<uint32_t>(shard_bytes & ~3u, 64);
-  uint32_t seg_bytes = eff(ctx->tune.segment_bytes, 1u << 14);
+  uint32_t seg_bytes = eff(ctx->tune.segment_bytes, P.quality >= 10 ? 1u << 15 : 1u << 14);
   seg_bytes = seg_bytes >= shard_bytes ? shard_bytes : std::max<uint32_t>(seg_bytes & ~(TILE - 1), TILE);
   uint32_t mb_bytes = eff(ctx->tune.metablock_bytes, shard_bytes);
   mb_bytes = mb_bytes >= shard_bytes ? shard_bytes : std::max<uint32_t>((mb_bytes / seg_bytes) * seg_bytes, seg_bytes);
@@ -289,6 +291,10 @@ int run_frontend(bgpu_ctx* ctx, const Job& job, const EncParams& P, const uint8_
 
 #include "hq_host.inc"
 
+int run_frontend_any(bgpu_ctx* ctx, const Job& job, const EncParams& P, const uint8_t* d_in) {
+  return P.quality >= 10 ? run_frontend_hq(ctx, job, P, d_in) : run_frontend(ctx, job, P, d_in);
+}
+
 void timing_begin(bgpu_ctx* ctx) {
   ctx->n_stage = 0; ctx->launches = 0;
   if (ctx->ev_ok) cudaEventRecord(ctx->ev[0], ctx->stream);
@@ -373,7 +379,7 @@ int collect(bgpu_ctx* ctx, const Job& job, uint8_t* const* out, const size_t* ou
 }
 
 int check_quality(const EncParams& P) { return (P.quality >= 1 && P.quality <= 4) ? BGPU_E_UNSUPPORTED : 0; }
-int check_quality_hq(const EncParams& P) { return P.quality >= 10 ? BGPU_E_UNSUPPORTED : 0; }  // q10/11 land in zopfli.cu
+int check_quality_hq(const EncParams&) { return 0; }   // q10/q11: hq_host.inc
 
 }  // namespace
 
@@ -400,7 +406,8 @@ void bgpu_ctx_destroy(bgpu_ctx* c) {
   DBuf* all[] = {&c->in, &c->sa_pos, &c->sa_v, &c->sb_pos, &c->sb_v, &c->sort_hist, &c->role, &c->ins, &c->cmds, &c->out, &c->shards, &c->mbs, &c->segs, &c->tile_seg, &c->seg_ncmd,
                  &c->seg_trail, &c->hist, &c->codes, &c->tree_bits, &c->tree_nbits, &c->tile_bits, &c->tile_off, &c->shard_bytes, &c->huff_meta,
                  &c->model_arena, &c->misc_arena, &c->d_models, &c->d_splits, &c->d_cb, &c->d_cx, &c->d_bh_ptrs, &c->d_bh_strides, &c->d_cx_outs,
-                 &c->h10_bstart, &c->h10_bend, &c->h10_short, &c->h10_forest, &c->h10_m, &c->h10_off, &c->h10_cnt, &c->h10_cursor, &c->h10_full};
+                 &c->h10_bstart, &c->h10_bend, &c->h10_short, &c->h10_forest, &c->h10_m, &c->h10_off, &c->h10_cnt, &c->h10_cursor, &c->h10_full,
+                 &c->zop_bytehist, &c->zop_model, &c->zop_lc, &c->zop_nodes, &c->zop_ring};
   for (DBuf* b : all) b->release();
   if (c->ev_ok) for (int i = 0; i <= bgpu_ctx::kMaxStages; i++) cudaEventDestroy(c->ev[i]);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
@@ -451,7 +458,7 @@ int bgpu_encode_batch(bgpu_ctx* c, int count, const uint8_t* const* in, const si
   }
   stage_mark(c, "h2d");
   if ((rc = upload_plan(c, job))) return rc;
-  if ((rc = run_frontend(c, job, P, c->in.as<uint8_t>()))) return rc;
+  if ((rc = run_frontend_any(c, job, P, c->in.as<uint8_t>()))) return rc;
   if ((rc = run_backend_any(c, job, P, c->in.as<uint8_t>()))) return rc;
   rc = collect(c, job, out, out_cap, out_len, map.data(), (int)map.size());
   timing_end(c);
@@ -476,7 +483,7 @@ int bgpu_encode_device(bgpu_ctx* c, const void* d_in, size_t n, int quality, int
   Job job; size_t lens[1] = {n}; plan_job(c, P, lens, 1, job);
   timing_begin(c);
   if ((rc = upload_plan(c, job))) return rc;
-  if ((rc = run_frontend(c, job, P, (const uint8_t*)d_in))) return rc;
+  if ((rc = run_frontend_any(c, job, P, (const uint8_t*)d_in))) return rc;
   if ((rc = run_backend_any(c, job, P, (const uint8_t*)d_in))) return rc;
   if (out) {
     uint8_t* outs[1] = {out}; size_t caps[1] = {out_cap};
@@ -535,7 +542,7 @@ static int stream_flush_shard(bgpu_stream* s, size_t n, bool last) {
   CK(cudaMemcpyAsync(c->in.p, s->pending.data(), n, cudaMemcpyHostToDevice, c->stream));
   CK(cudaMemsetAsync(c->in.as<uint8_t>() + n, 0, job.in_bytes + IN_PAD - n, c->stream));
   if ((rc = upload_plan(c, job))) return rc;
-  if ((rc = run_frontend(c, job, P, c->in.as<uint8_t>()))) return rc;
+  if ((rc = run_frontend_any(c, job, P, c->in.as<uint8_t>()))) return rc;
   if ((rc = run_backend(c, job, P, c->in.as<uint8_t>()))) return rc;
   size_t cap = sh.out_cap, len = 0, old = s->outbuf.size();
   s->outbuf.resize(old + cap);
@@ -630,7 +637,7 @@ int bgpu_stage_commands(bgpu_ctx* c, const uint8_t* in, size_t n, int quality, i
   CK(cudaMemcpyAsync(c->in.p, in, n, cudaMemcpyHostToDevice, c->stream));
   CK(cudaMemsetAsync(c->in.as<uint8_t>() + n, 0, job.in_bytes + IN_PAD - n, c->stream));
   if ((rc = upload_plan(c, job))) return rc;
-  if ((rc = run_frontend(c, job, P, c->in.as<uint8_t>()))) return rc;
+  if ((rc = run_frontend_any(c, job, P, c->in.as<uint8_t>()))) return rc;
   size_t slots = (n >> P.k.sh) + 2;
   std::vector<uint8_t> role(n); std::vector<uint32_t> ins(slots); std::vector<Cmd> cm(slots);
   CK(cudaMemcpyAsync(role.data(), c->role.p, n, cudaMemcpyDeviceToHost, c->stream));

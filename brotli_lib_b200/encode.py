@@ -90,9 +90,9 @@ class Context:
         return ln.value, ms.value, (out[: ln.value].tobytes() if fetch else None)
 
     def timings(self):
-        names = (C.c_char_p * 16)()
-        ms = (C.c_float * 16)()
-        k = self._L.bgpu_stage_timings(self._h, names, ms, 16)
+        names = (C.c_char_p * 64)()
+        ms = (C.c_float * 64)()
+        k = min(self._L.bgpu_stage_timings(self._h, names, ms, 64), 64)
         return [(names[i].decode(), ms[i]) for i in range(k)]
 
     def launch_count(self):

@@ -135,7 +135,7 @@ def test_end_to_end_default_roundtrip_and_size(gpu_ctx, name):
 def test_fuzz_matrix_all_supported_qualities(gpu_ctx):
     # test/brotli.test.ts:264-281
     for name, data in fuzz_inputs():
-        for q in (0, 5, 6, 7, 8, 9):
+        for q in (0, 5, 6, 7, 8, 9, 10, 11):
             s = gpu_ctx.encode(data, q)
             _rt(s, data)
             if len(data) < 64 or q == 0:
@@ -218,3 +218,84 @@ def test_full_size_shard_properties(gpu_ctx):
     assert len(s) < len(blob)
     # idempotence: same input, same stream
     assert s == gpu_ctx.encode(blob, 5, 22, 0)
+
+
+# ------------------------------------------------------------------ q10 / q11 (H10 + Zopfli)
+HQ_SIZE_INPUTS = ["alice29.txt", "enc-ttf.bin", "mapsdatazrh", "html-content.bin", "cp852-utf8", "compressed_repeated", "ukkonooa",
+                  "random_org_10k.bin", "font4k", "ramp"]
+
+
+@pytest.mark.parametrize("name", CORPUS + SYNTH)
+def test_hq_roundtrip(gpu_ctx, name):
+    """q10 / q11, all modes: every stream decodes bit-exactly with both Google C decoder versions."""
+    data = load_input(name)
+    for q, mode in ((10, 0), (11, 0), (11, 1), (11, 2)):
+        _rt(gpu_ctx.encode(data, q, 22, mode), data)
+    _rt(gpu_ctx.encode(data, 11, 24, 1), data)
+
+
+@pytest.mark.parametrize("quality", [10, 11])
+def test_hq_size_within_tolerance_of_oracle(gpu_ctx, quality):
+    """north_star: compressed size within 0.5 % of the reference at the same quality and lgwin.
+    The Zopfli pass is segment-parallel and float-driven, so the gate is on the corpus total
+    (negative = smaller than the reference, allowed); per-file numbers are printed."""
+    tg = to = 0
+    for name in HQ_SIZE_INPUTS:
+        data = load_input(name)
+        for mode in (0, 2):
+            s = gpu_ctx.encode(data, quality, 22, mode)
+            ref = len(O.encode(data, quality, 22, mode))
+            print(f"{name} q{quality} mode{mode}: gpu {len(s)} oracle {ref} ({100.0 * (len(s) - ref) / ref:+.2f} %)")
+            tg += len(s); to += ref
+            assert len(s) <= ref * 1.02 + 48, (name, mode, len(s), ref)
+    assert tg <= to * 1.005, (tg, to)
+
+
+def test_hq_trivial_metablocks_size_tracks_oracle(gpu_ctx):
+    """Same commands-only comparison (storeMetaBlockTrivial on both sides): isolates the parse."""
+    gpu_ctx.set_tuning(flags=TRIVIAL)
+    try:
+        tg = to = 0
+        for name in ["alice29.txt", "enc-ttf.bin", "mapsdatazrh"]:
+            data = load_input(name)
+            for q in (10, 11):
+                s = gpu_ctx.encode(data, q, 22, 0)
+                _rt(s, data)
+                tg += len(s); to += len(O.encode(data, q, 22, 0, force_trivial=True))
+        assert abs(tg - to) <= to * 0.005, (tg, to)
+    finally:
+        gpu_ctx.set_tuning()
+
+
+@pytest.mark.parametrize("shard,seg,mb", [(65536, 16384, 0), (100000, 4096, 8192), (1 << 20, 65536, 131072), (4096, 1024, 1024)])
+def test_hq_stitched_shards_segments_metablocks(gpu_ctx, shard, seg, mb):
+    parts = [load_input("alice29.txt"), bytes(70001), load_input("enc-ttf.bin")[:150003], load_input("quickfox_repeated")[:50000],
+             load_input("random_org_10k.bin")]
+    data = b"".join(parts)
+    gpu_ctx.set_tuning(shard_bytes=shard, segment_bytes=seg, metablock_bytes=mb)
+    try:
+        for q, mode in ((10, 0), (11, 2)):
+            _rt(gpu_ctx.encode(data, q, 22, mode), data)
+    finally:
+        gpu_ctx.set_tuning()
+
+
+def test_hq_batch_font_mode_and_streaming(gpu_ctx):
+    import brotli_lib_b200 as B
+    base = load_input("enc-ttf.bin")
+    items = [b"", base[:63], base[:64], base[1000:1000 + 4096], base[:100000], load_input("alice29.txt")[:30000], bytes(5000)]
+    outs = gpu_ctx.encode_batch(items, 11, 22, 2)
+    for d, s in zip(items, outs):
+        _rt(s, d)
+        assert s == gpu_ctx.encode(d, 11, 22, 2)
+    g = Xorshift32(0x12345678)
+    data = g.bytes(4096) + load_input("alice29.txt")[:20000]
+    for q in (10, 11):
+        enc = B.BrotliEncoder({"quality": q}, context=gpu_ctx)
+        out, pos = [], 0
+        while pos < len(data):
+            k = 1 + (g.next() % 2570)
+            out.append(enc.update(data[pos:pos + k]))
+            pos += k
+        out.append(enc.finish())
+        _rt(b"".join(out), data)
