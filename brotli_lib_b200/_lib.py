@@ -13,7 +13,7 @@ SYMBOLS = [
     "bgpu_ctx_create", "bgpu_ctx_destroy", "bgpu_ctx_set_tuning", "bgpu_ctx_set_stream", "bgpu_max_compressed_size", "bgpu_encode",
     "bgpu_encode_batch", "bgpu_encode_device", "bgpu_stream_create", "bgpu_stream_update", "bgpu_stream_finish",
     "bgpu_stream_destroy", "bgpu_stage_match_candidates", "bgpu_stage_commands", "bgpu_stage_store_trivial",
-    "bgpu_stage_huffman", "bgpu_stage_h10_matches", "bgpu_stage_timings", "bgpu_last_launch_count", "bgpu_strerror", "bgpu_last_cuda_error",
+    "bgpu_stage_huffman", "bgpu_stage_h10_matches", "bgpu_stage_timings", "bgpu_last_launch_count", "bgpu_last_counter", "bgpu_strerror", "bgpu_last_cuda_error",
     "bgpu_version",
 ]
 
@@ -58,6 +58,8 @@ def load():
     L.bgpu_stage_h10_matches.argtypes = [vp, vp, sz, i, vp, vp, vp, sz, szp]
     L.bgpu_stage_timings.argtypes = [vp, C.POINTER(C.c_char_p), C.POINTER(C.c_float), i]
     L.bgpu_last_launch_count.argtypes = [vp]
+    L.bgpu_last_counter.argtypes = [vp, i]
+    L.bgpu_last_counter.restype = C.c_uint64
     L.bgpu_strerror.argtypes = [i]
     L.bgpu_strerror.restype = C.c_char_p
     L.bgpu_last_cuda_error.restype = C.c_char_p

@@ -92,9 +92,10 @@ struct bgpu_ctx {
   bgpu_tuning tune{0, 0, 0, 0};
   DBuf in, sa_pos, sa_v, sb_pos, sb_v, sort_hist, role, ins, cmds, out, shards, mbs, segs, tile_seg, seg_ncmd, seg_trail, hist, codes, tree_bits, tree_nbits,
       tile_bits, tile_off, shard_bytes, huff_meta, model_arena, misc_arena, d_models, d_splits, d_cb, d_cx, d_bh_ptrs, d_bh_strides, d_cx_outs,
-      h10_bstart, h10_bend, h10_short, h10_forest, h10_m, h10_off, h10_cnt, h10_cursor, h10_full,
+      h10_bstart, h10_bend, h10_short, h10_forest, h10_m, h10_off, h10_cnt, h10_cursor, h10_full, h10_hot,
       zop_bytehist, zop_model, zop_lc, zop_nodes, zop_ring;
   uint32_t h10_cap = 0;
+  uint64_t counters[4] = {0, 0, 0, 0};   // [0] H10 match entries of the last q10/q11 call
   bool lut_ready = false;
   std::vector<uint32_t> h_shard_bytes;
   // timings
@@ -296,7 +297,7 @@ int run_frontend_any(bgpu_ctx* ctx, const Job& job, const EncParams& P, const ui
 }
 
 void timing_begin(bgpu_ctx* ctx) {
-  ctx->n_stage = 0; ctx->launches = 0;
+  ctx->n_stage = 0; ctx->launches = 0; ctx->counters[0] = 0;
   if (ctx->ev_ok) cudaEventRecord(ctx->ev[0], ctx->stream);
 }
 void timing_end(bgpu_ctx* ctx) {
@@ -406,7 +407,7 @@ void bgpu_ctx_destroy(bgpu_ctx* c) {
   DBuf* all[] = {&c->in, &c->sa_pos, &c->sa_v, &c->sb_pos, &c->sb_v, &c->sort_hist, &c->role, &c->ins, &c->cmds, &c->out, &c->shards, &c->mbs, &c->segs, &c->tile_seg, &c->seg_ncmd,
                  &c->seg_trail, &c->hist, &c->codes, &c->tree_bits, &c->tree_nbits, &c->tile_bits, &c->tile_off, &c->shard_bytes, &c->huff_meta,
                  &c->model_arena, &c->misc_arena, &c->d_models, &c->d_splits, &c->d_cb, &c->d_cx, &c->d_bh_ptrs, &c->d_bh_strides, &c->d_cx_outs,
-                 &c->h10_bstart, &c->h10_bend, &c->h10_short, &c->h10_forest, &c->h10_m, &c->h10_off, &c->h10_cnt, &c->h10_cursor, &c->h10_full,
+                 &c->h10_bstart, &c->h10_bend, &c->h10_short, &c->h10_forest, &c->h10_m, &c->h10_off, &c->h10_cnt, &c->h10_cursor, &c->h10_full, &c->h10_hot,
                  &c->zop_bytehist, &c->zop_model, &c->zop_lc, &c->zop_nodes, &c->zop_ring};
   for (DBuf* b : all) b->release();
   if (c->ev_ok) for (int i = 0; i <= bgpu_ctx::kMaxStages; i++) cudaEventDestroy(c->ev[i]);
@@ -803,6 +804,7 @@ int bgpu_stage_timings(bgpu_ctx* c, const char** names, float* ms, int cap) {
   return c->n_stage;
 }
 int bgpu_last_launch_count(bgpu_ctx* c) { return c ? c->launches : 0; }
+uint64_t bgpu_last_counter(bgpu_ctx* c, int which) { return (c && which >= 0 && which < 4) ? c->counters[which] : 0; }
 
 const char* bgpu_strerror(int code) {
   switch (code) {

@@ -98,6 +98,10 @@ class Context:
     def launch_count(self):
         return self._L.bgpu_last_launch_count(self._h)
 
+    def counter(self, which=0):
+        """Work counters of the last call (0: H10 match entries)."""
+        return int(self._L.bgpu_last_counter(self._h, which))
+
     # ---- stage entry points (parity tests) ----
     def stage_match_candidates(self, data, quality=5, lgwin=22):
         a = _as_u8(data)

@@ -133,6 +133,8 @@ int bgpu_stage_h10_matches(bgpu_ctx* ctx, const uint8_t* in, size_t n, int lgwin
 int bgpu_stage_timings(bgpu_ctx* ctx, const char** names, float* ms, int cap);
 /* Number of kernel launches issued by the last encode call. */
 int bgpu_last_launch_count(bgpu_ctx* ctx);
+/* Work counters of the last encode call: which = 0 -> H10 match entries found (sum over all positions). */
+uint64_t bgpu_last_counter(bgpu_ctx* ctx, int which);
 
 const char* bgpu_strerror(int code);
 const char* bgpu_last_cuda_error(void);
