@@ -53,21 +53,47 @@ struct ClusterProb {
 __device__ __forceinline__ float flog2(float v) { return __log2f(v); }
 
 // Warp-cooperative cost of histogram a (+ b).  All lanes return the same value; *total_out the sum.
+// alpha is a multiple of 4 and <= 768, rows are 16-byte aligned: every lane fetches its (up to 6)
+// 16-byte pieces of both rows up front, so a pair evaluation costs ONE L2 round trip instead of
+// alpha / 32 dependent ones (profiles/r1i: k_cluster_final was 34 % of the q5 step, latency bound).
 __device__ __forceinline__ float hist_cost(const uint32_t* a, const uint32_t* b, int alpha, uint32_t* total_out) {
   const uint32_t lane = threadIdx.x & 31;
-  float ent = 0.f; uint32_t tot = 0, nnz = 0, runs = 0, carry = 1;
-  for (int c = 0; c < alpha; c += 32) {
-    const int i = c + (int)lane;
-    uint32_t x = 0;
-    if (i < alpha) { x = __ldcg(a + i); if (b) x += __ldcg(b + i); }
-    tot += x;
-    if (x) ent -= (float)x * flog2((float)x);
-    const uint32_t W = __ballot_sync(0xffffffffu, x != 0);
-    nnz += __popc(W);
-    runs += __popc(W & ~((W << 1) | carry));   // zero runs that END here (leading and interior ones, never the trailing run)
-    carry = W >> 31;
+  const int nvec = alpha >> 2;
+  const uint4* a4 = reinterpret_cast<const uint4*>(a);
+  const uint4* b4 = reinterpret_cast<const uint4*>(b);
+  uint4 v[6];
+#pragma unroll
+  for (int t = 0; t < 6; t++) {
+    const int i = t * 32 + (int)lane;
+    v[t] = make_uint4(0, 0, 0, 0);
+    if (i < nvec) {
+      v[t] = __ldcg(a4 + i);
+      if (b) { const uint4 y = __ldcg(b4 + i); v[t].x += y.x; v[t].y += y.y; v[t].z += y.z; v[t].w += y.w; }
+    }
   }
-  for (int o = 16; o; o >>= 1) { ent += __shfl_xor_sync(0xffffffffu, ent, o); tot += __shfl_xor_sync(0xffffffffu, tot, o); }
+  float ent = 0.f; uint32_t tot = 0, nnz = 0, runs = 0, carry = 1;
+#pragma unroll
+  for (int t = 0; t < 6; t++) {
+    if (t * 32 < nvec) {
+      const uint4 x = v[t];
+      tot += x.x + x.y + x.z + x.w;
+      if (x.x) ent -= (float)x.x * flog2((float)x.x);
+      if (x.y) ent -= (float)x.y * flog2((float)x.y);
+      if (x.z) ent -= (float)x.z * flog2((float)x.z);
+      if (x.w) ent -= (float)x.w * flog2((float)x.w);
+      const uint32_t m = (x.x ? 1u : 0u) | (x.y ? 2u : 0u) | (x.z ? 4u : 0u) | (x.w ? 8u : 0u);
+      // zero runs that END at a non-zero bin (leading and interior ones, never the trailing run)
+      uint32_t prev = __shfl_up_sync(0xffffffffu, m >> 3, 1);
+      if (lane == 0) prev = carry;
+      nnz += __popc(m);
+      runs += __popc(m & ~((m << 1) | prev) & 15u);
+      carry = __shfl_sync(0xffffffffu, m >> 3, 31);
+    }
+  }
+  for (int o = 16; o; o >>= 1) {
+    ent += __shfl_xor_sync(0xffffffffu, ent, o); tot += __shfl_xor_sync(0xffffffffu, tot, o);
+    nnz += __shfl_xor_sync(0xffffffffu, nnz, o); runs += __shfl_xor_sync(0xffffffffu, runs, o);
+  }
   if (total_out) *total_out = tot;
   if (nnz <= 1) return 12.f;
   const float T = (float)tot;
@@ -378,7 +404,8 @@ struct SplitProb {
   const void* data;        // u8 (literals) or u16 symbols
   uint32_t* hist;          // [SPLIT_MAXK][alpha]  entropy-code histograms
   uint8_t* gid;            // [n_gran]  entropy code of each granule
-  uint64_t* sw;            // [n_gran]  switch bitmap of the DP
+  __half* table;           // [alpha][64]  insert-cost table of the current refinement iteration (k_split_table)
+  __half* acc;             // [n_gran][64]  per-granule insert costs (k_split_acc), shared by the 3 categories of a metablock
   uint32_t* state;         // [4]  0: live entropy codes K, 1: number of blocks
   uint32_t* blk_start;     // [MAX_BLOCKS + 1]  first symbol of each block (prefix), blk_start[nb] = n
   uint8_t* blk_type;       // [MAX_BLOCKS]
@@ -427,11 +454,94 @@ __global__ void __launch_bounds__(256) k_split_hist(const SplitProb* __restrict_
     for (uint32_t i = threadIdx.x; i < p.alpha; i += 256) { const uint32_t v = s_hh[i]; if (v) atomicAdd(&p.hist[cur * p.alpha + i], v); }
 }
 
-// findBlocks over granules (block-splitter.ts:117-211).  grid (chunks, problems); 128 threads =
-// 4 warps, each warp one chunk of SPLIT_CHUNK granules; the insert-cost table of the problem
-// (alpha x 64 halves) sits in dynamic shared memory.
-__global__ void __launch_bounds__(128) k_split_dp(const SplitProb* __restrict__ probs) {
+// findBlocks over granules (block-splitter.ts:117-211), in two kernels:
+//   k_split_acc  every granule in parallel (one warp each): A[g][k] = sum over the granule's symbols of
+//                insertCost[sym][k], stored relative to the granule's minimum and clamped at 64 bits
+//                (the DP is invariant under a per-granule constant, and anything 64 above the minimum is
+//                clamped to the block-switch cost right after it is added) as 64 halves = 128 B per granule;
+//   k_split_dp   the dependent chain: one warp per chunk of SPLIT_CHUNK granules, 2 codes per lane,
+//                switch words and ids of the chunk kept in shared memory for the trace-back.
+// The insert-cost table of the problem (alpha x 64 halves) sits in dynamic shared memory of k_split_acc.
+constexpr uint32_t SPLIT_ACC_GRAN_PER_CTA = 256;   // 8 warps x 32 granules
+constexpr float SPLIT_ACC_CLAMP = 64.f;
+
+// insertCost[sym][k] = log2(total_k) - log2(count_k[sym])   (:136-143; empty bin: -(log2(1) + 2) sic),
+// once per problem and refinement iteration, as alpha x 64 halves in global memory.
+__global__ void __launch_bounds__(256) k_split_table(const SplitProb* __restrict__ probs) {
+  __shared__ float s_lt[SPLIT_MAXK];
+  const SplitProb p = probs[blockIdx.x];
+  const uint32_t n = *p.n_ptr;
+  const uint32_t K = p.state[0];
+  if (n < 128 || K <= 1) return;
+  const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  for (uint32_t k = w; k < SPLIT_MAXK; k += 8) {
+    uint32_t sum = 0;
+    if (k < K) for (uint32_t i = lane; i < p.alpha; i += 32) sum += p.hist[k * p.alpha + i];
+    for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    if (lane == 0) s_lt[k] = sum ? flog2((float)sum) : 0.f;
+  }
+  __syncthreads();
+  for (uint32_t e = tid; e < p.alpha * SPLIT_MAXK; e += 256) {
+    const uint32_t sym = e / SPLIT_MAXK, k = e % SPLIT_MAXK;
+    float c = 60000.f;   // codes >= K never win
+    if (k < K) { const uint32_t cnt = p.hist[k * p.alpha + sym]; c = fmaxf(0.f, s_lt[k] - (cnt ? flog2((float)cnt) : -2.f)); }
+    p.table[e] = __float2half(fminf(c, 60000.f));
+  }
+}
+
+__global__ void __launch_bounds__(256) k_split_acc(const SplitProb* __restrict__ probs) {
   extern __shared__ __align__(16) __half s_ic[];   // [alpha][64]
+  const SplitProb p = probs[blockIdx.y];
+  const uint32_t n = *p.n_ptr;
+  if (n < 128) return;
+  const uint32_t G = (n + p.gran - 1) / p.gran;
+  const uint32_t K = p.state[0];
+  const uint32_t g0 = blockIdx.x * SPLIT_ACC_GRAN_PER_CTA;
+  if (g0 >= G || K <= 1) return;
+  const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(p.table);
+    uint4* dst = reinterpret_cast<uint4*>(s_ic);
+    for (uint32_t e = tid; e < p.alpha * SPLIT_MAXK / 8; e += 256) dst[e] = src[e];
+  }
+  __syncthreads();
+  const __half2* ic2 = reinterpret_cast<const __half2*>(s_ic);
+  __half2* acc2 = reinterpret_cast<__half2*>(p.acc);
+  const uint32_t gend = min(G, g0 + SPLIT_ACC_GRAN_PER_CTA);
+  for (uint32_t g = g0 + w; g < gend; g += 8) {
+    const uint32_t sb = g * p.gran, cnt = min(n, sb + p.gran) - sb;
+    float a0 = 0.f, a1 = 0.f;
+    if (!p.wide) {
+      // 128 one-byte symbols: one u32 (4 symbols) per lane, broadcast by shuffle
+      const uint8_t* d = reinterpret_cast<const uint8_t*>(p.data) + sb;
+      uint32_t wv = 0;
+      if (lane * 4 < cnt) {
+        if (lane * 4 + 4 <= cnt && ((reinterpret_cast<uintptr_t>(d) & 3) == 0)) wv = *reinterpret_cast<const uint32_t*>(d + lane * 4);
+        else for (uint32_t b = 0; b < 4 && lane * 4 + b < cnt; b++) wv |= (uint32_t)d[lane * 4 + b] << (8 * b);
+      }
+#pragma unroll 8
+      for (uint32_t i = 0; i < cnt; i++) {
+        const uint32_t sym = (__shfl_sync(0xffffffffu, wv, i >> 2) >> ((i & 3) * 8)) & 0xFF;
+        const float2 f = __half22float2(ic2[sym * (SPLIT_MAXK / 2) + lane]);
+        a0 += f.x; a1 += f.y;
+      }
+    } else {
+      const uint16_t* d = reinterpret_cast<const uint16_t*>(p.data) + sb;
+      const uint32_t mine = lane < cnt ? d[lane] : 0;
+      for (uint32_t i = 0; i < cnt; i++) {
+        const uint32_t sym = __shfl_sync(0xffffffffu, mine, i);
+        const float2 f = __half22float2(ic2[sym * (SPLIT_MAXK / 2) + lane]);
+        a0 += f.x; a1 += f.y;
+      }
+    }
+    const float m = fminf(a0, a1);
+    const float mn = __uint_as_float(__reduce_min_sync(0xffffffffu, __float_as_uint(m)));   // costs >= 0: bit order == value order
+    acc2[(size_t)g * (SPLIT_MAXK / 2) + lane] = __floats2half2_rn(fminf(a0 - mn, SPLIT_ACC_CLAMP), fminf(a1 - mn, SPLIT_ACC_CLAMP));
+  }
+}
+
+__global__ void __launch_bounds__(128) k_split_dp(const SplitProb* __restrict__ probs) {
+  extern __shared__ __align__(16) uint8_t s_dp[];   // per warp: uint2 sw[SPLIT_CHUNK], u8 gid[SPLIT_CHUNK]
   const SplitProb p = probs[blockIdx.y];
   const uint32_t n = *p.n_ptr;
   if (n < 128) return;
@@ -444,36 +554,18 @@ __global__ void __launch_bounds__(128) k_split_dp(const SplitProb* __restrict__ 
     for (uint32_t g = blockIdx.x * 4 * SPLIT_CHUNK + tid; g < min(G, (blockIdx.x * 4 + 4) * SPLIT_CHUNK); g += 128) p.gid[g] = 0;
     return;
   }
-  // insertCost[sym][k] = log2(total_k) - log2(count_k[sym])   (:136-143; empty bin: -(log2(1) + 2) sic)
-  {
-    __shared__ float s_lt[SPLIT_MAXK];
-    if (tid < SPLIT_MAXK) {
-      float t = 0.f;
-      if (tid < K) { uint32_t s = 0; for (uint32_t i = 0; i < p.alpha; i++) s += p.hist[tid * p.alpha + i]; t = s ? flog2((float)s) : 0.f; }
-      s_lt[tid] = t;
-    }
-    __syncthreads();
-    for (uint32_t e = tid; e < p.alpha * SPLIT_MAXK; e += 128) {
-      const uint32_t sym = e / SPLIT_MAXK, k = e % SPLIT_MAXK;
-      float c = 60000.f;   // codes >= K never win
-      if (k < K) { const uint32_t cnt = p.hist[k * p.alpha + sym]; c = fmaxf(0.f, s_lt[k] - (cnt ? flog2((float)cnt) : -2.f)); }
-      s_ic[e] = __float2half(fminf(c, 60000.f));
-    }
-    __syncthreads();
-  }
   const uint32_t chunk = blockIdx.x * 4 + w;
   if (chunk >= nchunk) return;
+  uint2* s_sw = reinterpret_cast<uint2*>(s_dp + (size_t)w * SPLIT_CHUNK * 9);
+  uint8_t* s_gid = reinterpret_cast<uint8_t*>(s_sw + SPLIT_CHUNK);
   const uint32_t gbeg = chunk * SPLIT_CHUNK, gend = min(G, gbeg + SPLIT_CHUNK);
   float c0 = 0.f, c1 = 0.f;   // codes 2*lane, 2*lane+1
-  const __half2* ic2 = reinterpret_cast<const __half2*>(s_ic);
+  const __half2* acc2 = reinterpret_cast<const __half2*>(p.acc);
+  __half2 nxt = acc2[(size_t)gbeg * (SPLIT_MAXK / 2) + lane];
   for (uint32_t g = gbeg; g < gend; g++) {
-    const uint32_t sb = g * p.gran, se = min(n, sb + p.gran);
-    float a0 = 0.f, a1 = 0.f;
-    for (uint32_t i = sb; i < se; i++) {
-      const float2 f = __half22float2(ic2[split_sym(p, i) * (SPLIT_MAXK / 2) + lane]);
-      a0 += f.x; a1 += f.y;
-    }
-    c0 += a0; c1 += a1;
+    const float2 f = __half22float2(nxt);
+    if (g + 1 < gend) nxt = acc2[(size_t)(g + 1) * (SPLIT_MAXK / 2) + lane];
+    c0 += f.x; c1 += f.y;
     // warp arg-min (costs are >= 0, so the float order is the order of the bit patterns)
     const float m = fminf(c0, c1);
     const uint32_t mb = __reduce_min_sync(0xffffffffu, __float_as_uint(m));
@@ -481,6 +573,7 @@ __global__ void __launch_bounds__(128) k_split_dp(const SplitProb* __restrict__ 
     const uint32_t who = __ballot_sync(0xffffffffu, __float_as_uint(m) == mb);
     const uint32_t wl = __ffs((int)who) - 1;
     const uint32_t first = __shfl_sync(0xffffffffu, (c0 <= c1) ? 2 * lane : 2 * lane + 1, wl);
+    const uint32_t sb = g * p.gran;
     float bsc = p.switch_cost;
     if (sb < 2000) bsc *= 0.77f + (0.07f / 2000.f) * (float)sb;   // :165-170
     c0 -= minc; c1 -= minc;
@@ -488,42 +581,52 @@ __global__ void __launch_bounds__(128) k_split_dp(const SplitProb* __restrict__ 
     if (s0) c0 = bsc;
     if (s1) c1 = bsc;
     const uint32_t e0 = __ballot_sync(0xffffffffu, s0), e1 = __ballot_sync(0xffffffffu, s1);
-    if (lane == 0) {
-      // interleave: bit 2l of the switch word = code 2l (e0 bit l), bit 2l+1 = code 2l+1 (e1 bit l)
-      uint64_t sw = 0;
-      for (int b = 0; b < 32; b++) sw |= ((uint64_t)((e0 >> b) & 1) << (2 * b)) | ((uint64_t)((e1 >> b) & 1) << (2 * b + 1));
-      p.sw[g] = sw; p.gid[g] = (uint8_t)first;
+    // switch bit of code 2l is bit l of e0, of code 2l + 1 bit l of e1
+    if (lane == 0) { s_sw[g - gbeg] = make_uint2(e0, e1); s_gid[g - gbeg] = (uint8_t)first; }
+  }
+  __syncwarp();
+  // trace back (:194-209) in shared memory, then one coalesced store of the chunk's ids
+  if (lane == 0) {
+    uint32_t g = gend - 1 - gbeg;
+    uint32_t cur = s_gid[g];
+    while (g > 0) {
+      g--;
+      const uint2 sw = s_sw[g];
+      if ((((cur & 1) ? sw.y : sw.x) >> (cur >> 1)) & 1) cur = s_gid[g];
+      s_gid[g] = (uint8_t)cur;
     }
   }
   __syncwarp();
-  // trace back (:194-209)
-  if (lane == 0) {
-    uint32_t g = gend - 1;
-    uint8_t cur = p.gid[g];
-    while (g > gbeg) {
-      g--;
-      if ((p.sw[g] >> cur) & 1) cur = p.gid[g];
-      p.gid[g] = cur;
-    }
-  }
+  for (uint32_t g = gbeg + lane; g < gend; g += 32) p.gid[g] = s_gid[g - gbeg];
 }
 
 // remapBlockIds (:213-234) + histogram reset for the next refinement.  One CTA per problem.
 __global__ void __launch_bounds__(256) k_split_remap(const SplitProb* __restrict__ probs) {
-  __shared__ uint32_t s_new[SPLIT_MAXK]; __shared__ uint32_t s_k;
+  __shared__ uint32_t s_new[SPLIT_MAXK]; __shared__ uint32_t s_first[SPLIT_MAXK]; __shared__ uint32_t s_k;
   const SplitProb p = probs[blockIdx.x];
   const uint32_t n = *p.n_ptr;
   if (n < 128) return;
   const uint32_t G = (n + p.gran - 1) / p.gran;
   const uint32_t K = p.state[0];
-  if (threadIdx.x < SPLIT_MAXK) s_new[threadIdx.x] = 0xFFFFFFFFu;
+  if (threadIdx.x < SPLIT_MAXK) { s_new[threadIdx.x] = 0xFFFFFFFFu; s_first[threadIdx.x] = 0xFFFFFFFFu; }
   __syncthreads();
-  if (threadIdx.x == 0) {
-    uint32_t next = 0;
-    if (K > 1) { for (uint32_t g = 0; g < G && next < K; g++) { const uint32_t id = p.gid[g]; if (s_new[id] == 0xFFFFFFFFu) s_new[id] = next++; } }
-    else next = 1;
-    s_k = next;
-  }
+  if (K > 1) {
+    // first granule of every code (parallel), then new ids in order of first appearance
+    for (uint32_t g = threadIdx.x; g < G; g += 256) {
+      const uint32_t id = p.gid[g];
+      if (g == 0 || p.gid[g - 1] != id) atomicMin(&s_first[id], g);
+    }
+    __syncthreads();
+    if (threadIdx.x < SPLIT_MAXK) {
+      const uint32_t f = s_first[threadIdx.x];
+      if (f != 0xFFFFFFFFu) {
+        uint32_t rank = 0;
+        for (uint32_t k = 0; k < SPLIT_MAXK; k++) rank += s_first[k] < f;
+        s_new[threadIdx.x] = rank;
+      }
+    }
+    if (threadIdx.x == 0) { uint32_t c = 0; for (uint32_t k = 0; k < SPLIT_MAXK; k++) c += s_first[k] != 0xFFFFFFFFu; s_k = c; }
+  } else if (threadIdx.x == 0) s_k = 1;
   __syncthreads();
   if (K > 1) for (uint32_t g = threadIdx.x; g < G; g += 256) p.gid[g] = (uint8_t)s_new[p.gid[g]];
   for (uint32_t i = threadIdx.x; i < SPLIT_MAXK * p.alpha; i += 256) p.hist[i] = 0;
