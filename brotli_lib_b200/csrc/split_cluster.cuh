@@ -326,75 +326,133 @@ __global__ void __launch_bounds__(512) k_cluster_final(const ClusterProb* __rest
     }
     __syncthreads();
   }
-  // compact the live clusters: slot -> dense id (order of slots)
-  __shared__ uint32_t s_ncl;
-  uint32_t* s_dense = s_size;   // reuse: dense id of slot k
+  // compact the live clusters (order of slots): list2[c] = cluster index, state[2] = count; the remap and
+  // the reindexing run as their own kernels (k_cluster_remap: parallel over inputs, k_cluster_reindex)
   if (tid == 0) {
     uint32_t c = 0;
-    for (uint32_t k = 0; k < n; k++) if (s_live[k]) { s_dense[k] = c; s_idx[c] = s_idx[k]; s_cost[c] = s_cost[k]; s_tot[c] = s_tot[k]; c++; }
-    s_ncl = c;
+    for (uint32_t k = 0; k < n; k++) if (s_live[k]) { p.total[s_idx[k]] = s_tot[k]; p.list2[c++] = s_idx[k]; }
+    p.state[2] = c;
   }
-  __syncthreads();
-  const uint32_t ncl = s_ncl;
-  // ---- remap (cluster.ts:244-275).  One warp per input; distance of input h to cluster c:
-  //   sum over the support of h of [f(o + x) - f(o)] (+3 bits for a symbol new to the cluster)
-  //   + g(Tc + Th) - g(Tc),   f(p) = -p log2 p, g(T) = T log2 T.
-  for (uint32_t i = w; i < p.m; i += 16) {
-    const uint32_t* h = p.in + (size_t)i * p.stride;
-    // resolve the input's current cluster through the alias chain: default when nothing is cheaper
-    uint32_t cur = i;
-    while (true) { const uint32_t a = p.alias[cur]; if (a == cur) break; cur = a; }
-    uint32_t th = 0;
-    for (uint32_t k = lane; k < p.alpha; k += 32) th += h[k];
+}
+
+// remap (cluster.ts:244-275).  grid (ceil(max inputs / 64), problems), 8 warps, 8 inputs per warp.
+// Distance of input h to cluster c:
+//   sum over the support of h of [f(o + x) - f(o)] (+3 bits for a symbol new to the cluster)
+//   + g(Tc + Th) - g(Tc),   f(p) = -p log2 p, g(T) = T log2 T.
+// The input row stays in registers (<= 6 x 16 bytes per lane); every cluster row is fetched with all
+// its 16-byte pieces in flight at once.
+__global__ void __launch_bounds__(256) k_cluster_remap(const ClusterProb* __restrict__ probs) {
+  const ClusterProb p = probs[blockIdx.y];
+  const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const uint32_t i0 = blockIdx.x * 64 + w * 8;
+  if (i0 >= p.m) return;
+  const uint32_t ncl = p.state[2];
+  const int nvec = (int)p.alpha >> 2;
+  for (uint32_t i = i0; i < min(p.m, i0 + 8); i++) {
+    const uint4* h4 = reinterpret_cast<const uint4*>(p.in + (size_t)i * p.stride);
+    uint4 hv[6]; uint32_t th = 0;
+#pragma unroll
+    for (int t = 0; t < 6; t++) {
+      const int k = t * 32 + (int)lane;
+      hv[t] = k < nvec ? h4[k] : make_uint4(0, 0, 0, 0);
+      th += hv[t].x + hv[t].y + hv[t].z + hv[t].w;
+    }
     for (int o = 16; o; o >>= 1) th += __shfl_xor_sync(0xffffffffu, th, o);
     uint32_t bestc = 0xFFFFFFFFu; float bestd = 3.0e38f;
     if (th != 0) {
+      // the input's current cluster through the alias chain: preferred on ties
+      uint32_t cur = i;
+      while (true) { const uint32_t a = p.alias[cur]; if (a == cur) break; cur = a; }
       for (uint32_t c = 0; c < ncl; c++) {
-        const uint32_t* o = p.work + (size_t)s_idx[c] * p.stride;
+        const uint32_t ci = p.list2[c];
+        const uint4* o4 = reinterpret_cast<const uint4*>(p.work + (size_t)ci * p.stride);
+        uint4 ov[6];
+#pragma unroll
+        for (int t = 0; t < 6; t++) { const int k = t * 32 + (int)lane; ov[t] = (k < nvec && (hv[t].x | hv[t].y | hv[t].z | hv[t].w)) ? __ldcg(o4 + k) : make_uint4(0, 0, 0, 0); }
         float d = 0.f;
-        for (uint32_t k = lane; k < p.alpha; k += 32) {
-          const uint32_t x = h[k];
-          if (x) {
-            const uint32_t oc = __ldcg(o + k);
-            const float s = (float)(oc + x);
-            d -= s * flog2(s);
-            if (oc) d += (float)oc * flog2((float)oc); else d += 3.f;
+#pragma unroll
+        for (int t = 0; t < 6; t++) {
+          const uint32_t xs[4] = {hv[t].x, hv[t].y, hv[t].z, hv[t].w}, os[4] = {ov[t].x, ov[t].y, ov[t].z, ov[t].w};
+#pragma unroll
+          for (int q = 0; q < 4; q++) {
+            if (xs[q]) {
+              const float sum = (float)(os[q] + xs[q]);
+              d -= sum * flog2(sum);
+              if (os[q]) d += (float)os[q] * flog2((float)os[q]); else d += 3.f;
+            }
           }
         }
         for (int oo = 16; oo; oo >>= 1) d += __shfl_xor_sync(0xffffffffu, d, oo);
-        const float tc = (float)s_tot[c], ts = tc + (float)th;
+        const float tc = (float)p.total[ci], ts = tc + (float)th;
         d += ts * flog2(ts) - (tc > 0.f ? tc * flog2(tc) : 0.f);
-        // the cluster that already holds the input is preferred on ties
-        const bool own = s_idx[c] == cur;
+        const bool own = ci == cur;
         if (d < bestd || (d == bestd && own)) { bestd = d; bestc = c; }
       }
     }
-    if (lane == 0) p.sym[i] = bestc;   // 0xFFFFFFFF: empty input, takes its predecessor's cluster below
+    if (lane == 0) p.sym[i] = bestc;   // 0xFFFFFFFF: empty input, takes its predecessor's cluster (k_cluster_reindex)
+  }
+}
+
+// Empty inputs follow the previous non-empty input (cluster.ts:252: bestOut starts at symbols[i-1]; an
+// all-empty prefix takes the first non-empty input's cluster, or cluster 0), then the clusters are
+// renumbered by first appearance (cluster.ts:278-314).  One CTA per problem.
+__global__ void __launch_bounds__(256) k_cluster_reindex(const ClusterProb* __restrict__ probs) {
+  __shared__ uint32_t s_first[CL_FINAL_MAX], s_new[CL_FINAL_MAX];
+  __shared__ int s_wlast[8]; __shared__ int s_carry; __shared__ uint32_t s_firstsym, s_cnt;
+  const ClusterProb p = probs[blockIdx.x];
+  const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const uint32_t ncl = p.state[2];
+  if (p.m == 0 || ncl == 0 || ncl > CL_FINAL_MAX) return;
+  for (uint32_t k = tid; k < CL_FINAL_MAX; k += 256) s_first[k] = 0xFFFFFFFFu;
+  if (tid == 0) { s_carry = -1; s_firstsym = 0xFFFFFFFFu; }
+  __syncthreads();
+  // first non-empty input
+  {
+    uint32_t f = 0xFFFFFFFFu;
+    for (uint32_t i = tid; i < p.m; i += 256) if (p.sym[i] != 0xFFFFFFFFu) { f = i; break; }
+    if (f != 0xFFFFFFFFu) atomicMin(&s_firstsym, f);
   }
   __syncthreads();
-  // empty inputs follow the previous input (cluster.ts:252: bestOut starts at symbols[i-1]); reindex
-  // by first appearance (cluster.ts:278-314); s_cost is reused as the new-id table
-  uint32_t* s_new = reinterpret_cast<uint32_t*>(s_cost);
-  for (uint32_t k = tid; k < ncl; k += 512) s_new[k] = 0xFFFFFFFFu;
+  const uint32_t first_ne = s_firstsym;
+  const uint32_t lead = first_ne != 0xFFFFFFFFu ? p.sym[first_ne] : 0;
   __syncthreads();
-  if (tid == 0) {
-    uint32_t prev = 0xFFFFFFFFu, next = 0;
-    // an all-empty prefix takes the first non-empty input's cluster (or cluster 0)
-    for (uint32_t i = 0; i < p.m; i++) {
-      uint32_t c = p.sym[i];
-      if (c == 0xFFFFFFFFu) c = prev;
-      if (c == 0xFFFFFFFFu) {
-        uint32_t k = i + 1;
-        while (k < p.m && p.sym[k] == 0xFFFFFFFFu) k++;
-        c = k < p.m ? p.sym[k] : 0;
-      }
-      prev = c;
-      if (s_new[c] == 0xFFFFFFFFu) s_new[c] = next++;
-      p.sym[i] = s_new[c];
+  // fill pass: chunks of 256 inputs, prefix-max of "index of the last non-empty input"
+  for (uint32_t base = 0; base < p.m; base += 256) {
+    const uint32_t i = base + tid;
+    const uint32_t sy = i < p.m ? p.sym[i] : 0xFFFFFFFFu;
+    int v = sy != 0xFFFFFFFFu ? (int)i : -1;
+    for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, v, o); if (lane >= (uint32_t)o) v = max(v, y); }
+    if (lane == 31) s_wlast[w] = v;
+    __syncthreads();
+    int pre = s_carry;
+    for (uint32_t k = 0; k < w; k++) pre = max(pre, s_wlast[k]);
+    v = max(v, pre);
+    __syncthreads();
+    if (tid == 255) s_carry = v;
+    if (i < p.m) {
+      const uint32_t c = v >= 0 ? (v == (int)i ? sy : p.sym[v]) : lead;
+      p.alias[i] = c;                      // alias is free now: effective (filled) cluster of input i
+      atomicMin(&s_first[c], i);
     }
-    p.state[2] = next;
+    __syncthreads();
   }
+  // new id = rank of the cluster's first appearance
+  for (uint32_t c = tid; c < ncl; c += 256) {
+    const uint32_t f = s_first[c];
+    uint32_t r = 0;
+    if (f != 0xFFFFFFFFu) for (uint32_t k = 0; k < ncl; k++) r += s_first[k] < f;
+    s_new[c] = r;
+  }
+  if (tid == 0) s_cnt = 0;
   __syncthreads();
+  {
+    uint32_t used = 0;
+    for (uint32_t c = tid; c < ncl; c += 256) used += s_first[c] != 0xFFFFFFFFu;
+    if (used) atomicAdd(&s_cnt, used);
+  }
+  for (uint32_t i = tid; i < p.m; i += 256) p.sym[i] = s_new[p.alias[i]];
+  __syncthreads();
+  if (tid == 0) p.state[2] = s_cnt;
 }
 
 // ---------------------------------------------------------------------------------------
