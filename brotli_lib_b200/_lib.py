@@ -11,7 +11,7 @@ E_UNSUPPORTED = -3
 
 SYMBOLS = [
     "bgpu_ctx_create", "bgpu_ctx_destroy", "bgpu_ctx_set_tuning", "bgpu_ctx_set_stream", "bgpu_max_compressed_size", "bgpu_encode",
-    "bgpu_encode_batch", "bgpu_encode_device", "bgpu_stream_create", "bgpu_stream_update", "bgpu_stream_finish",
+    "bgpu_encode_batch", "bgpu_encode_part", "bgpu_encode_device", "bgpu_stream_create", "bgpu_stream_update", "bgpu_stream_finish",
     "bgpu_stream_destroy", "bgpu_stage_match_candidates", "bgpu_stage_commands", "bgpu_stage_store_trivial",
     "bgpu_stage_huffman", "bgpu_stage_h10_matches", "bgpu_stage_timings", "bgpu_last_launch_count", "bgpu_last_counter", "bgpu_strerror", "bgpu_last_cuda_error",
     "bgpu_version",
@@ -44,6 +44,7 @@ def load():
     L.bgpu_max_compressed_size.restype = sz
     L.bgpu_encode.argtypes = [vp, vp, sz, i, i, i, vp, sz, szp]
     L.bgpu_encode_batch.argtypes = [vp, i, C.POINTER(vp), szp, i, i, i, C.POINTER(vp), szp, szp]
+    L.bgpu_encode_part.argtypes = [vp, vp, sz, vp, C.c_uint, i, i, i, vp, sz, szp]
     L.bgpu_encode_device.argtypes = [vp, vp, sz, i, i, i, vp, sz, szp, C.POINTER(C.c_float)]
     L.bgpu_stream_create.argtypes = [vp, i, i, i, C.POINTER(vp)]
     L.bgpu_stream_update.argtypes = [vp, vp, sz, C.POINTER(vp), szp]

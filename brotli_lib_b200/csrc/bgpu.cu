@@ -109,7 +109,12 @@ namespace {
 uint32_t eff(uint32_t v, uint32_t dflt) { return v ? v : dflt; }
 
 // Splits every stream into shards / metablocks / parse segments / tiles.
-void plan_job(const bgpu_ctx* ctx, const EncParams& P, const size_t* lens, int count, Job& job) {
+// part_flags[s] (optional): BGPU_PART_FIRST | BGPU_PART_LAST of stream s; a part that is not FIRST carries no
+// window header and starts with an unknown distance ring, a part that is not LAST ends with the
+// byte-aligning empty metadata block instead of ISLAST.  `lead` bytes are reserved before the first
+// stream (the two bytes that precede a non-first part live there: literal context, §8e rule 4).
+void plan_job(const bgpu_ctx* ctx, const EncParams& P, const size_t* lens, int count, Job& job,
+              const uint32_t* part_flags = nullptr, size_t lead = 0) {
   uint32_t shard_bytes = std::min<uint32_t>(eff(ctx->tune.shard_bytes, 1u << 22), 1u << 22);
   if (P.lgwin < 22) shard_bytes = std::min<uint32_t>(shard_bytes, ((1u << P.lgwin) - 16) & ~3u);
   shard_bytes = std::max<uint32_t>(shard_bytes & ~3u, 64);
@@ -118,14 +123,15 @@ void plan_job(const bgpu_ctx* ctx, const EncParams& P, const size_t* lens, int c
   uint32_t mb_bytes = eff(ctx->tune.metablock_bytes, shard_bytes);
   mb_bytes = mb_bytes >= shard_bytes ? shard_bytes : std::max<uint32_t>((mb_bytes / seg_bytes) * seg_bytes, seg_bytes);
   uint32_t wb_n, wb_v; window_bits(P.lgwin, &wb_n, &wb_v);
-  size_t in_off = 0, out_off = 0;
+  size_t in_off = lead, out_off = 0;
   for (int s = 0; s < count; s++) {
+    const bool part_first = !part_flags || (part_flags[s] & BGPU_PART_FIRST), part_last = !part_flags || (part_flags[s] & BGPU_PART_LAST);
     StreamPlan sp; sp.in_off = in_off; sp.len = lens[s]; sp.first_shard = (uint32_t)job.shards.size();
     size_t n = lens[s];
     for (size_t so = 0; so < n; so += shard_bytes) {
       ShardD sh; memset(&sh, 0, sizeof sh);
       sh.in_off = in_off + so; sh.len = (uint32_t)std::min<size_t>(shard_bytes, n - so);
-      sh.flags = (so == 0 ? 1u : 0u) | (so + shard_bytes >= n ? 2u : 0u);
+      sh.flags = ((so == 0 && part_first) ? 1u : 0u) | ((so + shard_bytes >= n && part_last) ? 2u : 0u);
       sh.start_nbits = wb_n; sh.start_value = wb_v;
       sh.first_mb = (uint32_t)job.mbs.size();
       sh.first_stile = job.n_stile;
@@ -142,7 +148,7 @@ void plan_job(const bgpu_ctx* ctx, const EncParams& P, const size_t* lens, int c
           SegD sg; memset(&sg, 0, sizeof sg);
           sg.shard = shard_idx; sg.rel_pos = mo + go; sg.len = std::min(seg_bytes, mb.len - go); sg.mb = mb_idx;
           sg.first_tile = (uint32_t)job.tile_seg.size();
-          sg.ring_known = (so == 0 && mo == 0 && go == 0) ? 1 : 0;   // encode.ts:202 {4,11,15,16} only at stream start
+          sg.ring_known = (so == 0 && mo == 0 && go == 0 && part_first) ? 1 : 0;   // encode.ts:202 {4,11,15,16} only at stream start
           uint32_t seg_idx = (uint32_t)job.segs.size();
           for (uint32_t to = 0; to < sg.len; to += TILE) job.tile_seg.push_back(seg_idx);
           job.segs.push_back(sg);
@@ -470,6 +476,50 @@ int bgpu_encode(bgpu_ctx* c, const uint8_t* in, size_t n, int quality, int lgwin
   if (!out_len) return BGPU_E_INVALID;
   const uint8_t* ins[1] = {in}; size_t ns[1] = {n}; uint8_t* outs[1] = {out}; size_t caps[1] = {out_cap};
   return bgpu_encode_batch(c, 1, ins, ns, quality, lgwin, mode, outs, caps, out_len);
+}
+
+// One contiguous piece of a stream that other contexts (other GPUs) encode the rest of.
+int bgpu_encode_part(bgpu_ctx* c, const uint8_t* in, size_t n, const uint8_t* prev2, unsigned part_flags, int quality, int lgwin, int mode,
+                     uint8_t* out, size_t out_cap, size_t* out_len) {
+  if (!c || !out_len || (n && !in)) return BGPU_E_INVALID;
+  const bool first = part_flags & BGPU_PART_FIRST, last = part_flags & BGPU_PART_LAST;
+  if (!first && n && !prev2) return BGPU_E_INVALID;
+  EncParams P = make_params(quality, lgwin, mode);
+  if (P.quality < 5) return BGPU_E_UNSUPPORTED;   // the host-only uncompressed path has no part form
+  int rc;
+  if ((rc = check_quality_hq(P))) return rc;
+  if (n == 0) {
+    // nothing to code: the header (FIRST) and / or ISLAST + ISEMPTY (LAST), encode.ts:399-405
+    HostBits w;
+    if (first) { uint32_t wn, wv; window_bits(P.lgwin, &wn, &wv); w.put(wn, wv); }
+    if (last) { w.put(1, 1); w.put(1, 1); }
+    else if (first) { w.put(6, 6); }             // byte-align the header with an empty metadata block
+    *out_len = w.b.size();
+    if (w.b.size() > out_cap || (w.b.size() && !out)) return BGPU_E_OUTPUT_TOO_SMALL;
+    if (!w.b.empty()) memcpy(out, w.b.data(), w.b.size());
+    return 0;
+  }
+  CK(cudaSetDevice(c->device));
+  const size_t lead = first ? 0 : 256;
+  uint32_t pf[1] = {part_flags}; size_t lens[1] = {n};
+  Job job; plan_job(c, P, lens, 1, job, pf, lead);
+  if ((rc = c->in.reserve(job.in_bytes + IN_PAD))) return rc;
+  timing_begin(c);
+  uint8_t* d_in = c->in.as<uint8_t>();
+  if (lead) {
+    CK(cudaMemsetAsync(d_in, 0, lead, c->stream));
+    CK(cudaMemcpyAsync(d_in + lead - 2, prev2, 2, cudaMemcpyHostToDevice, c->stream));
+  }
+  CK(cudaMemcpyAsync(d_in + lead, in, n, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemsetAsync(d_in + lead + n, 0, job.in_bytes + IN_PAD - lead - n, c->stream));
+  stage_mark(c, "h2d");
+  if ((rc = upload_plan(c, job))) return rc;
+  if ((rc = run_frontend_any(c, job, P, d_in))) return rc;
+  if ((rc = run_backend_any(c, job, P, d_in))) return rc;
+  uint8_t* outs[1] = {out}; size_t caps[1] = {out_cap};
+  rc = collect(c, job, outs, caps, out_len, nullptr, 1);
+  timing_end(c);
+  return rc;
 }
 
 int bgpu_encode_device(bgpu_ctx* c, const void* d_in, size_t n, int quality, int lgwin, int mode, uint8_t* out, size_t out_cap,

@@ -76,6 +76,21 @@ class Context:
         _lib.check(self._L.bgpu_encode_batch(self._h, k, inp, ns, int(quality), int(lgwin), int(mode), outp, caps, lens))
         return [outs[i][: lens[i]].tobytes() for i in range(k)]
 
+    def encode_part(self, data, prev2=b"", first=True, last=True, quality=11, lgwin=22, mode=EncoderMode.GENERIC):
+        """One contiguous part of a stream whose other parts are encoded elsewhere (bgpu_encode_part).
+        prev2: the two input bytes before `data` (needed unless first)."""
+        a = _as_u8(data)
+        cap = self._L.bgpu_max_compressed_size(a.size)
+        out = np.empty(cap, dtype=np.uint8)
+        n = C.c_size_t(0)
+        pv = _as_u8(prev2)
+        if not first and pv.size != 2:
+            raise ValueError("prev2 must hold the two bytes before a non-first part")
+        flags = (1 if first else 0) | (2 if last else 0)
+        _lib.check(self._L.bgpu_encode_part(self._h, _ptr(a), a.size, _ptr(pv), flags, int(quality), int(lgwin), int(mode),
+                                            out.ctypes.data, cap, C.byref(n)))
+        return out[: n.value].tobytes()
+
     def encode_device(self, d_ptr, n, quality=11, lgwin=22, mode=EncoderMode.GENERIC, fetch=False):
         """Input already resident on the device (bench).  Returns (compressed_size, kernel_ms, bytes|None)."""
         ms = C.c_float(0)

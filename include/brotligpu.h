@@ -71,6 +71,23 @@ int bgpu_encode_batch(bgpu_ctx* ctx, int count, const uint8_t* const* in, const 
                       int quality, int lgwin, int mode, uint8_t* const* out, const size_t* out_cap,
                       size_t* out_len);
 
+/* One contiguous PART of a brotliEncode stream, for inputs split over several contexts / GPUs
+ * (north_star: "each chunk is compressed on its own GPU ... stitched on the host into a single valid
+ * stream at byte-aligned metablock boundaries").  The reference has no such call: it stands in for the
+ * metablock loop of src/encode/encode.ts:213-281 run over bytes [off, off + n) of the input.
+ *   BGPU_PART_FIRST  the part opens the stream: window header (bit-writer.ts:172-194) and the
+ *                    {4, 11, 15, 16} distance ring (encode.ts:202);
+ *   BGPU_PART_LAST   the part's final metablock carries ISLAST.
+ * A part without FIRST starts with an unknown distance ring and takes its first literal contexts from
+ * prev2[0..1] = the two input bytes before `in` (in stream order); a part without LAST ends with an
+ * empty metadata block (RFC 7932 section 9.2) so that it is byte-aligned.  The concatenation of the
+ * parts of an input, in order, is one valid stream.  Parts should be multiples of the 4 MiB shard.
+ * quality >= 5 only (BGPU_E_UNSUPPORTED below). */
+#define BGPU_PART_FIRST 1u
+#define BGPU_PART_LAST 2u
+int bgpu_encode_part(bgpu_ctx* ctx, const uint8_t* in, size_t n, const uint8_t* prev2, unsigned part_flags,
+                     int quality, int lgwin, int mode, uint8_t* out, size_t out_cap, size_t* out_len);
+
 /* Same pipeline with the input already resident in device memory (d_in: device pointer, 256-byte
  * aligned, n + 64 bytes readable).  The compressed stream stays on the device unless `out` is
  * non-NULL.  Used by bench.py for the device-resident `value`; the timed CUDA-event duration of

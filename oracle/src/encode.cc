@@ -77,27 +77,36 @@ static void OneShotCommands(const Bytes& data, size_t pos, size_t metablockLen, 
 }
 
 // encode.ts:181-281.  forceTrivial selects storeMetaBlockTrivial for stage-parity tests.
-static std::vector<uint8_t> EncodeStandard(const uint8_t* in, size_t n, const EncoderParams& p, bool forceTrivial, MetaBlockStats* stats) {
+// partFirst / partLast / prev1 / prev2 are NOT in the reference: they restate SURVEY.md §8e's stitching
+// rules (header once, unknown distance ring and true literal context after a boundary, byte-aligning
+// empty metadata block instead of ISLAST) so that parts encoded independently concatenate to one stream.
+// Metablocks after the first (inputs > 16 MiB) take the true previous two bytes as literal context; the
+// reference passes none (encode.ts:271-275 -> 0, 0), which desynchronises its own decoder there.
+static std::vector<uint8_t> EncodeStandard(const uint8_t* in, size_t n, const EncoderParams& p, bool forceTrivial, MetaBlockStats* stats,
+                                           bool partFirst = true, bool partLast = true, uint8_t prev1 = 0, uint8_t prev2 = 0) {
   BitWriter w(std::max<size_t>(1024, (size_t)((double)n * 1.2)));
   unsigned bits, value; EncodeWindowBits(p.lgwin, &bits, &value);
-  w.writeBits(bits, value);
+  if (partFirst) w.writeBits(bits, value);
   std::unique_ptr<HashChainHasher> hc; std::unique_ptr<BinaryTreeHasher> bt;
   if (p.quality <= 9) hc.reset(CreateHashChainHasher(p.quality, p.lgwin));
   else bt.reset(new BinaryTreeHasher(p.lgwin, n));
   int32_t distCache[16] = {4, 11, 15, 16};
+  if (!partFirst) for (int i = 0; i < 16; i++) distCache[i] = 0;
   size_t mask = ((size_t)1 << p.lgwin) - 1;
   Bytes data{in, n};
   const size_t maxMetablock = (size_t)1 << 24;
   size_t pos = 0;
   while (pos < n) {
     size_t mlen = std::min(n - pos, maxMetablock);
-    bool isLast = pos + mlen >= n;
+    bool isLast = partLast && pos + mlen >= n;
     std::vector<Command> commands;
     OneShotCommands(data, pos, mlen, p, mask, hc.get(), bt.get(), distCache, commands);
     if (forceTrivial) StoreMetaBlockTrivial(w, in, pos, mlen, mask, isLast, commands, DistanceAlphabetSize(p), p.npostfix, p.ndirect);
-    else StoreMetaBlock(w, data, pos, mlen, mask, isLast, commands, DistanceAlphabetSize(p), p.quality, p.npostfix, p.ndirect, 0, 0, stats);
+    else StoreMetaBlock(w, data, pos, mlen, mask, isLast, commands, DistanceAlphabetSize(p), p.quality, p.npostfix, p.ndirect,
+                        pos ? in[pos - 1] : prev1, pos > 1 ? in[pos - 2] : (pos ? prev1 : prev2), stats);
     pos += mlen;
   }
+  if (!partLast) { w.writeBits(6, 6); w.alignToByte(); }   // empty metadata block, RFC 7932 section 9.2
   return w.finish();
 }
 
@@ -183,6 +192,20 @@ int oracle_encode_stats(const uint8_t* in, size_t n, int quality, int lgwin, int
   *out_len = v.size();
   stats[0] = s.trivial; stats[1] = s.litTypes; stats[2] = s.cmdTypes; stats[3] = s.distTypes;
   stats[4] = s.litClusters; stats[5] = s.distClusters; stats[6] = s.contextMode;
+  return 0;
+}
+
+// One part of a stream (see EncodeStandard): flags bit 0 = first part, bit 1 = last part; prev = the two
+// bytes before `in` in stream order (prev[0] at -2, prev[1] at -1), ignored for a first part.
+int oracle_encode_part(const uint8_t* in, size_t n, const uint8_t* prev, int flags, int quality, int lgwin, int mode,
+                       uint8_t* out, size_t cap, size_t* out_len) {
+  EncoderParams p = MakeParams(quality, lgwin, mode);
+  if (p.quality < 5 || n == 0) return -2;
+  const bool first = flags & 1, last = flags & 2;
+  std::vector<uint8_t> v = EncodeStandard(in, n, p, false, nullptr, first, last, first ? 0 : prev[1], first ? 0 : prev[0]);
+  *out_len = v.size();
+  if (v.size() > cap) return -1;
+  memcpy(out, v.data(), v.size());
   return 0;
 }
 

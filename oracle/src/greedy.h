@@ -105,7 +105,9 @@ static inline uint32_t DistanceToCode(uint32_t distance, const int32_t* distCach
   static const int8_t off[16] = {0, 0, 0, 0, -1, 1, -2, 2, -3, 3, -1, 1, -2, 2, -3, 3};
   for (int i = 0; i < 16; i++) {
     int64_t cached = (int64_t)distCache[idx[i]] + off[i];
-    if ((int64_t)distance == cached && cached > 0) return i;
+    // distCache[..] > 0: always true in the reference; a part that does not open the stream starts with
+    // an unknown (all-zero) ring whose entries must never be referenced (SURVEY.md §8e rule 3)
+    if ((int64_t)distance == cached && cached > 0 && distCache[idx[i]] > 0) return i;
   }
   return distance + 16 - 1;
 }

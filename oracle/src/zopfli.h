@@ -274,6 +274,7 @@ static inline size_t UpdateNodes(size_t numBytes, size_t blockStart, size_t pos,
     for (int j = 0; j < 16 && bestLen < maxLen; j++) {
       int64_t backward = (int64_t)pd.distanceCache[kIdx[j]] + kOff[j];
       if (backward <= 0 || backward > (int64_t)maxDistance) continue;
+      if (pd.distanceCache[kIdx[j]] <= 0) continue;   // unknown ring entry of a non-first part (never in the reference)
       size_t prevIx = (curIx - (size_t)backward) & mask;
       if (cur + bestLen > mask) break;
       if (rb.at(prevIx + bestLen) != rb.at(cur + bestLen)) continue;

@@ -43,6 +43,7 @@ def lib():
         L.oracle_encode.argtypes = [u8p, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, u8p, C.c_size_t, szp]
         L.oracle_encode_stats.argtypes = [u8p, C.c_size_t, C.c_int, C.c_int, C.c_int, szp, C.POINTER(C.c_int)]
         L.oracle_encode_shards.argtypes = [u8p, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, szp]
+        L.oracle_encode_part.argtypes = [u8p, C.c_size_t, u8p, C.c_int, C.c_int, C.c_int, C.c_int, u8p, C.c_size_t, szp]
         L.oracle_h5_chain_best.argtypes = [u8p, C.c_size_t, C.c_int, C.c_int, u8p, u8p]
         L.oracle_h10_all_matches.argtypes = [u8p, C.c_size_t, C.c_int, u8p, u8p, u8p, C.c_size_t, szp]
         L.oracle_commands.argtypes = [u8p, C.c_size_t, C.c_int, C.c_int, C.c_int, u8p, C.c_size_t, szp]
@@ -75,6 +76,32 @@ def encode(data, quality=11, lgwin=22, mode=0, force_trivial=False):
     if rc:
         raise RuntimeError(f"oracle_encode rc={rc}")
     return out[: n.value].tobytes()
+
+
+def encode_part(data, prev2=b"", first=True, last=True, quality=11, lgwin=22, mode=0, shard=1 << 22):
+    """One part of a stream (SURVEY.md §8e rules), itself cut into independent `shard`-byte windows the
+    way the GPU path does; concatenating the parts of an input in order gives one valid stream."""
+    L = lib()
+    data = bytes(data)
+    out = bytearray()
+    n = len(data)
+    for off in range(0, n, shard):
+        chunk = data[off:off + shard]
+        f = first and off == 0
+        l = last and off + shard >= n
+        pv = bytes(prev2) if off == 0 else data[off - 2:off]
+        if off == 1:
+            pv = bytes(prev2)[1:] + data[:1]
+        pv = (b"\0\0" + pv)[-2:]
+        cap = 2 * len(chunk) + 4096
+        buf = np.empty(cap, dtype=np.uint8)
+        ln = C.c_size_t(0)
+        (ca, cp), (pa, pp) = _buf(chunk), _buf(pv)
+        rc = L.oracle_encode_part(cp, ca.size, pp, (1 if f else 0) | (2 if l else 0), quality, lgwin, mode, buf.ctypes.data, cap, C.byref(ln))
+        if rc:
+            raise RuntimeError(f"oracle_encode_part rc={rc}")
+        out += buf[: ln.value].tobytes()
+    return bytes(out)
 
 
 def encode_stats(data, quality=11, lgwin=22, mode=0):

@@ -1,0 +1,147 @@
+"""One input over several ranks (brotli_lib_b200/sharded.py, bgpu_encode_part): partition, per-rank part,
+host gather + stitch.  CPU tier: the host logic under torch.distributed/gloo at world_size 2 and 3 with
+the oracle as the part encoder (checker only).  GPU tier: the same parts through the C ABI."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+import _oracle as O
+from brotli_lib_b200 import sharded as S
+from brotli_lib_b200 import workloads as W
+from conftest import load_input
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def test_partition_covers_input_in_whole_shards():
+    for n in [0, 1, 63, 64, 4095, 1 << 22, (1 << 22) + 1, 10 * (1 << 22) - 7, 3 * (1 << 22)]:
+        for world in [1, 2, 3, 4, 8]:
+            parts = S.partition(n, world)
+            assert len(parts) == world
+            assert sum(ln for _, ln in parts) == n
+            pos = 0
+            for off, ln in parts:
+                assert off == pos or ln == 0
+                pos += ln
+                if off + ln < n:
+                    assert ln % S.SHARD_BYTES == 0      # only the stream's tail is ragged
+            roles = S.part_roles(parts)
+            assert sum(f for f, _ in roles) == (1 if n else 0)
+            assert sum(l for _, l in roles) == (1 if n else 0)
+
+
+def _oracle_part(chunk, prev2, first, last, quality, lgwin, mode, shard=4096):
+    return O.encode_part(bytes(chunk), prev2, first, last, quality, lgwin, mode, shard=shard)
+
+
+@pytest.mark.parametrize("quality", [5, 10])
+def test_oracle_parts_concatenate_to_one_stream(quality):
+    """SURVEY.md §8e rules on the checker itself: parts cut at arbitrary (even odd) offsets decode."""
+    data = load_input("alice29.txt")[:60000] + bytes(5000) + load_input("enc-ttf.bin")[:30000]
+    whole = O.encode(data, quality, 22, 0)
+    for cuts in [[20000, 61001], [1, 2, 64000], [30000]]:
+        edges = [0] + cuts + [len(data)]
+        parts = []
+        for i in range(len(edges) - 1):
+            a, b = edges[i], edges[i + 1]
+            pv = (b"\0\0" + data[:a])[-2:]
+            parts.append(O.encode_part(data[a:b], pv, i == 0, i == len(edges) - 2, quality, 22, 0, shard=16384))
+        s = S.stitch(parts)
+        assert O.decode(s, len(data)) == data
+        assert len(s) < len(whole) * 1.15 + 64
+
+
+def _rank_main(rank, world, port, path, n, quality, q):
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        data = np.fromfile(path, dtype=np.uint8)[:n].tobytes()
+        enc = lambda c, p, f, l, qq, w, m: _oracle_part(c, p, f, l, qq, w, m, shard=8192)
+        out = S.brotliEncodeSharded(data, {"quality": quality, "lgwin": 22}, part_encoder=enc, shard_bytes=8192)
+        if rank == 0:
+            q.put(out)
+        else:
+            assert out is None
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world,quality", [(2, 5), (3, 9), (2, 11)])
+def test_gloo_ranks_encode_parts_and_rank0_stitches(tmp_path, world, quality):
+    import torch.multiprocessing as mp
+    data = (load_input("alice29.txt")[:70000] + load_input("html-content.bin")[:40000])[: (50001 if quality == 11 else 110000)]
+    path = str(tmp_path / "in.bin")
+    with open(path, "wb") as f:
+        f.write(data)
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_rank_main, args=(r, world, port, path, len(data), quality, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    out = q.get(timeout=240)
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    assert O.decode(out, len(data)) == data
+    # what a single process stitching the same parts would produce
+    parts = S.partition(len(data), world, 8192)
+    roles = S.part_roles(parts)
+    ref = b"".join(_oracle_part(data[o:o + l], (b"\0\0" + data[:o])[-2:], roles[g][0], roles[g][1], quality, 22, 0, shard=8192)
+                   for g, (o, l) in enumerate(parts) if l)
+    assert out == ref
+
+
+# ---------------------------------------------------------------- GPU tier
+@pytest.mark.gpu
+@pytest.mark.parametrize("quality,mode", [(5, 0), (9, 2), (10, 0), (11, 0)])
+def test_gpu_parts_stitch_to_one_stream(gpu_ctx, quality, mode):
+    n = 3 * 65536 + 12345 if quality >= 10 else 5 * 65536 + 777
+    data = np.concatenate([W.text(n // 2, 11), W.records(n - n // 2, 12)]).tobytes()
+    gpu_ctx.set_tuning(shard_bytes=65536)
+    try:
+        for world in [1, 2, 3]:
+            parts = S.partition(len(data), world, 65536)
+            roles = S.part_roles(parts)
+            enc = lambda c, p, f, l, qq, w, m: gpu_ctx.encode_part(c, p, f, l, qq, w, m)
+            pieces = [S.encode_my_part(data, g, world, quality, 22, mode, enc, 65536) for g in range(world)]
+            s = S.stitch(pieces)
+            assert O.decode(s, len(data), "system") == data
+            if O.have_ref_decoder():
+                assert O.decode(s, len(data), "ref") == data
+            if world == 1:
+                assert s == gpu_ctx.encode(data, quality, 22, mode)
+            else:
+                # same shards, same kernels: only the part boundaries' framing differs from the one-context stream
+                assert abs(len(s) - len(gpu_ctx.encode(data, quality, 22, mode))) <= 4 * world
+            ref = b"".join(O.encode_part(data[o:o + l], (b"\0\0" + data[:o])[-2:], roles[g][0], roles[g][1], quality, 22, mode, shard=65536)
+                           for g, (o, l) in enumerate(parts) if l)
+            assert len(s) <= len(ref) * 1.005 + 64
+    finally:
+        gpu_ctx.set_tuning()
+
+
+@pytest.mark.gpu
+def test_gpu_part_edge_cases(gpu_ctx):
+    data = load_input("alice29.txt")[:100000]
+    # ragged parts, a 1-byte part, an empty last part
+    cuts = [0, 65536, 65537, 100000, 100000]
+    pieces = []
+    for i in range(4):
+        a, b = cuts[i], cuts[i + 1]
+        pieces.append(gpu_ctx.encode_part(data[a:b], (b"\0\0" + data[:a])[-2:], i == 0, i == 3, 5, 22, 0))
+    assert O.decode(b"".join(pieces), len(data)) == data
+    # header-only and trailer-only parts around a body
+    s = gpu_ctx.encode_part(b"", b"", True, False, 5, 22, 0) + gpu_ctx.encode_part(data, b"\0\0", False, False, 5, 22, 0) \
+        + gpu_ctx.encode_part(b"", data[-2:], False, True, 5, 22, 0)
+    assert O.decode(s, len(data)) == data
