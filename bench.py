@@ -189,7 +189,7 @@ def run_reference(args, wl, rank, world):
     }
     print(json.dumps(line))
 
-def measure(args, wl, ctx, torch, dist, dev, rank, world, local_rank, steps, warmup, verify):
+def measure(args, wl, ctx, torch, dist, dev, rank, world, local_rank, steps, warmup, verify, tune):
     """Device-resident and end-to-end timing of one workload on this rank; returns the JSON object (rank 0) or None."""
     import numpy as np
     n = wl["size_mb"] << 20
@@ -228,7 +228,6 @@ def measure(args, wl, ctx, torch, dist, dev, rank, world, local_rank, steps, war
     for _ in range(warmup):
         step_device()
     sampler = ClockSampler(local_rank)
-    stage_ms = {}
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     sampler.start()
@@ -236,8 +235,6 @@ def measure(args, wl, ctx, torch, dist, dev, rank, world, local_rank, steps, war
     out_size = 0
     for _ in range(steps):
         out_size, kms, _ = step_device()
-        for name, ms in ctx.timings():
-            stage_ms[name] = stage_ms.get(name, 0.0) + ms
     ev1.record(stream)
     barrier()
     t_dev = ev0.elapsed_time(ev1) * 1e-3
@@ -253,6 +250,23 @@ def measure(args, wl, ctx, torch, dist, dev, rank, world, local_rank, steps, war
     ev1.record(stream)
     barrier()
     t_e2e = ev0.elapsed_time(ev1) * 1e-3
+    # ---- per-kernel durations: in the timed regions above the groups of shards run on several CUDA
+    # streams (lanes) and kernels of different groups overlap, so a kernel's own duration is taken from
+    # one-lane (in-order) passes of the same work, CUDA events around every launch family
+    ctx.set_tuning(**dict(tune, lanes=1))
+    step_device()
+    stage_ms = {}
+    stage_steps = max(1, min(steps, 2))
+    barrier()
+    ev0.record(stream)
+    for _ in range(stage_steps):
+        step_device()
+        for name, ms in ctx.timings():
+            stage_ms[name] = stage_ms.get(name, 0.0) + ms
+    ev1.record(stream)
+    barrier()
+    t_one_lane = ev0.elapsed_time(ev1) * 1e-3 / stage_steps
+    ctx.set_tuning(**tune)
     times = torch.tensor([t_dev, t_e2e], dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
@@ -270,7 +284,7 @@ def measure(args, wl, ctx, torch, dist, dev, rank, world, local_rank, steps, war
     peak, which = peaks()
     per_kernel, per_stage = {}, {}
     for name, ms in stage_ms.items():
-        avg = ms / steps
+        avg = ms / stage_steps
         per_kernel[name] = round(per_kernel.get(name, 0.0) + avg, 3)
         st = STAGE_OF.get(name)
         if st:
@@ -287,7 +301,9 @@ def measure(args, wl, ctx, torch, dist, dev, rank, world, local_rank, steps, war
         "warmup": warmup, "ms_per_step": t_dev / steps * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": wl["label"].format(mb=wl["size_mb"], shards=(n + (1 << 22) - 1) >> 22),
-                   "timing": "CUDA events on the launching stream, max over ranks",
+                   "timing": "CUDA events on the launching stream (lanes fork from / join to it), max over ranks",
+                   "lanes": tune.get("lanes") or "library default (3 lanes x 32-shard groups for q5-9, 1 for q10/11)",
+                   "stage_timing": f"roofline.stages / launch_ms: one-lane in-order passes after the timed region ({round(t_one_lane * 1e3, 1)} ms per step)",
                    "l2": f"input ({wl['size_mb']} MiB) and every intermediate array exceed the 126 MB L2; no flush needed",
                    "compressed_ratio": round(M / n, 4), "verified_roundtrip": verified, "datagen_s": round(t_gen, 1),
                    "h10_matches_per_position": round(n_matches / n, 3) if n_matches else None},
@@ -310,10 +326,10 @@ def run_gpu(args, wl, rank, world, local_rank):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     ctx = B.Context(local_rank)
-    if args.segment_kb:
-        ctx.set_tuning(segment_bytes=args.segment_kb << 10)
+    tune = {"segment_bytes": args.segment_kb << 10, "lanes": args.lanes, "group_shards": args.group_shards}
+    ctx.set_tuning(**tune)
     warm = max(args.warmup, 3)
-    line = measure(args, wl, ctx, torch, dist, dev, rank, world, local_rank, args.steps, warm, not args.no_verify)
+    line = measure(args, wl, ctx, torch, dist, dev, rank, world, local_rank, args.steps, warm, not args.no_verify, tune)
     ctx.close()
     torch.cuda.empty_cache()
     q11 = None
@@ -323,7 +339,9 @@ def run_gpu(args, wl, rank, world, local_rank):
         w3 = dict(WORKLOADS["config3"])
         if args.q11_size_mb:
             w3["size_mb"] = args.q11_size_mb
-        q11 = measure(args, w3, ctx, torch, dist, dev, rank, world, local_rank, min(args.steps, 3), 3, not args.no_verify)
+        tune11 = {"lanes": args.q11_lanes, "group_shards": args.q11_group_shards}
+        ctx.set_tuning(**tune11)
+        q11 = measure(args, w3, ctx, torch, dist, dev, rank, world, local_rank, min(args.steps, 3), 3, not args.no_verify, tune11)
         ctx.close()
     if rank == 0:
         if q11 is not None:
@@ -357,6 +375,10 @@ def main():
     ap.add_argument("--quality", type=int, default=0, help="quality override")
     ap.add_argument("--lgwin", type=int, default=0)
     ap.add_argument("--segment-kb", type=int, default=0, help="parse segment size override (0 = library default)")
+    ap.add_argument("--lanes", type=int, default=0, help="CUDA streams encoding groups of shards at once (0 = library default)")
+    ap.add_argument("--group-shards", type=int, default=0, help="shards per lane group (0 = library default)")
+    ap.add_argument("--q11-lanes", type=int, default=0)
+    ap.add_argument("--q11-group-shards", type=int, default=0)
     ap.add_argument("--no-verify", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-q11", action="store_true", help="skip the config-3 (q11) measurement that accompanies the default run")

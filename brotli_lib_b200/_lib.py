@@ -20,7 +20,7 @@ SYMBOLS = [
 
 class Tuning(C.Structure):
     _fields_ = [("shard_bytes", C.c_uint32), ("segment_bytes", C.c_uint32), ("metablock_bytes", C.c_uint32),
-                ("flags", C.c_uint32)]
+                ("flags", C.c_uint32), ("lanes", C.c_uint32), ("group_shards", C.c_uint32)]
 
 
 _lib = None

@@ -89,7 +89,12 @@ constexpr int PARSE_G = 8;   // lanes per parse segment (kernels.cuh k_parse)
 struct bgpu_ctx {
   int device = 0;
   cudaStream_t stream = nullptr, own_stream = nullptr;
-  bgpu_tuning tune{0, 0, 0, 0};
+  bgpu_tuning tune{0, 0, 0, 0, 0, 0};
+  // lanes (lanes_host.inc): private sub-contexts that encode groups of shards concurrently
+  std::vector<bgpu_ctx*> lanes; bool is_lane = false;
+  cudaEvent_t lane_ev = nullptr, fork_ev = nullptr;
+  uint32_t* h_sizes = nullptr; size_t h_sizes_cap = 0;   // pinned: shard sizes of the lane's current group
+  uint8_t* pin = nullptr; size_t pin_cap = 0, pin_used = 0, pin_want = 0;   // pinned staging of descriptor uploads
   DBuf in, sa_pos, sa_v, sb_pos, sb_v, sort_hist, role, ins, cmds, out, shards, mbs, segs, tile_seg, seg_ncmd, seg_trail, hist, codes, tree_bits, tree_nbits,
       tile_bits, tile_off, shard_bytes, huff_meta, model_arena, misc_arena, d_models, d_splits, d_cb, d_cx, d_bh_ptrs, d_bh_strides, d_cx_outs,
       h10_bstart, h10_bend, h10_short, h10_forest, h10_m, h10_off, h10_cnt, h10_cursor, h10_full, h10_hot,
@@ -170,11 +175,34 @@ void plan_job(const bgpu_ctx* ctx, const EncParams& P, const size_t* lens, int c
   job.in_bytes = in_off; job.out_bytes = out_off;
 }
 
+// Descriptor upload through the context's pinned staging arena: a cudaMemcpyAsync from pageable memory
+// blocks the host until everything queued before it on the stream has run, which would stop the host
+// from feeding the other lanes (lanes_host.inc).  The arena is rewound by timing_begin (start of a job,
+// after the previous job's final synchronisation); when it is too small the copy falls back to the
+// pageable path once and the arena grows at the next rewind.
 int upload(bgpu_ctx* ctx, DBuf& b, const void* src, size_t bytes) {
   int rc = b.reserve(bytes ? bytes : 16);
   if (rc) return rc;
-  if (bytes) CK(cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  if (!bytes) return 0;
+  const size_t need = (bytes + 255) & ~(size_t)255;
+  ctx->pin_want += need;
+  if (ctx->pin && ctx->pin_used + need <= ctx->pin_cap) {
+    uint8_t* stage = ctx->pin + ctx->pin_used; ctx->pin_used += need;
+    memcpy(stage, src, bytes);
+    CK(cudaMemcpyAsync(b.p, stage, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  } else {
+    CK(cudaMemcpyAsync(b.p, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  }
   return 0;
+}
+void pin_rewind(bgpu_ctx* ctx) {
+  if (ctx->pin_want > ctx->pin_cap) {
+    if (ctx->pin) cudaFreeHost(ctx->pin);
+    ctx->pin = nullptr; ctx->pin_cap = 0;
+    const size_t want = ctx->pin_want + ctx->pin_want / 4 + (1u << 16);
+    if (cudaMallocHost(&ctx->pin, want) == cudaSuccess) ctx->pin_cap = want; else { ctx->pin = nullptr; cudaGetLastError(); }
+  }
+  ctx->pin_used = 0; ctx->pin_want = 0;
 }
 
 void stage_mark(bgpu_ctx* ctx, const char* name) {
@@ -303,6 +331,7 @@ int run_frontend_any(bgpu_ctx* ctx, const Job& job, const EncParams& P, const ui
 }
 
 void timing_begin(bgpu_ctx* ctx) {
+  pin_rewind(ctx);
   ctx->n_stage = 0; ctx->launches = 0; ctx->counters[0] = 0;
   if (ctx->ev_ok) cudaEventRecord(ctx->ev[0], ctx->stream);
 }
@@ -385,6 +414,8 @@ int collect(bgpu_ctx* ctx, const Job& job, uint8_t* const* out, const size_t* ou
   return rc;
 }
 
+#include "lanes_host.inc"
+
 int check_quality(const EncParams& P) { return (P.quality >= 1 && P.quality <= 4) ? BGPU_E_UNSUPPORTED : 0; }
 int check_quality_hq(const EncParams&) { return 0; }   // q10/q11: hq_host.inc
 
@@ -416,6 +447,12 @@ void bgpu_ctx_destroy(bgpu_ctx* c) {
                  &c->h10_bstart, &c->h10_bend, &c->h10_short, &c->h10_forest, &c->h10_m, &c->h10_off, &c->h10_cnt, &c->h10_cursor, &c->h10_full, &c->h10_hot,
                  &c->zop_bytehist, &c->zop_model, &c->zop_lc, &c->zop_nodes, &c->zop_ring};
   for (DBuf* b : all) b->release();
+  for (bgpu_ctx* l : c->lanes) bgpu_ctx_destroy(l);
+  c->lanes.clear();
+  if (c->lane_ev) cudaEventDestroy(c->lane_ev);
+  if (c->fork_ev) cudaEventDestroy(c->fork_ev);
+  if (c->h_sizes) cudaFreeHost(c->h_sizes);
+  if (c->pin) cudaFreeHost(c->pin);
   if (c->ev_ok) for (int i = 0; i <= bgpu_ctx::kMaxStages; i++) cudaEventDestroy(c->ev[i]);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
   delete c;
@@ -455,6 +492,13 @@ int bgpu_encode_batch(bgpu_ctx* c, int count, const uint8_t* const* in, const si
   }
   if (map.empty()) return result;
   if ((rc = check_quality_hq(P))) return rc;
+  {
+    uint32_t L; size_t gb;
+    if (lens.size() == 1 && lanes_apply(c, P, lens[0], &L, &gb)) {
+      rc = encode_lanes(c, ptrs[0], nullptr, lens[0], P, L, gb, out[map[0]], out_cap[map[0]], &out_len[map[0]], nullptr);
+      return rc ? rc : result;
+    }
+  }
   Job job; plan_job(c, P, lens.data(), (int)lens.size(), job);
   if ((rc = c->in.reserve(job.in_bytes + IN_PAD))) return rc;
   timing_begin(c);
@@ -531,6 +575,10 @@ int bgpu_encode_device(bgpu_ctx* c, const void* d_in, size_t n, int quality, int
   if ((rc = check_quality(P))) return rc;
   if ((rc = check_quality_hq(P))) return rc;
   CK(cudaSetDevice(c->device));
+  {
+    uint32_t L; size_t gb;
+    if (lanes_apply(c, P, n, &L, &gb)) return encode_lanes(c, nullptr, (const uint8_t*)d_in, n, P, L, gb, out, out_cap, out_len, kernel_ms);
+  }
   Job job; size_t lens[1] = {n}; plan_job(c, P, lens, 1, job);
   timing_begin(c);
   if ((rc = upload_plan(c, job))) return rc;

@@ -54,6 +54,27 @@ __device__ __forceinline__ uint32_t h10_match_from(const uint8_t* in, uint32_t a
   return k < limit ? k : limit;
 }
 
+// Same value as h10_match_from, compared 16 bytes per step with the loads of both sides in flight
+// together (one memory round trip per step instead of one per 4 bytes); *right receives
+// in[a + len] > in[b + len], taken from the bytes already loaded (meaningful when len < limit).
+__device__ __forceinline__ uint32_t h10_match16(const uint8_t* in, uint32_t a, uint32_t b, uint32_t from, uint32_t limit, bool* right) {
+  uint32_t k = from;
+  while (k < limit) {
+    const uint4 x = ld128u(in, (uint64_t)a + k), y = ld128u(in, (uint64_t)b + k);
+    const uint32_t n = prefix16(x, y);
+    if (n < 16) {
+      const uint32_t wa = n < 4 ? x.x : (n < 8 ? x.y : (n < 12 ? x.z : x.w));
+      const uint32_t wb = n < 4 ? y.x : (n < 8 ? y.y : (n < 12 ? y.z : y.w));
+      const uint32_t sh = (n & 3) * 8;
+      *right = ((wa >> sh) & 0xFFu) > ((wb >> sh) & 0xFFu);
+      k += n;
+      break;
+    }
+    k += 16;
+  }
+  return k < limit ? k : limit;
+}
+
 // Short scan (hash-binary-tree.ts:168-193).  out[p] = e0 | e1 << 14 with e = dist | len << 6
 // (dist <= 63, len <= 128), e1 set only when e0 has length 2.
 __global__ void __launch_bounds__(256) k_h10_short(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
@@ -145,7 +166,8 @@ __global__ void __launch_bounds__(128) k_h10_tree(const uint8_t* __restrict__ in
       }
       // both children travel with the data compare: one dependent memory round trip per level
       const uint2 ch = *reinterpret_cast<const uint2*>(fr + 2 * prev);
-      const uint32_t len = h10_match_from(sin, cur, prev, min(bl, br), maxComp);
+      bool right = false;
+      const uint32_t len = h10_match16(sin, cur, prev, min(bl, br), maxComp, &right);
       if (len > best || (short_capped && len >= H10_MAX_TREE_COMP)) {
         best = max(best, len);
         if (n < H10_MAX_MATCHES) lm[n++] = h10_pack(cur - prev, len);
@@ -154,7 +176,7 @@ __global__ void __launch_bounds__(128) k_h10_tree(const uint8_t* __restrict__ in
         if (reroot) { fr[nodeL] = ch.x; fr[nodeR] = ch.y; }
         break;
       }
-      if (sin[cur + len] > sin[prev + len]) {
+      if (right) {
         bl = len;
         if (reroot) fr[nodeL] = prev;
         nodeL = 2 * prev + 1;
@@ -242,9 +264,9 @@ __global__ void __launch_bounds__(128) k_h10_tree_hot(const uint8_t* __restrict_
         short_capped = best >= H10_MAX_TREE_COMP && maxLength > H10_MAX_TREE_COMP;
       }
       // level-1 compare of every insert against its predecessor: independent of the tree state
-      uint32_t len = 0; bool haveLen = false, l1t = false;
+      uint32_t len = 0; bool haveLen = false, l1t = false, right = false;
       if (active && startPrev != H10_INVALID && cur - startPrev <= maxBackward) {
-        len = h10_match_from(sin, cur, startPrev, 0, maxComp);
+        len = h10_match16(sin, cur, startPrev, 0, maxComp, &right);
         haveLen = true; l1t = len >= maxComp;
       }
       const bool next_l1t = __shfl_down_sync(FULL, l1t && reroot, 1) && lane < 31;
@@ -275,14 +297,13 @@ __global__ void __launch_bounds__(128) k_h10_tree_hot(const uint8_t* __restrict_
                 done = true; break;
               }
               const uint2 ch = __ldcg(fr2 + prev);
-              if (!haveLen) { len = h10_match_from(sin, cur, prev, min(bl, br), maxComp); haveLen = true; }
+              if (!haveLen) { len = h10_match16(sin, cur, prev, min(bl, br), maxComp, &right); haveLen = true; }
               if (len >= maxComp) {
                 if (ch.x == H10_PENDING || ch.y == H10_PENDING) break;
                 if (len > best || short_capped) { best = max(best, len); if (n < H10_MAX_MATCHES) lm[n++] = h10_pack(cur - prev, len); }
                 if (reroot) { fr[nodeL] = ch.x; fr[nodeR] = ch.y; }
                 done = true; break;
               }
-              const bool right = sin[cur + len] > sin[prev + len];
               const uint32_t child = right ? ch.y : ch.x;
               if (child == H10_PENDING) break;
               if (len > best) { best = len; if (n < H10_MAX_MATCHES) lm[n++] = h10_pack(cur - prev, len); }

@@ -480,36 +480,39 @@ __device__ __forceinline__ uint32_t split_k0(uint32_t n, uint32_t sym_per_hist) 
 
 // (Re)builds the entropy-code histograms from the granule assignment.  init = 1: granule j
 // belongs to code j * K / G (contiguous slices).  grid (chunks of 64 granules, problems).
-__global__ void __launch_bounds__(256) k_split_hist(const SplitProb* __restrict__ probs, int init) {
+__global__ void __launch_bounds__(256) k_split_hist(const SplitProb* __restrict__ probs, int init, uint32_t gpc) {
   extern __shared__ uint32_t s_hh[];   // alpha counters
   const SplitProb p = probs[blockIdx.y];
   const uint32_t n = *p.n_ptr;
   if (n < 128) return;
   const uint32_t G = (n + p.gran - 1) / p.gran;
   const uint32_t K = init ? split_k0(n, p.sym_per_hist) : p.state[0];
-  const uint32_t g0 = blockIdx.x * 64;
+  const uint32_t g0 = blockIdx.x * gpc;   // gpc granules per CTA (about 8192 symbols)
   if (g0 >= G) return;
   if (K <= 1 && !init) return;
-  const uint32_t g1 = min(G, g0 + 64);
+  const uint32_t g1 = min(G, g0 + gpc);
   for (uint32_t i = threadIdx.x; i < p.alpha; i += 256) s_hh[i] = 0;
   __syncthreads();
-  uint32_t cur = 0xFFFFFFFFu;
-  for (uint32_t g = g0; g < g1; g++) {
-    const uint32_t id = init ? (uint32_t)(((uint64_t)g * K) / G) : p.gid[g];
-    if (id != cur) {
-      if (cur != 0xFFFFFFFFu) {
-        __syncthreads();
-        for (uint32_t i = threadIdx.x; i < p.alpha; i += 256) { const uint32_t v = s_hh[i]; if (v) { atomicAdd(&p.hist[cur * p.alpha + i], v); s_hh[i] = 0; } }
-        __syncthreads();
-      }
-      cur = id;
+  // runs of granules with the same entropy code are counted with all 256 threads at once (a granule is
+  // only 16 symbols in the command / distance streams), then flushed to the code's global histogram
+  __shared__ uint32_t s_run_end, s_run_id;
+  uint32_t g = g0;
+  while (g < g1) {
+    if (threadIdx.x == 0) {
+      const uint32_t id = init ? (uint32_t)(((uint64_t)g * K) / G) : p.gid[g];
+      uint32_t e = g + 1;
+      while (e < g1 && (init ? (uint32_t)(((uint64_t)e * K) / G) : (uint32_t)p.gid[e]) == id) e++;
+      s_run_end = e; s_run_id = id;
     }
-    const uint32_t e = min(n, (g + 1) * p.gran);
-    for (uint32_t i = g * p.gran + threadIdx.x; i < e; i += 256) atomicAdd(&s_hh[split_sym(p, i)], 1u);
+    __syncthreads();
+    const uint32_t ge = s_run_end, id = s_run_id;
+    const uint32_t b = g * p.gran, e = min(n, ge * p.gran);
+    for (uint32_t i = b + threadIdx.x; i < e; i += 256) atomicAdd(&s_hh[split_sym(p, i)], 1u);
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < p.alpha; i += 256) { const uint32_t v = s_hh[i]; if (v) { atomicAdd(&p.hist[id * p.alpha + i], v); s_hh[i] = 0; } }
+    __syncthreads();
+    g = ge;
   }
-  __syncthreads();
-  if (cur != 0xFFFFFFFFu)
-    for (uint32_t i = threadIdx.x; i < p.alpha; i += 256) { const uint32_t v = s_hh[i]; if (v) atomicAdd(&p.hist[cur * p.alpha + i], v); }
 }
 
 // findBlocks over granules (block-splitter.ts:117-211), in two kernels:
@@ -520,7 +523,8 @@ __global__ void __launch_bounds__(256) k_split_hist(const SplitProb* __restrict_
 //   k_split_dp   the dependent chain: one warp per chunk of SPLIT_CHUNK granules, 2 codes per lane,
 //                switch words and ids of the chunk kept in shared memory for the trace-back.
 // The insert-cost table of the problem (alpha x 64 halves) sits in dynamic shared memory of k_split_acc.
-constexpr uint32_t SPLIT_ACC_GRAN_PER_CTA = 256;   // 8 warps x 32 granules
+constexpr uint32_t SPLIT_ACC_GPC_LIT = 256, SPLIT_ACC_GPC_WIDE = 1024;   // granules per CTA (128 / 16 symbols each)
+constexpr uint32_t SPLIT_HIST_GPC_LIT = 64, SPLIT_HIST_GPC_WIDE = 512;
 constexpr float SPLIT_ACC_CLAMP = 64.f;
 
 // insertCost[sym][k] = log2(total_k) - log2(count_k[sym])   (:136-143; empty bin: -(log2(1) + 2) sic),
@@ -547,14 +551,14 @@ __global__ void __launch_bounds__(256) k_split_table(const SplitProb* __restrict
   }
 }
 
-__global__ void __launch_bounds__(256) k_split_acc(const SplitProb* __restrict__ probs) {
+__global__ void __launch_bounds__(256) k_split_acc(const SplitProb* __restrict__ probs, uint32_t gpc) {
   extern __shared__ __align__(16) __half s_ic[];   // [alpha][64]
   const SplitProb p = probs[blockIdx.y];
   const uint32_t n = *p.n_ptr;
   if (n < 128) return;
   const uint32_t G = (n + p.gran - 1) / p.gran;
   const uint32_t K = p.state[0];
-  const uint32_t g0 = blockIdx.x * SPLIT_ACC_GRAN_PER_CTA;
+  const uint32_t g0 = blockIdx.x * gpc;   // granules per CTA: amortises the table load (up to 90 KB)
   if (g0 >= G || K <= 1) return;
   const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   {
@@ -565,7 +569,7 @@ __global__ void __launch_bounds__(256) k_split_acc(const SplitProb* __restrict__
   __syncthreads();
   const __half2* ic2 = reinterpret_cast<const __half2*>(s_ic);
   __half2* acc2 = reinterpret_cast<__half2*>(p.acc);
-  const uint32_t gend = min(G, g0 + SPLIT_ACC_GRAN_PER_CTA);
+  const uint32_t gend = min(G, g0 + gpc);
   for (uint32_t g = g0 + w; g < gend; g += 8) {
     const uint32_t sb = g * p.gran, cnt = min(n, sb + p.gran) - sb;
     float a0 = 0.f, a1 = 0.f;

@@ -34,8 +34,8 @@ class Context:
         if shard_bytes or segment_bytes or metablock_bytes:
             self.set_tuning(shard_bytes, segment_bytes, metablock_bytes)
 
-    def set_tuning(self, shard_bytes=0, segment_bytes=0, metablock_bytes=0, flags=0):
-        t = _lib.Tuning(shard_bytes, segment_bytes, metablock_bytes, flags)
+    def set_tuning(self, shard_bytes=0, segment_bytes=0, metablock_bytes=0, flags=0, lanes=0, group_shards=0):
+        t = _lib.Tuning(shard_bytes, segment_bytes, metablock_bytes, flags, lanes, group_shards)
         _lib.check(self._L.bgpu_ctx_set_tuning(self._h, C.byref(t)))
 
     def set_stream(self, cuda_stream):

@@ -145,3 +145,37 @@ def test_gpu_part_edge_cases(gpu_ctx):
     s = gpu_ctx.encode_part(b"", b"", True, False, 5, 22, 0) + gpu_ctx.encode_part(data, b"\0\0", False, False, 5, 22, 0) \
         + gpu_ctx.encode_part(b"", data[-2:], False, True, 5, 22, 0)
     assert O.decode(s, len(data)) == data
+
+
+# ---------------------------------------------------------------- lanes (groups of shards on concurrent CUDA streams)
+@pytest.mark.gpu
+@pytest.mark.parametrize("quality,mode,lanes,group", [(5, 0, 3, 2), (9, 2, 2, 1), (6, 0, 4, 3), (10, 0, 2, 2), (11, 0, 3, 1)])
+def test_lanes_stream_identical_to_single_lane(gpu_ctx, quality, mode, lanes, group):
+    """Group boundaries are shard boundaries, so the lane pipeline must emit the very same bytes as one
+    in-order stream — from host input (bgpu_encode) and from device-resident input (bgpu_encode_device)."""
+    import torch
+    n = (5 if quality >= 10 else 11) * 65536 + 4321
+    data = np.concatenate([W.text(n // 3, 21), W.records(n // 3, 22), W.text(n - 2 * (n // 3), 23)]).tobytes()
+    try:
+        gpu_ctx.set_tuning(shard_bytes=65536, lanes=1)
+        ref = gpu_ctx.encode(data, quality, 22, mode)
+        assert O.decode(ref, len(data)) == data
+        gpu_ctx.set_tuning(shard_bytes=65536, lanes=lanes, group_shards=group)
+        s = gpu_ctx.encode(data, quality, 22, mode)
+        assert s == ref
+        assert gpu_ctx.launch_count() > 0 and len(gpu_ctx.timings()) > 0
+        d = torch.zeros(len(data) + 4096, dtype=torch.uint8, device="cuda")
+        d[: len(data)] = torch.frombuffer(bytearray(data), dtype=torch.uint8).cuda()
+        torch.cuda.synchronize()
+        size, ms, s2 = gpu_ctx.encode_device(d.data_ptr(), len(data), quality, 22, mode, fetch=True)
+        assert s2 == ref and size == len(ref) and ms > 0
+        # output buffer too small: the needed size is still reported
+        import ctypes as C
+        from brotli_lib_b200 import _lib
+        small = np.empty(16, dtype=np.uint8)
+        ln = C.c_size_t(0)
+        a = np.frombuffer(data, dtype=np.uint8)
+        rc = gpu_ctx._L.bgpu_encode(gpu_ctx._h, a.ctypes.data, a.size, quality, 22, mode, small.ctypes.data, small.size, C.byref(ln))
+        assert rc == _lib.E_OUTPUT_TOO_SMALL and ln.value == len(ref)
+    finally:
+        gpu_ctx.set_tuning()
