@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libbrotligpu.so")
+LIB_PATH = os.environ.get("BGPU_LIB_PATH") or os.path.join(HERE, "libbrotligpu.so")   # override: kernel variants during development
 
 E_OUTPUT_TOO_SMALL = -2
 E_UNSUPPORTED = -3

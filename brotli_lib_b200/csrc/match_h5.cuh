@@ -193,12 +193,12 @@ __device__ __forceinline__ uint4 ld128u(const uint8_t* base, uint64_t off) {
 }
 // number of equal leading bytes of two 16-byte blocks (16 if identical)
 __device__ __forceinline__ uint32_t prefix16(const uint4& x, const uint4& y) {
-  uint32_t d;
-  if ((d = x.x ^ y.x)) return (uint32_t)(__ffs((int)d) - 1) >> 3;
-  if ((d = x.y ^ y.y)) return 4 + ((uint32_t)(__ffs((int)d) - 1) >> 3);
-  if ((d = x.z ^ y.z)) return 8 + ((uint32_t)(__ffs((int)d) - 1) >> 3);
-  if ((d = x.w ^ y.w)) return 12 + ((uint32_t)(__ffs((int)d) - 1) >> 3);
-  return 16;
+  // branch-free: the first differing word by selects, then its first differing byte
+  const uint32_t d0 = x.x ^ y.x, d1 = x.y ^ y.y, d2 = x.z ^ y.z, d3 = x.w ^ y.w;
+  const bool lo_any = (d0 | d1) != 0;
+  const uint32_t d = lo_any ? (d0 ? d0 : d1) : (d2 ? d2 : d3);
+  const uint32_t base = lo_any ? (d0 ? 0u : 4u) : (d2 ? 8u : 12u);
+  return d ? base + ((uint32_t)(__ffs((int)d) - 1) >> 3) : 16u;
 }
 
 // Shared-memory plan of k_probe_sorted (dynamic, PROBE_SMEM bytes).
@@ -282,28 +282,58 @@ __global__ void __launch_bounds__(256) k_probe_sorted(const uint8_t* __restrict_
         mask[k] = m;
       }
     }
-    // ---- confirmed candidates, newest first; up to 20 bytes from shared memory
+    // ---- confirmed candidates, newest first; up to 20 bytes from shared memory.  PROBE_WIDE entries of the
+    // thread advance together, one candidate each per round, so that their shared-memory gathers
+    // (position + 16 data bytes of the candidate; profiles/r1t: short-scoreboard stalls on exactly these
+    // loads are 35 % of the kernel's samples) are in flight at once instead of one after the other.
+#ifndef PROBE_WIDE
+#define PROBE_WIDE 2
+#endif
 #pragma unroll
-    for (int k = 0; k < 4; k++) {
-      const uint32_t e = e0 + k;
-      const uint32_t p = s_p[halo + e];
-      const uint32_t maxLen = min(sh.len - p, 128u);
-      const uint4 x = s_x[halo + e];
-      uint32_t m = mask[k], lm = 0;
-      while (m) {
-        const uint32_t jj = __ffs((int)m) - 1; m &= m - 1;
-        const uint32_t ci = halo + e - jc - jj - 1;
-        const uint32_t backward = p - s_p[ci];
-        if (backward > MAX_BACKWARD) break;          // hash-chains.ts:124 (only within 16 bytes of a 4 MiB shard's end)
-        uint32_t len = 4 + prefix16(x, s_x[ci]);
-        if (len == 20 && maxLen > 20) { lm |= 1u << jj; continue; }
-        len = min(len, maxLen);
-        const int score = 135 * (int)len + 960 - 30 * log2_floor(backward);
-        // ties keep the earlier (nearer) candidate; a deferred long candidate is always nearer than
-        // the ones after it and longer than 20 bytes, so ordering against it is settled below
-        if (score > bScore[k]) { bScore[k] = score; bLen[k] = len; bDist[k] = backward; }
+    for (int k0 = 0; k0 < 4; k0 += PROBE_WIDE) {
+      uint32_t pk[PROBE_WIDE], mlen[PROBE_WIDE], mk[PROBE_WIDE], lmk[PROBE_WIDE]; uint4 xk[PROBE_WIDE];
+      uint32_t any = 0;
+#pragma unroll
+      for (int k = 0; k < PROBE_WIDE; k++) {
+        pk[k] = s_p[halo + e0 + k0 + k];
+        mlen[k] = min(sh.len - pk[k], 128u);
+        xk[k] = s_x[halo + e0 + k0 + k];
+        mk[k] = mask[k0 + k]; lmk[k] = 0; any |= mk[k];
       }
-      longm[k] = lm;
+      while (any) {
+        uint32_t cp[PROBE_WIDE], jj[PROBE_WIDE]; uint4 cx[PROBE_WIDE]; bool act[PROBE_WIDE];
+#pragma unroll
+        for (int k = 0; k < PROBE_WIDE; k++) {
+          act[k] = mk[k] != 0;
+          jj[k] = act[k] ? (uint32_t)__ffs((int)mk[k]) - 1 : 0u;
+          mk[k] &= mk[k] - 1;                       // 0 stays 0
+          const uint32_t ci = halo + e0 + k0 + k - jc - jj[k] - 1;
+          cp[k] = act[k] ? s_p[ci] : 0u;
+          cx[k] = act[k] ? s_x[ci] : make_uint4(0, 0, 0, 0);
+        }
+        any = 0;
+#pragma unroll
+        for (int k = 0; k < PROBE_WIDE; k++) {
+          if (act[k]) {
+            const uint32_t backward = pk[k] - cp[k];
+            if (backward > MAX_BACKWARD) mk[k] = 0;   // hash-chains.ts:124: the walk ends here (only within 16 bytes of a 4 MiB shard's end)
+            else {
+              uint32_t len = 4 + prefix16(xk[k], cx[k]);
+              if (len == 20 && mlen[k] > 20) lmk[k] |= 1u << jj[k];
+              else {
+                len = min(len, mlen[k]);
+                const int score = 135 * (int)len + 960 - 30 * log2_floor(backward);
+                // ties keep the earlier (nearer) candidate; a deferred long candidate is always nearer than
+                // the ones after it and longer than 20 bytes, so ordering against it is settled below
+                if (score > bScore[k0 + k]) { bScore[k0 + k] = score; bLen[k0 + k] = len; bDist[k0 + k] = backward; }
+              }
+            }
+          }
+          any |= mk[k];
+        }
+      }
+#pragma unroll
+      for (int k = 0; k < PROBE_WIDE; k++) longm[k0 + k] = lmk[k];
     }
     // ---- deferred candidates of >= 20 bytes (input reads), newest first
 #pragma unroll

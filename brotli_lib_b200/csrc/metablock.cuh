@@ -147,7 +147,9 @@ __global__ void __launch_bounds__(256) k_mb_compact(const uint8_t* __restrict__ 
   const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   const uint32_t tile_rel = sg.rel_pos + (tile - sg.first_tile) * TILE;
   const uint32_t tile_end = min(sg.rel_pos + sg.len, tile_rel + TILE);
-  const uint8_t* lut = c_ctx_lut + (M.cnt[3] << 9);
+  // the LUT is indexed by data bytes: divergent across a warp, which the constant cache would serialise
+  __shared__ uint8_t lut[512];
+  for (uint32_t i = tid; i < 512; i += 256) lut[i] = c_ctx_lut[(M.cnt[3] << 9) + i];
   uint32_t r[4], pre[4]; uint32_t nl = 0, nc = 0, nd = 0;
 #pragma unroll
   for (int k = 0; k < 4; k++) {

@@ -10,17 +10,32 @@ namespace bgpu {
 
 struct Tok4 { uint32_t n[4]; uint64_t v[4]; };
 
-__device__ __forceinline__ void switch_token(const MbModel& M, int cat, uint32_t rank, uint32_t* type, uint32_t* n, uint64_t* v) {
+// Per-tile view of the metablock's model, in shared memory.  A tile of 1024 positions usually sits
+// inside ONE block of each category (blocks hold hundreds to thousands of symbols): then the block
+// type is a tile constant, no position emits a block switch, and the chain  rank -> block -> type ->
+// context-map row  (three dependent global loads per symbol; profiles/r1k: long-scoreboard stalls
+// 8.3 per issue in k_write2) collapses to a shared-memory row look-up.  Tiles that do contain a block
+// boundary of a category keep the per-symbol look-ups for that category.  The context LUT row of the
+// metablock's mode is staged here too: indexed by data bytes, it diverges across a warp, which the
+// constant cache serialises.
+struct TileModel {
+  uint32_t uni[3], type[3];
+  uint32_t cmap_lit[64], cmap_dist[4];
+  uint8_t lut[512];
+};
+
+__device__ __forceinline__ void switch_token(const MbModel& M, const TileModel& T, int cat, uint32_t rank, uint32_t* type, uint32_t* n, uint64_t* v) {
+  *n = 0; *v = 0;
+  if (T.uni[cat]) { *type = T.type[cat]; return; }
   const uint32_t b = M.sym_blk[cat][rank];
   *type = M.blk_type[cat][b];
-  *n = 0; *v = 0;
   if (b && M.blk_start[cat][b] == rank) { const uint64_t t = M.blk_tok[cat][b]; *n = (uint32_t)(t >> 56); *v = t & 0x00FFFFFFFFFFFFFFull; }
 }
 
 // il / ic / id: rank of this position's literal / command / distance symbol inside the metablock.
 __device__ __forceinline__ Tok4 position_tokens2(const uint8_t* __restrict__ in, uint64_t p, uint32_t r, const uint32_t* __restrict__ ins_at,
                                                  const Cmd* __restrict__ cmds, const MbModel& M, uint32_t il, uint32_t ic, uint32_t id,
-                                                 int sh, bool trivial, const uint8_t* lut) {
+                                                 int sh, bool trivial, const TileModel& T) {
   Tok4 t;
 #pragma unroll
   for (int k = 0; k < 4; k++) { t.n[k] = 0; t.v[k] = 0; }
@@ -30,7 +45,7 @@ __device__ __forceinline__ Tok4 position_tokens2(const uint8_t* __restrict__ in,
     if (r & 8) { prefix = insert_only_prefix(ins); copyField = 2u << 25; }
     else { const Cmd c = cmds[(p + ins) >> sh]; prefix = c.cmdPrefix; copyField = c.copyLen; }
     uint32_t type;
-    switch_token(M, CMD, ic, &type, &t.n[0], &t.v[0]);
+    switch_token(M, T, CMD, ic, &type, &t.n[0], &t.v[0]);
     const uint32_t e = M.codes[CMD][(size_t)type * ALPHA_CMD + prefix];
     uint64_t xv; const uint32_t xn = cmd_extra(ins, copyField, &xv);
     t.n[1] = (e & 0xFF) + xn;
@@ -38,23 +53,23 @@ __device__ __forceinline__ Tok4 position_tokens2(const uint8_t* __restrict__ in,
   }
   if (r & 1) {
     uint32_t type;
-    switch_token(M, LIT, il, &type, &t.n[2], &t.v[2]);
+    switch_token(M, T, LIT, il, &type, &t.n[2], &t.v[2]);
     uint32_t ctx = 0;
     if (!trivial) {
       const bool s1 = M.stream_start && p == M.abs, s2 = M.stream_start && p <= M.abs + 1;
-      ctx = lut[s1 ? 0 : in[p - 1]] | lut[256 + (s2 ? 0 : in[p - 2])];
+      ctx = T.lut[s1 ? 0 : in[p - 1]] | T.lut[256 + (s2 ? 0 : in[p - 2])];
     }
-    const uint32_t cl = M.cmap[LIT][type * 64 + ctx];
+    const uint32_t cl = T.uni[LIT] ? T.cmap_lit[ctx] : M.cmap[LIT][type * 64 + ctx];
     const uint32_t e = M.codes[LIT][cl * 256 + in[p]];
     t.n[3] = e & 0xFF; t.v[3] = e >> 8;
   } else if (r & 2) {
     const Cmd c = cmds[p >> sh];
     if (c.cmdPrefix >= 128) {
       uint32_t type;
-      switch_token(M, DIST, id, &type, &t.n[2], &t.v[2]);
+      switch_token(M, T, DIST, id, &type, &t.n[2], &t.v[2]);
       const uint32_t copyLen = c.copyLen & 0x1FFFFFF;
       const uint32_t dctx = trivial ? 0 : (copyLen > 4 ? 3 : copyLen - 2);
-      const uint32_t cl = M.cmap[DIST][type * 4 + dctx];
+      const uint32_t cl = T.uni[DIST] ? T.cmap_dist[dctx] : M.cmap[DIST][type * 4 + dctx];
       const uint32_t e = M.codes[DIST][cl * ALPHA_DIST_MAX + (c.distPrefix & 0x3FF)];
       t.n[3] = (e & 0xFF) + (c.distPrefix >> 10);
       t.v[3] = (uint64_t)(e >> 8) | ((uint64_t)c.distExtra << (e & 0xFF));
@@ -70,15 +85,22 @@ __device__ __forceinline__ TileRanks tile_ranks(const MbModel& M, uint32_t tile,
                                                 uint32_t (*s_w)[3]) {
   const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   TileRanks R; uint32_t nl = 0, nc = 0, nd = 0;
+  // the thread's 4 roles are one aligned 32-bit load (shards are 256-byte aligned, tiles start at multiples
+  // of 1024); the command records of its copy starts are then fetched together, not one after the other
+  const uint32_t rel0 = tile_rel + 4 * tid;
+  const uint64_t p0 = sh.in_off + rel0;
+  uint32_t r4 = rel0 < tile_end ? *reinterpret_cast<const uint32_t*>(role + p0) : 0u;
+  if (rel0 + 4 > tile_end && rel0 < tile_end) r4 &= (1u << (8 * (tile_end - rel0))) - 1u;   // ragged last tile of a segment
+  uint32_t pre[4];
 #pragma unroll
   for (int k = 0; k < 4; k++) {
-    const uint32_t rel = tile_rel + 4 * tid + k;
-    R.r[k] = 0;
-    if (rel < tile_end) {
-      const uint64_t p = sh.in_off + rel;
-      R.r[k] = role[p];
-      if ((R.r[k] & 2) && !(R.r[k] & 1) && cmds[p >> shft].cmdPrefix >= 128) { nd++; R.r[k] |= 16; }   // bit 4: codes a distance
-    }
+    R.r[k] = (r4 >> (8 * k)) & 0xFFu;
+    const bool copy_start = (R.r[k] & 2) && !(R.r[k] & 1);
+    pre[k] = copy_start ? cmds[(p0 + k) >> shft].cmdPrefix : 0u;
+  }
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    if (pre[k] >= 128) { nd++; R.r[k] |= 16; }   // bit 4: codes a distance
     nl += R.r[k] & 1; nc += (R.r[k] >> 2) & 1;
   }
   const uint32_t packed = nl | (nc << 11) | (nd << 22);
@@ -94,29 +116,63 @@ __device__ __forceinline__ TileRanks tile_ranks(const MbModel& M, uint32_t tile,
   return R;
 }
 
+// One word per (tile, category), written by k_tile_model: bit 31 = one block covers the tile's symbols of
+// the category and does not start inside the tile; low bits = that block's type.
+__global__ void __launch_bounds__(256) k_tile_model(const SegD* __restrict__ segs, const uint32_t* __restrict__ tile_seg,
+                                                    const MbModel* __restrict__ models, uint32_t n_tile, uint32_t* __restrict__ tile_model) {
+  const uint32_t i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= n_tile * 3) return;
+  const uint32_t tile = i / 3, cat = i % 3;
+  const MbModel& M = models[segs[tile_seg[tile]].mb];
+  const uint32_t lt = tile - M.first_tile;
+  const uint32_t first = M.tile_base[lt * 3 + cat];
+  const uint32_t end = lt + 1 < M.n_tile ? M.tile_base[(lt + 1) * 3 + cat] : M.cnt[cat];
+  uint32_t uni = 1, type = 0;
+  if (end > first) {
+    const uint32_t b = M.sym_blk[cat][first];
+    const uint32_t* bs = M.blk_start[cat];
+    uni = (end <= bs[b + 1] && (b == 0 || bs[b] < first)) ? 1u : 0u;   // block 0 never emits a switch
+    type = M.blk_type[cat][b];
+  }
+  tile_model[i] = (uni << 31) | type;
+}
+
+// Fills the tile's TileModel.  No barrier inside: call it BEFORE tile_ranks, whose __syncthreads then
+// publishes it, so that these loads travel together with the role / command loads of tile_ranks.
+__device__ __forceinline__ void tile_model_load(const MbModel& M, uint32_t tile, const uint32_t* __restrict__ tile_model, bool trivial, TileModel& T) {
+  const uint32_t tid = threadIdx.x;
+  const uint32_t wl = tile_model[tile * 3 + LIT], wd = tile_model[tile * 3 + DIST];
+  if (tid < 3) { const uint32_t w = tile_model[tile * 3 + tid]; T.uni[tid] = w >> 31; T.type[tid] = w & 0xFFFFu; }
+  const uint8_t* lut = c_ctx_lut + (M.cnt[3] << 9);
+  for (uint32_t i = tid; i < 512; i += 256) T.lut[i] = lut[i];
+  if (tid < 64) T.cmap_lit[tid] = ((wl >> 31) && (!trivial || tid == 0)) ? M.cmap[LIT][(wl & 0xFFFFu) * 64 + tid] : 0;
+  else if (tid < 68) T.cmap_dist[tid - 64] = ((wd >> 31) && (!trivial || tid == 64)) ? M.cmap[DIST][(wd & 0xFFFFu) * 4 + (tid - 64)] : 0;
+}
+
 __global__ void __launch_bounds__(256) k_tilebits2(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
                                                    const SegD* __restrict__ segs, const uint32_t* __restrict__ tile_seg,
                                                    const MbModel* __restrict__ models, const uint8_t* __restrict__ role,
                                                    const uint32_t* __restrict__ ins_at, const Cmd* __restrict__ cmds,
-                                                   uint32_t* __restrict__ tile_bits, Params P) {
+                                                   const uint32_t* __restrict__ tile_model, uint32_t* __restrict__ tile_bits, Params P) {
   __shared__ uint32_t s_w[8][3];
   __shared__ uint32_t s_sum[8];
+  __shared__ TileModel s_T;
   const uint32_t tile = blockIdx.x;
   const SegD sg = segs[tile_seg[tile]];
   const ShardD sh = shards[sg.shard];
   const MbModel& M = models[sg.mb];
   const bool trivial = M.cnt[4] != 0;
-  const uint8_t* lut = c_ctx_lut + (M.cnt[3] << 9);
   const uint32_t tile_rel = sg.rel_pos + (tile - sg.first_tile) * TILE;
   const uint32_t tile_end = min(sg.rel_pos + sg.len, tile_rel + TILE);
-  TileRanks R = tile_ranks(M, tile, sh, tile_rel, tile_end, role, cmds, P.sh, s_w);
+  tile_model_load(M, tile, tile_model, trivial, s_T);
+  TileRanks R = tile_ranks(M, tile, sh, tile_rel, tile_end, role, cmds, P.sh, s_w);   // contains a __syncthreads
   uint32_t bits = 0;
 #pragma unroll
   for (int k = 0; k < 4; k++) {
     const uint32_t r = R.r[k];
     if (!r) continue;
     const uint64_t p = sh.in_off + tile_rel + 4 * threadIdx.x + k;
-    const Tok4 t = position_tokens2(in, p, r, ins_at, cmds, M, R.il, R.ic, R.id, P.sh, trivial, lut);
+    const Tok4 t = position_tokens2(in, p, r, ins_at, cmds, M, R.il, R.ic, R.id, P.sh, trivial, s_T);
     bits += t.n[0] + t.n[1] + t.n[2] + t.n[3];
     R.il += r & 1; R.ic += (r >> 2) & 1; R.id += (r >> 4) & 1;
   }
@@ -208,11 +264,12 @@ __global__ void __launch_bounds__(256) k_write2(const uint8_t* __restrict__ in, 
                                                 const SegD* __restrict__ segs, const uint32_t* __restrict__ tile_seg,
                                                 const MbModel* __restrict__ models, const uint8_t* __restrict__ role,
                                                 const uint32_t* __restrict__ ins_at, const Cmd* __restrict__ cmds,
-                                                const uint32_t* __restrict__ tile_bits, const uint32_t* __restrict__ tile_off,
-                                                uint8_t* __restrict__ out, Params P) {
+                                                const uint32_t* __restrict__ tile_model, const uint32_t* __restrict__ tile_bits,
+                                                const uint32_t* __restrict__ tile_off, uint8_t* __restrict__ out, Params P) {
   __shared__ uint32_t s_stage[STAGE_WORDS];
   __shared__ uint32_t s_w[8][3];
   __shared__ uint32_t s_warp[8];
+  __shared__ TileModel s_T;
   const uint32_t tile = blockIdx.x;
   const uint32_t total = tile_bits[tile];
   if (total == 0) return;
@@ -220,7 +277,6 @@ __global__ void __launch_bounds__(256) k_write2(const uint8_t* __restrict__ in, 
   const ShardD sh = shards[sg.shard];
   const MbModel& M = models[sg.mb];
   const bool trivial = M.cnt[4] != 0;
-  const uint8_t* lut = c_ctx_lut + (M.cnt[3] << 9);
   const uint32_t tid = threadIdx.x;
   const uint32_t off = tile_off[tile];
   const uint32_t head = off & 31;
@@ -229,6 +285,7 @@ __global__ void __launch_bounds__(256) k_write2(const uint8_t* __restrict__ in, 
   if (staged) for (uint32_t i = tid; i < nwords + 2; i += 256) s_stage[i] = 0;
   const uint32_t tile_rel = sg.rel_pos + (tile - sg.first_tile) * TILE;
   const uint32_t tile_end = min(sg.rel_pos + sg.len, tile_rel + TILE);
+  tile_model_load(M, tile, tile_model, trivial, s_T);
   TileRanks R = tile_ranks(M, tile, sh, tile_rel, tile_end, role, cmds, P.sh, s_w);   // contains a __syncthreads
   Tok4 tk[4]; uint32_t mine = 0;
 #pragma unroll
@@ -238,7 +295,7 @@ __global__ void __launch_bounds__(256) k_write2(const uint8_t* __restrict__ in, 
     for (int f = 0; f < 4; f++) { tk[k].n[f] = 0; tk[k].v[f] = 0; }
     if (r) {
       const uint64_t p = sh.in_off + tile_rel + 4 * tid + k;
-      tk[k] = position_tokens2(in, p, r, ins_at, cmds, M, R.il, R.ic, R.id, P.sh, trivial, lut);
+      tk[k] = position_tokens2(in, p, r, ins_at, cmds, M, R.il, R.ic, R.id, P.sh, trivial, s_T);
       R.il += r & 1; R.ic += (r >> 2) & 1; R.id += (r >> 4) & 1;
     }
     mine += tk[k].n[0] + tk[k].n[1] + tk[k].n[2] + tk[k].n[3];

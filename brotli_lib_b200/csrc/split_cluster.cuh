@@ -590,10 +590,22 @@ __global__ void __launch_bounds__(256) k_split_acc(const SplitProb* __restrict__
     } else {
       const uint16_t* d = reinterpret_cast<const uint16_t*>(p.data) + sb;
       const uint32_t mine = lane < cnt ? d[lane] : 0;
-      for (uint32_t i = 0; i < cnt; i++) {
-        const uint32_t sym = __shfl_sync(0xffffffffu, mine, i);
-        const float2 f = __half22float2(ic2[sym * (SPLIT_MAXK / 2) + lane]);
-        a0 += f.x; a1 += f.y;
+      if (cnt == 16) {
+        // full granule: all 16 table rows in flight at once, two partial sums
+        float b0 = 0.f, b1 = 0.f;
+#pragma unroll
+        for (uint32_t i = 0; i < 16; i += 2) {
+          const uint32_t s0 = __shfl_sync(0xffffffffu, mine, i), s1 = __shfl_sync(0xffffffffu, mine, i + 1);
+          const float2 f = __half22float2(ic2[s0 * (SPLIT_MAXK / 2) + lane]), g = __half22float2(ic2[s1 * (SPLIT_MAXK / 2) + lane]);
+          a0 += f.x; a1 += f.y; b0 += g.x; b1 += g.y;
+        }
+        a0 += b0; a1 += b1;
+      } else {
+        for (uint32_t i = 0; i < cnt; i++) {
+          const uint32_t sym = __shfl_sync(0xffffffffu, mine, i);
+          const float2 f = __half22float2(ic2[sym * (SPLIT_MAXK / 2) + lane]);
+          a0 += f.x; a1 += f.y;
+        }
       }
     }
     const float m = fminf(a0, a1);

@@ -42,8 +42,8 @@ typedef struct bgpu_tuning {
   uint32_t metablock_bytes; /* metablock size inside a shard (default = shard)                    */
   uint32_t flags;           /* BGPU_F_*                                                           */
   uint32_t lanes;           /* CUDA streams that encode groups of shards of one large input at once
-                               (default 3; 1 = one in-order stream; q10/q11 use lanes only when set)  */
-  uint32_t group_shards;    /* shards per group (default 32 = 128 MiB)                             */
+                               (default 4; 1 = one in-order stream; q10/q11 use lanes only when set)  */
+  uint32_t group_shards;    /* shards per group (default: shards / lanes, clamped to 16..64)       */
 } bgpu_tuning;
 #define BGPU_F_KEEP_DEVICE_OUTPUT 1u /* bench: skip the device->host gather (device-resident timing) */
 #define BGPU_F_TRIVIAL_METABLOCKS 2u /* storeMetaBlockTrivial for every metablock (metablock.ts:290-389): no block split, no context map */
