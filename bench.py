@@ -141,6 +141,11 @@ STAGE_OF = {"k_sort_pass0": "match_finding", "k_sort_pass1": "match_finding", "k
             "k_hist": "histograms", "k_huff": "huffman", "k_tilebits": "bit_writer", "k_offsets": "bit_writer", "k_write": "bit_writer",
             "k_mb_compact": "histograms", "k_ctx_hist": "histograms", "k_split": "block_split", "k_cluster_blocks": "clustering",
             "k_cluster_ctx": "clustering", "k_huff_hdr": "huffman", "k_write2": "bit_writer"}
+STAGE_KERNELS = {"match_finding": "k_sort_hist/scan/scatter x2 + k_probe_sorted", "h10_matches": "k_sort_* x3 + k_h10_short/runs/tree/tree_hot",
+                 "parse": "k_parse<8> + k_stitch", "zopfli": "k_zop_model/litcost/dp (+ k_stitch, k_hist between passes)",
+                 "histograms": "k_mb_counts/scan/compact + k_ctx_hist", "block_split": "k_split_table/acc/dp/remap/hist, k_split_blocks, k_block_hist",
+                 "clustering": "k_cluster_batch/gather/final/remap/reindex", "huffman": "k_huff_mb + k_mb_header",
+                 "bit_writer": "k_tile_model + k_tilebits2 + k_offsets2 + k_write2"}
 ALGO_BYTES = {
     "match_finding": lambda n, M, S: 9.0 * n,                # K1+K2+K3: N + 8N
     "h10_matches": lambda n, M, S: n + 8.0 * S,              # K4: N + 8 * matches
@@ -162,6 +167,18 @@ def peaks():
         except Exception:
             pass
     return 6650.0, "fallback"
+
+
+def ncu_traffic(stage, n):
+    """DRAM bytes per step of the stage's kernels from the committed `ncu --set full` capture
+    (profiles/traffic.json: dram__bytes_read.sum + dram__bytes_write.sum), only for the input size it was taken at."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json"))).get(stage)
+        if t and int(t["input_bytes"]) == int(n):
+            return int(t["dram_bytes"])
+    except Exception:
+        pass
+    return None
 
 
 def run_reference(args, wl, rank, world):
@@ -310,8 +327,8 @@ def measure(args, wl, ctx, torch, dist, dev, rank, world, local_rank, steps, war
         "e2e": {"value": n * world * steps / t_e2e / 1e9, "unit": UNIT, "h2d_bytes_per_step": n, "d2h_bytes_per_step": int(e2e_size)},
         "gpu_launches": launches,
         "clocks": clocks,
-        "roofline": {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
-                     "traffic": None, "peak_source": which, "whole_step_frac": round((n + M) * steps / t_dev / 1e9 / peak, 4),
+        "roofline": {"bound": "hbm", "kernel": top, "kernels": STAGE_KERNELS.get(top, top), "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
+                     "traffic": ncu_traffic(top, n), "peak_source": which, "whole_step_frac": round((n + M) * steps / t_dev / 1e9 / peak, 4),
                      "stages": stages, "launch_ms": per_kernel},
     }
 

@@ -153,7 +153,8 @@ __global__ void __launch_bounds__(256) k_tilebits2(const uint8_t* __restrict__ i
                                                    const SegD* __restrict__ segs, const uint32_t* __restrict__ tile_seg,
                                                    const MbModel* __restrict__ models, const uint8_t* __restrict__ role,
                                                    const uint32_t* __restrict__ ins_at, const Cmd* __restrict__ cmds,
-                                                   const uint32_t* __restrict__ tile_model, uint32_t* __restrict__ tile_bits, Params P) {
+                                                   const uint32_t* __restrict__ tile_model, uint32_t* __restrict__ tile_bits,
+                                                   uint32_t* __restrict__ warp_base, uint16_t* __restrict__ thr_off, Params P) {
   __shared__ uint32_t s_w[8][3];
   __shared__ uint32_t s_sum[8];
   __shared__ TileModel s_T;
@@ -176,10 +177,19 @@ __global__ void __launch_bounds__(256) k_tilebits2(const uint8_t* __restrict__ i
     bits += t.n[0] + t.n[1] + t.n[2] + t.n[3];
     R.il += r & 1; R.ic += (r >> 2) & 1; R.id += (r >> 4) & 1;
   }
-  for (int o = 16; o; o >>= 1) bits += __shfl_xor_sync(0xffffffffu, bits, o);
-  if ((threadIdx.x & 31) == 0) s_sum[threadIdx.x >> 5] = bits;
+  // bit offset of the thread inside its warp (u16: 128 positions hold < 64 Ki bits) and of the warp inside
+  // the tile: k_write2 then knows where every thread writes before it computes a single token
+  uint32_t incl = bits;
+  for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o); if ((threadIdx.x & 31) >= (uint32_t)o) incl += y; }
+  thr_off[(size_t)tile * 256 + threadIdx.x] = (uint16_t)(incl - bits);
+  if ((threadIdx.x & 31) == 31) s_sum[threadIdx.x >> 5] = incl;
   __syncthreads();
-  if (threadIdx.x == 0) { uint32_t s = 0; for (int i = 0; i < 8; i++) s += s_sum[i]; tile_bits[tile] = s; }
+  if (threadIdx.x < 8) {
+    uint32_t base = 0;
+    for (uint32_t i = 0; i < threadIdx.x; i++) base += s_sum[i];
+    warp_base[(size_t)tile * 8 + threadIdx.x] = base;
+    if (threadIdx.x == 7) tile_bits[tile] = base + s_sum[7];
+  }
 }
 
 // atomicOr-copy of `nbits` bits from src (bit 0 of word 0 first) to bit position `pos` of w.
@@ -265,10 +275,10 @@ __global__ void __launch_bounds__(256) k_write2(const uint8_t* __restrict__ in, 
                                                 const MbModel* __restrict__ models, const uint8_t* __restrict__ role,
                                                 const uint32_t* __restrict__ ins_at, const Cmd* __restrict__ cmds,
                                                 const uint32_t* __restrict__ tile_model, const uint32_t* __restrict__ tile_bits,
-                                                const uint32_t* __restrict__ tile_off, uint8_t* __restrict__ out, Params P) {
+                                                const uint32_t* __restrict__ tile_off, const uint32_t* __restrict__ warp_base,
+                                                const uint16_t* __restrict__ thr_off, uint8_t* __restrict__ out, Params P) {
   __shared__ uint32_t s_stage[STAGE_WORDS];
   __shared__ uint32_t s_w[8][3];
-  __shared__ uint32_t s_warp[8];
   __shared__ TileModel s_T;
   const uint32_t tile = blockIdx.x;
   const uint32_t total = tile_bits[tile];
@@ -287,33 +297,21 @@ __global__ void __launch_bounds__(256) k_write2(const uint8_t* __restrict__ in, 
   const uint32_t tile_end = min(sg.rel_pos + sg.len, tile_rel + TILE);
   tile_model_load(M, tile, tile_model, trivial, s_T);
   TileRanks R = tile_ranks(M, tile, sh, tile_rel, tile_end, role, cmds, P.sh, s_w);   // contains a __syncthreads
-  Tok4 tk[4]; uint32_t mine = 0;
-#pragma unroll
-  for (int k = 0; k < 4; k++) {
-    const uint32_t r = R.r[k];
-#pragma unroll
-    for (int f = 0; f < 4; f++) { tk[k].n[f] = 0; tk[k].v[f] = 0; }
-    if (r) {
-      const uint64_t p = sh.in_off + tile_rel + 4 * tid + k;
-      tk[k] = position_tokens2(in, p, r, ins_at, cmds, M, R.il, R.ic, R.id, P.sh, trivial, s_T);
-      R.il += r & 1; R.ic += (r >> 2) & 1; R.id += (r >> 4) & 1;
-    }
-    mine += tk[k].n[0] + tk[k].n[1] + tk[k].n[2] + tk[k].n[3];
-  }
-  uint32_t incl = mine;
-  for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o); if ((tid & 31) >= (uint32_t)o) incl += y; }
-  if ((tid & 31) == 31) s_warp[tid >> 5] = incl;
-  __syncthreads();
-  uint32_t wbase = 0;
-  for (uint32_t i = 0; i < (tid >> 5); i++) wbase += s_warp[i];
-  uint32_t bitpos = head + wbase + incl - mine;
+  // the thread's bit offset comes from k_tilebits2, so each position's tokens are packed as soon as they
+  // are known: no token array, no second scan (80 -> fewer registers, more resident CTAs)
+  uint32_t bitpos = head + warp_base[(size_t)tile * 8 + (tid >> 5)] + thr_off[(size_t)tile * 256 + tid];
   uint32_t* gw = reinterpret_cast<uint32_t*>(out + sh.out_off) + (off >> 5);
 #pragma unroll
   for (int k = 0; k < 4; k++) {
+    const uint32_t r = R.r[k];
+    if (!r) continue;
+    const uint64_t p = sh.in_off + tile_rel + 4 * tid + k;
+    const Tok4 t = position_tokens2(in, p, r, ins_at, cmds, M, R.il, R.ic, R.id, P.sh, trivial, s_T);
+    R.il += r & 1; R.ic += (r >> 2) & 1; R.id += (r >> 4) & 1;
 #pragma unroll
     for (int f = 0; f < 4; f++) {
-      if (staged) sput(s_stage, bitpos, tk[k].n[f], tk[k].v[f]); else sput(gw, bitpos, tk[k].n[f], tk[k].v[f]);
-      bitpos += tk[k].n[f];
+      if (staged) sput(s_stage, bitpos, t.n[f], t.v[f]); else sput(gw, bitpos, t.n[f], t.v[f]);
+      bitpos += t.n[f];
     }
   }
   if (!staged) return;

@@ -56,24 +56,27 @@ __device__ __forceinline__ float flog2(float v) { return __log2f(v); }
 // alpha is a multiple of 4 and <= 768, rows are 16-byte aligned: every lane fetches its (up to 6)
 // 16-byte pieces of both rows up front, so a pair evaluation costs ONE L2 round trip instead of
 // alpha / 32 dependent ones (profiles/r1i: k_cluster_final was 34 % of the q5 step, latency bound).
+// NV = 16-byte pieces per lane: 2 covers alpha <= 256 (literal histograms), 6 covers alpha <= 768; the narrow
+// form keeps the kernels that only see literal problems at a third of the row registers.
+template <bool SHARED = false, int NV = 6>
 __device__ __forceinline__ float hist_cost(const uint32_t* a, const uint32_t* b, int alpha, uint32_t* total_out) {
   const uint32_t lane = threadIdx.x & 31;
   const int nvec = alpha >> 2;
   const uint4* a4 = reinterpret_cast<const uint4*>(a);
   const uint4* b4 = reinterpret_cast<const uint4*>(b);
-  uint4 v[6];
+  uint4 v[NV];
 #pragma unroll
-  for (int t = 0; t < 6; t++) {
+  for (int t = 0; t < NV; t++) {
     const int i = t * 32 + (int)lane;
     v[t] = make_uint4(0, 0, 0, 0);
     if (i < nvec) {
-      v[t] = __ldcg(a4 + i);
-      if (b) { const uint4 y = __ldcg(b4 + i); v[t].x += y.x; v[t].y += y.y; v[t].z += y.z; v[t].w += y.w; }
+      v[t] = SHARED ? a4[i] : __ldcg(a4 + i);
+      if (b) { const uint4 y = SHARED ? b4[i] : __ldcg(b4 + i); v[t].x += y.x; v[t].y += y.y; v[t].z += y.z; v[t].w += y.w; }
     }
   }
   float ent = 0.f; uint32_t tot = 0, nnz = 0, runs = 0, carry = 1;
 #pragma unroll
-  for (int t = 0; t < 6; t++) {
+  for (int t = 0; t < NV; t++) {
     if (t * 32 < nvec) {
       const uint4 x = v[t];
       tot += x.x + x.y + x.z + x.w;
@@ -109,7 +112,13 @@ __device__ __forceinline__ float cluster_cost_diff(float a, float b) { const flo
 // grid (max batches, problems), 256 threads.  mode 0: first round (list = identity, costs computed
 // here); mode 1: later rounds over p.list.  Merges while the best pair improves the cost, then —
 // if the batch still holds more than `target` clusters — merges the cheapest pairs regardless.
-__global__ void __launch_bounds__(256) k_cluster_batch(const ClusterProb* __restrict__ probs, int mode) {
+// When the batch's 64 rows fit the dynamic shared memory given at launch (alpha <= 256: literal context
+// maps and literal block histograms), they are staged there and every pair evaluation and merge works on
+// shared memory; the survivors' rows are written back at the end.  profiles/r1k: the global-memory form
+// is bound by one L2 round trip per pair evaluation (2016 + ~63 * 62 of them per batch).
+template <int NV>
+__global__ void __launch_bounds__(256) k_cluster_batch(const ClusterProb* __restrict__ probs, int mode, uint32_t smem_bytes) {
+  extern __shared__ __align__(16) uint32_t s_rows[];   // [CL_BATCH][alpha] when staged
   __shared__ float s_d[CL_BATCH][CL_BATCH];      // costDiff of pair (i < j) at [i][j]
   __shared__ float s_c[CL_BATCH][CL_BATCH];      // combined cost of the pair
   __shared__ uint32_t s_idx[CL_BATCH];           // cluster index of slot i
@@ -119,6 +128,7 @@ __global__ void __launch_bounds__(256) k_cluster_batch(const ClusterProb* __rest
   __shared__ float s_rv[8]; __shared__ int s_ri[8];
   __shared__ int s_best;
   const ClusterProb p = probs[blockIdx.y];
+  if ((p.alpha > 256) != (NV > 2)) return;                 // the other instantiation's problem
   const uint32_t live = mode == 0 ? p.m : p.state[0];
   if (mode == 1 && live <= CL_FINAL_MAX) return;           // the final round takes over
   const uint32_t b0 = blockIdx.x * CL_BATCH;
@@ -127,6 +137,7 @@ __global__ void __launch_bounds__(256) k_cluster_batch(const ClusterProb* __rest
   const uint32_t target = mode == 0 ? CL_BATCH : p.state[1];
   const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   const uint32_t* src_list = mode == 0 ? nullptr : p.list;
+  const bool staged = (size_t)p.alpha * CL_BATCH * 4 <= smem_bytes;
   if (tid < CL_BATCH) {
     s_live[tid] = tid < n;
     if (tid < n) {
@@ -140,10 +151,16 @@ __global__ void __launch_bounds__(256) k_cluster_batch(const ClusterProb* __rest
     // out[i] = in[i]; bitCost = cost (cluster.ts:336-341)
     for (uint32_t i = w; i < n; i += 8) {
       const uint32_t ci = s_idx[i];
-      const uint32_t* a = p.in + (size_t)ci * p.stride; uint32_t* o = p.work + (size_t)ci * p.stride;
+      const uint32_t* a = p.in + (size_t)ci * p.stride; uint32_t* o = staged ? s_rows + (size_t)i * p.alpha : p.work + (size_t)ci * p.stride;
       for (uint32_t k = lane; k < p.alpha; k += 32) o[k] = a[k];
-      uint32_t t; const float c = hist_cost(a, nullptr, (int)p.alpha, &t);
+      uint32_t t; const float c = hist_cost<false, NV>(a, nullptr, (int)p.alpha, &t);
       if (lane == 0) { s_cost[i] = c; s_tot[i] = t; s_size[i] = 1; p.alias[ci] = ci; }
+    }
+    __syncthreads();
+  } else if (staged) {
+    for (uint32_t i = w; i < n; i += 8) {
+      const uint32_t* a = p.work + (size_t)s_idx[i] * p.stride; uint32_t* o = s_rows + (size_t)i * p.alpha;
+      for (uint32_t k = lane; k < p.alpha; k += 32) o[k] = __ldcg(a + k);
     }
     __syncthreads();
   }
@@ -152,7 +169,8 @@ __global__ void __launch_bounds__(256) k_cluster_batch(const ClusterProb* __rest
     float combo;
     if (s_tot[i] == 0) combo = s_cost[j];
     else if (s_tot[j] == 0) combo = s_cost[i];
-    else combo = hist_cost(p.work + (size_t)s_idx[i] * p.stride, p.work + (size_t)s_idx[j] * p.stride, (int)p.alpha, nullptr);
+    else if (staged) combo = hist_cost<true, NV>(s_rows + (size_t)i * p.alpha, s_rows + (size_t)j * p.alpha, (int)p.alpha, nullptr);
+    else combo = hist_cost<false, NV>(p.work + (size_t)s_idx[i] * p.stride, p.work + (size_t)s_idx[j] * p.stride, (int)p.alpha, nullptr);
     if (lane == 0) {
       s_c[i][j] = combo;
       s_d[i][j] = 0.5f * cluster_cost_diff((float)s_size[i], (float)s_size[j]) - s_cost[i] - s_cost[j] + combo;
@@ -191,7 +209,10 @@ __global__ void __launch_bounds__(256) k_cluster_batch(const ClusterProb* __rest
     if (best < 0) break;
     const uint32_t i = (uint32_t)best / n, j = (uint32_t)best % n;
     // merge j into i (cluster.ts:170-176)
-    {
+    if (staged) {
+      uint32_t* a = s_rows + (size_t)i * p.alpha; const uint32_t* b = s_rows + (size_t)j * p.alpha;
+      for (uint32_t k = tid; k < p.alpha; k += 256) a[k] += b[k];
+    } else {
       uint32_t* a = p.work + (size_t)s_idx[i] * p.stride; const uint32_t* b = p.work + (size_t)s_idx[j] * p.stride;
       for (uint32_t k = tid; k < p.alpha; k += 256) a[k] = __ldcg(a + k) + __ldcg(b + k);
     }
@@ -210,6 +231,13 @@ __global__ void __launch_bounds__(256) k_cluster_batch(const ClusterProb* __rest
     __syncthreads();
   }
   // survivors of this batch, in slot order
+  if (staged) {
+    for (uint32_t i = w; i < n; i += 8) {
+      if (!s_live[i]) continue;
+      uint32_t* o = p.work + (size_t)s_idx[i] * p.stride; const uint32_t* a = s_rows + (size_t)i * p.alpha;
+      for (uint32_t k = lane; k < p.alpha; k += 32) o[k] = a[k];
+    }
+  }
   if (tid == 0) {
     uint32_t cnt = 0;
     for (uint32_t k = 0; k < n; k++)
@@ -341,18 +369,33 @@ __global__ void __launch_bounds__(512) k_cluster_final(const ClusterProb* __rest
 //   + g(Tc + Th) - g(Tc),   f(p) = -p log2 p, g(T) = T log2 T.
 // The input row stays in registers (<= 6 x 16 bytes per lane); every cluster row is fetched with all
 // its 16-byte pieces in flight at once.
-__global__ void __launch_bounds__(256) k_cluster_remap(const ClusterProb* __restrict__ probs) {
+// When the final clusters' rows fit the dynamic shared memory (<= 64 clusters of <= 256 bins: every literal
+// context map) the CTA stages them once and its 64 inputs are measured against shared memory.
+template <int NV>
+__global__ void __launch_bounds__(256) k_cluster_remap(const ClusterProb* __restrict__ probs, uint32_t smem_bytes) {
+  extern __shared__ __align__(16) uint32_t s_cl[];   // [ncl][alpha] when staged
   const ClusterProb p = probs[blockIdx.y];
+  if ((p.alpha > 256) != (NV > 2)) return;
   const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5;
-  const uint32_t i0 = blockIdx.x * 64 + w * 8;
-  if (i0 >= p.m) return;
+  if (blockIdx.x * 64 >= p.m) return;
   const uint32_t ncl = p.state[2];
   const int nvec = (int)p.alpha >> 2;
+  const bool staged = (size_t)ncl * p.alpha * 4 <= smem_bytes;
+  if (staged) {
+    for (uint32_t c = w; c < ncl; c += 8) {
+      const uint4* src = reinterpret_cast<const uint4*>(p.work + (size_t)p.list2[c] * p.stride);
+      uint4* dst = reinterpret_cast<uint4*>(s_cl + (size_t)c * p.alpha);
+      for (int k = (int)lane; k < nvec; k += 32) dst[k] = __ldcg(src + k);
+    }
+    __syncthreads();
+  }
+  const uint32_t i0 = blockIdx.x * 64 + w * 8;
+  if (i0 >= p.m) return;
   for (uint32_t i = i0; i < min(p.m, i0 + 8); i++) {
     const uint4* h4 = reinterpret_cast<const uint4*>(p.in + (size_t)i * p.stride);
-    uint4 hv[6]; uint32_t th = 0;
+    uint4 hv[NV]; uint32_t th = 0;
 #pragma unroll
-    for (int t = 0; t < 6; t++) {
+    for (int t = 0; t < NV; t++) {
       const int k = t * 32 + (int)lane;
       hv[t] = k < nvec ? h4[k] : make_uint4(0, 0, 0, 0);
       th += hv[t].x + hv[t].y + hv[t].z + hv[t].w;
@@ -365,13 +408,16 @@ __global__ void __launch_bounds__(256) k_cluster_remap(const ClusterProb* __rest
       while (true) { const uint32_t a = p.alias[cur]; if (a == cur) break; cur = a; }
       for (uint32_t c = 0; c < ncl; c++) {
         const uint32_t ci = p.list2[c];
-        const uint4* o4 = reinterpret_cast<const uint4*>(p.work + (size_t)ci * p.stride);
-        uint4 ov[6];
+        const uint4* o4 = staged ? reinterpret_cast<const uint4*>(s_cl + (size_t)c * p.alpha) : reinterpret_cast<const uint4*>(p.work + (size_t)ci * p.stride);
+        uint4 ov[NV];
 #pragma unroll
-        for (int t = 0; t < 6; t++) { const int k = t * 32 + (int)lane; ov[t] = (k < nvec && (hv[t].x | hv[t].y | hv[t].z | hv[t].w)) ? __ldcg(o4 + k) : make_uint4(0, 0, 0, 0); }
+        for (int t = 0; t < NV; t++) {
+          const int k = t * 32 + (int)lane;
+          ov[t] = (k < nvec && (hv[t].x | hv[t].y | hv[t].z | hv[t].w)) ? (staged ? o4[k] : __ldcg(o4 + k)) : make_uint4(0, 0, 0, 0);
+        }
         float d = 0.f;
 #pragma unroll
-        for (int t = 0; t < 6; t++) {
+        for (int t = 0; t < NV; t++) {
           const uint32_t xs[4] = {hv[t].x, hv[t].y, hv[t].z, hv[t].w}, os[4] = {ov[t].x, ov[t].y, ov[t].z, ov[t].w};
 #pragma unroll
           for (int q = 0; q < 4; q++) {
@@ -581,8 +627,18 @@ __global__ void __launch_bounds__(256) k_split_acc(const SplitProb* __restrict__
         if (lane * 4 + 4 <= cnt && ((reinterpret_cast<uintptr_t>(d) & 3) == 0)) wv = *reinterpret_cast<const uint32_t*>(d + lane * 4);
         else for (uint32_t b = 0; b < 4 && lane * 4 + b < cnt; b++) wv |= (uint32_t)d[lane * 4 + b] << (8 * b);
       }
-#pragma unroll 8
-      for (uint32_t i = 0; i < cnt; i++) {
+      // 4 symbols (one shuffled word) per step: their table entries are summed as half2 (each <= 60000 by
+      // construction; four real costs stay far below the half range and lose < 1/16 bit) and widened once
+      const uint32_t cnt4 = cnt & ~3u;
+#pragma unroll 4
+      for (uint32_t i = 0; i < cnt4; i += 4) {
+        const uint32_t w4 = __shfl_sync(0xffffffffu, wv, i >> 2);
+        const __half2 h = __hadd2(__hadd2(ic2[(w4 & 0xFF) * (SPLIT_MAXK / 2) + lane], ic2[((w4 >> 8) & 0xFF) * (SPLIT_MAXK / 2) + lane]),
+                                  __hadd2(ic2[((w4 >> 16) & 0xFF) * (SPLIT_MAXK / 2) + lane], ic2[(w4 >> 24) * (SPLIT_MAXK / 2) + lane]));
+        const float2 f = __half22float2(h);
+        a0 += f.x; a1 += f.y;
+      }
+      for (uint32_t i = cnt4; i < cnt; i++) {
         const uint32_t sym = (__shfl_sync(0xffffffffu, wv, i >> 2) >> ((i & 3) * 8)) & 0xFF;
         const float2 f = __half22float2(ic2[sym * (SPLIT_MAXK / 2) + lane]);
         a0 += f.x; a1 += f.y;
@@ -591,15 +647,16 @@ __global__ void __launch_bounds__(256) k_split_acc(const SplitProb* __restrict__
       const uint16_t* d = reinterpret_cast<const uint16_t*>(p.data) + sb;
       const uint32_t mine = lane < cnt ? d[lane] : 0;
       if (cnt == 16) {
-        // full granule: all 16 table rows in flight at once, two partial sums
-        float b0 = 0.f, b1 = 0.f;
+        // full granule: all 16 table rows in flight at once; groups of 4 summed as half2, widened once each
 #pragma unroll
-        for (uint32_t i = 0; i < 16; i += 2) {
+        for (uint32_t i = 0; i < 16; i += 4) {
           const uint32_t s0 = __shfl_sync(0xffffffffu, mine, i), s1 = __shfl_sync(0xffffffffu, mine, i + 1);
-          const float2 f = __half22float2(ic2[s0 * (SPLIT_MAXK / 2) + lane]), g = __half22float2(ic2[s1 * (SPLIT_MAXK / 2) + lane]);
-          a0 += f.x; a1 += f.y; b0 += g.x; b1 += g.y;
+          const uint32_t s2 = __shfl_sync(0xffffffffu, mine, i + 2), s3 = __shfl_sync(0xffffffffu, mine, i + 3);
+          const __half2 h = __hadd2(__hadd2(ic2[s0 * (SPLIT_MAXK / 2) + lane], ic2[s1 * (SPLIT_MAXK / 2) + lane]),
+                                    __hadd2(ic2[s2 * (SPLIT_MAXK / 2) + lane], ic2[s3 * (SPLIT_MAXK / 2) + lane]));
+          const float2 f = __half22float2(h);
+          a0 += f.x; a1 += f.y;
         }
-        a0 += b0; a1 += b1;
       } else {
         for (uint32_t i = 0; i < cnt; i++) {
           const uint32_t sym = __shfl_sync(0xffffffffu, mine, i);
