@@ -82,7 +82,10 @@ struct Job {
 };
 
 constexpr size_t IN_PAD = 1024;
-constexpr int PARSE_G = 8;   // lanes per parse segment (kernels.cuh k_parse)
+#ifndef PARSE_G_BUILD
+#define PARSE_G_BUILD 8
+#endif
+constexpr int PARSE_G = PARSE_G_BUILD;   // lanes per parse segment (kernels.cuh k_parse)
 
 }  // namespace
 

@@ -89,6 +89,38 @@ __global__ void __launch_bounds__(256) k_ctx_zero(const MbModel* __restrict__ mo
   for (size_t i = first; i < (size_t)MAX_CTX_CLUSTERS * ALPHA_DIST_MAX; i += step) M.cl_hist[DIST][i] = 0;
 }
 
+// Literal histograms of a chunk that lies inside ONE block (the common case): counted in a CTA-private
+// [64 contexts][256 bytes] table of 16-bit counters in shared memory and flushed with one global atomic
+// per non-zero counter.  The plain per-symbol global atomics below pile up on the few hot (context, byte)
+// pairs of a text block (tens of thousands of increments of one address per metablock).
+// grid (chunks of 4096 literals, metablocks).  Chunks that span a block boundary are left to k_ctx_hist.
+__global__ void __launch_bounds__(256) k_ctx_hist_lit(const MbModel* __restrict__ models) {
+  __shared__ uint32_t s_h[64 * 256 / 2];   // two 16-bit counters per word: a chunk holds <= 4096 symbols
+  const MbModel& M = models[blockIdx.y];
+  const uint32_t n = M.cnt[LIT];
+  const uint32_t i0 = blockIdx.x * 4096;
+  if (i0 >= n) return;
+  const uint32_t i1 = min(n, i0 + 4096);
+  const uint16_t* sb = M.sym_blk[LIT];
+  const uint32_t b0 = sb[i0];
+  if (b0 != sb[i1 - 1]) return;            // not uniform: k_ctx_hist counts this chunk
+  const bool trivial = M.cnt[4] != 0;
+  const uint32_t t = M.blk_type[LIT][b0];
+  for (uint32_t i = threadIdx.x; i < 64 * 256 / 2; i += 256) s_h[i] = 0;
+  __syncthreads();
+  for (uint32_t i = i0 + threadIdx.x; i < i1; i += 256) {
+    const uint32_t idx = (trivial ? 0u : (uint32_t)M.clctx[i]) * 256 + M.clit[i];
+    atomicAdd(&s_h[idx >> 1], 1u << (16 * (idx & 1)));
+  }
+  __syncthreads();
+  uint32_t* h = M.ctx_hist[LIT] + (size_t)(trivial ? 0 : t * 64) * 256;
+  for (uint32_t i = threadIdx.x; i < 64 * 256 / 2; i += 256) {
+    const uint32_t v = s_h[i];
+    if (v & 0xFFFFu) atomicAdd(&h[2 * i], v & 0xFFFFu);
+    if (v >> 16) atomicAdd(&h[2 * i + 1], v >> 16);
+  }
+}
+
 // metablock.ts:558-637 in rank space.  grid (chunks of 4096 symbols, metablocks * 3).
 __global__ void __launch_bounds__(256) k_ctx_hist(const MbModel* __restrict__ models) {
   const MbModel& M = models[blockIdx.y / 3];
@@ -96,6 +128,7 @@ __global__ void __launch_bounds__(256) k_ctx_hist(const MbModel* __restrict__ mo
   const uint32_t n = M.cnt[cat];
   const uint32_t i0 = blockIdx.x * 4096;
   if (i0 >= n) return;
+  if (cat == LIT && M.sym_blk[LIT][i0] == M.sym_blk[LIT][min(n, i0 + 4096) - 1]) return;   // k_ctx_hist_lit took it
   const bool trivial = M.cnt[4] != 0;
   const uint8_t* bt = M.blk_type[cat]; const uint16_t* sb = M.sym_blk[cat];
   uint32_t* h = M.ctx_hist[cat];
