@@ -692,10 +692,20 @@ __global__ void __launch_bounds__(128) k_split_dp(const SplitProb* __restrict__ 
   const uint32_t gbeg = chunk * SPLIT_CHUNK, gend = min(G, gbeg + SPLIT_CHUNK);
   float c0 = 0.f, c1 = 0.f;   // codes 2*lane, 2*lane+1
   const __half2* acc2 = reinterpret_cast<const __half2*>(p.acc);
-  __half2 nxt = acc2[(size_t)gbeg * (SPLIT_MAXK / 2) + lane];
-  for (uint32_t g = gbeg; g < gend; g++) {
-    const float2 f = __half22float2(nxt);
-    if (g + 1 < gend) nxt = acc2[(size_t)(g + 1) * (SPLIT_MAXK / 2) + lane];
+  // The chain of a chunk is one dependent step per granule; its per-granule costs are prefetched SPLIT_PF
+  // granules ahead into a register ring, so no step waits for memory (one step ahead left an L2 round trip
+  // of ~700 cycles on every step of a ~150-cycle ALU chain: 1.3 ms per launch for the 16-symbol granules).
+  constexpr int SPLIT_PF = 8;
+  __half2 ring[SPLIT_PF];
+#pragma unroll
+  for (int k = 0; k < SPLIT_PF; k++) ring[k] = gbeg + k < gend ? acc2[(size_t)(gbeg + k) * (SPLIT_MAXK / 2) + lane] : __half2();
+  for (uint32_t g0 = gbeg; g0 < gend; g0 += SPLIT_PF) {
+#pragma unroll
+    for (int k = 0; k < SPLIT_PF; k++) {
+    const uint32_t g = g0 + k;
+    if (g >= gend) break;
+    const float2 f = __half22float2(ring[k]);
+    if (g + SPLIT_PF < gend) ring[k] = acc2[(size_t)(g + SPLIT_PF) * (SPLIT_MAXK / 2) + lane];
     c0 += f.x; c1 += f.y;
     // warp arg-min (costs are >= 0, so the float order is the order of the bit patterns)
     const float m = fminf(c0, c1);
@@ -714,6 +724,7 @@ __global__ void __launch_bounds__(128) k_split_dp(const SplitProb* __restrict__ 
     const uint32_t e0 = __ballot_sync(0xffffffffu, s0), e1 = __ballot_sync(0xffffffffu, s1);
     // switch bit of code 2l is bit l of e0, of code 2l + 1 bit l of e1
     if (lane == 0) { s_sw[g - gbeg] = make_uint2(e0, e1); s_gid[g - gbeg] = (uint8_t)first; }
+  }
   }
   __syncwarp();
   // trace back (:194-209) in shared memory, then one coalesced store of the chunk's ids
