@@ -179,3 +179,19 @@ def test_lanes_stream_identical_to_single_lane(gpu_ctx, quality, mode, lanes, gr
         assert rc == _lib.E_OUTPUT_TOO_SMALL and ln.value == len(ref)
     finally:
         gpu_ctx.set_tuning()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("quality", [5, 9])
+def test_default_lanes_with_ramped_groups_identical_to_single_lane(gpu_ctx, quality):
+    """Library defaults: 4 lanes, groups growing from 0.6x to 1.4x the mean (lanes_host.inc)."""
+    data = np.concatenate([W.text(150000, 31), W.records(150000, 32), W.text(101234, 33)]).tobytes()   # 49 shards of 8 KiB
+    try:
+        gpu_ctx.set_tuning(shard_bytes=8192, lanes=1)
+        ref = gpu_ctx.encode(data, quality, 22, 0)
+        gpu_ctx.set_tuning(shard_bytes=8192)
+        s = gpu_ctx.encode(data, quality, 22, 0)
+        assert s == ref
+        assert O.decode(s, len(data)) == data
+    finally:
+        gpu_ctx.set_tuning()
