@@ -128,11 +128,31 @@ __global__ void __launch_bounds__(256) k_ctx_hist(const MbModel* __restrict__ mo
   const uint32_t n = M.cnt[cat];
   const uint32_t i0 = blockIdx.x * 4096;
   if (i0 >= n) return;
-  if (cat == LIT && M.sym_blk[LIT][i0] == M.sym_blk[LIT][min(n, i0 + 4096) - 1]) return;   // k_ctx_hist_lit took it
+  const uint32_t i1 = min(n, i0 + 4096);
+  const uint16_t* sb = M.sym_blk[cat];
+  const bool uniform = sb[i0] == sb[i1 - 1];
+  if (cat == LIT && uniform) return;   // k_ctx_hist_lit took it
   const bool trivial = M.cnt[4] != 0;
-  const uint8_t* bt = M.blk_type[cat]; const uint16_t* sb = M.sym_blk[cat];
+  const uint8_t* bt = M.blk_type[cat];
   uint32_t* h = M.ctx_hist[cat];
-  for (uint32_t i = i0 + threadIdx.x; i < min(n, i0 + 4096); i += 256) {
+  if (uniform) {
+    // command / distance chunk inside one block: CTA-private counters (704, or 4 contexts x 128), one global
+    // atomic per non-zero counter — the command alphabet has a handful of very hot symbols
+    __shared__ uint32_t s_h[ALPHA_CMD > 4 * ALPHA_DIST_MAX ? ALPHA_CMD : 4 * ALPHA_DIST_MAX];
+    const uint32_t rows = cat == CMD ? ALPHA_CMD : 4 * ALPHA_DIST_MAX;
+    for (uint32_t i = threadIdx.x; i < rows; i += 256) s_h[i] = 0;
+    __syncthreads();
+    for (uint32_t i = i0 + threadIdx.x; i < i1; i += 256) {
+      if (cat == CMD) atomicAdd(&s_h[M.csym[i]], 1u);
+      else atomicAdd(&s_h[(trivial ? 0u : (uint32_t)M.ddctx[i]) * ALPHA_DIST_MAX + M.dsym[i]], 1u);
+    }
+    __syncthreads();
+    const uint32_t t = bt[sb[i0]];
+    uint32_t* hb = cat == CMD ? h + (size_t)t * ALPHA_CMD : h + (size_t)(trivial ? 0 : t * 4) * ALPHA_DIST_MAX;
+    for (uint32_t i = threadIdx.x; i < rows; i += 256) { const uint32_t v = s_h[i]; if (v) atomicAdd(&hb[i], v); }
+    return;
+  }
+  for (uint32_t i = i0 + threadIdx.x; i < i1; i += 256) {
     const uint32_t t = bt[sb[i]];
     if (cat == LIT) atomicAdd(&h[((size_t)(trivial ? 0 : t * 64 + M.clctx[i])) * 256 + M.clit[i]], 1u);
     else if (cat == CMD) atomicAdd(&h[(size_t)t * ALPHA_CMD + M.csym[i]], 1u);
