@@ -55,6 +55,20 @@ __constant__ uint8_t c_ctx_lut[2048];   // context.ts:12-162 (filled by the host
 
 __device__ __forceinline__ bool cmd_has_dist(uint32_t role, uint32_t cmdPrefix) { return (role & 2) && cmdPrefix >= 128; }
 
+// Roles of 4 consecutive positions as ONE aligned 32-bit load (shards are 256-byte aligned, tiles start at
+// multiples of 1024) and the command prefixes of the copy starts among them fetched together rather than
+// one dependent pair after the other.  Positions at or beyond tile_end read as role 0.
+__device__ __forceinline__ void load_roles4(const uint8_t* __restrict__ role, const Cmd* __restrict__ cmds, uint64_t p0, uint32_t rel0,
+                                            uint32_t tile_end, int shft, uint32_t r[4], uint32_t pre[4]) {
+  uint32_t r4 = rel0 < tile_end ? *reinterpret_cast<const uint32_t*>(role + p0) : 0u;
+  if (rel0 + 4 > tile_end && rel0 < tile_end) r4 &= (1u << (8 * (tile_end - rel0))) - 1u;   // ragged last tile of a segment
+#pragma unroll
+  for (int k = 0; k < 4; k++) {
+    r[k] = (r4 >> (8 * k)) & 0xFFu;
+    pre[k] = (r[k] & 2) ? cmds[(p0 + k) >> shft].cmdPrefix : 0u;
+  }
+}
+
 // ---------------------------------------------------------------------------------------
 // A.  Per-tile symbol counts.  grid = tiles, 256 threads (4 positions each).
 __global__ void __launch_bounds__(256) k_mb_counts(const ShardD* __restrict__ shards, const SegD* __restrict__ segs,
@@ -70,11 +84,12 @@ __global__ void __launch_bounds__(256) k_mb_counts(const ShardD* __restrict__ sh
   const uint32_t tile_rel = sg.rel_pos + (tile - sg.first_tile) * TILE;
   const uint32_t tile_end = min(sg.rel_pos + sg.len, tile_rel + TILE);
   uint32_t nl = 0, nc = 0, nd = 0;
-  for (uint32_t rel = tile_rel + threadIdx.x; rel < tile_end; rel += 256) {
-    const uint64_t p = sh.in_off + rel;
-    const uint32_t r = role[p];
-    nl += r & 1; nc += (r >> 2) & 1;
-    if ((r & 2) && cmds[p >> P.sh].cmdPrefix >= 128) nd++;
+  {
+    uint32_t r[4], pre[4];
+    const uint32_t rel0 = tile_rel + 4 * threadIdx.x;
+    load_roles4(role, cmds, sh.in_off + rel0, rel0, tile_end, P.sh, r, pre);
+#pragma unroll
+    for (int k = 0; k < 4; k++) { nl += r[k] & 1; nc += (r[k] >> 2) & 1; nd += cmd_has_dist(r[k], pre[k]) ? 1 : 0; }
   }
   for (int o = 16; o; o >>= 1) { nl += __shfl_xor_sync(0xffffffffu, nl, o); nc += __shfl_xor_sync(0xffffffffu, nc, o); nd += __shfl_xor_sync(0xffffffffu, nd, o); }
   if ((threadIdx.x & 31) == 0) { atomicAdd(&s_c[0], nl); atomicAdd(&s_c[1], nc); atomicAdd(&s_c[2], nd); }
@@ -151,17 +166,9 @@ __global__ void __launch_bounds__(256) k_mb_compact(const uint8_t* __restrict__ 
   __shared__ uint8_t lut[512];
   for (uint32_t i = tid; i < 512; i += 256) lut[i] = c_ctx_lut[(M.cnt[3] << 9) + i];
   uint32_t r[4], pre[4]; uint32_t nl = 0, nc = 0, nd = 0;
+  load_roles4(role, cmds, sh.in_off + tile_rel + 4 * tid, tile_rel + 4 * tid, tile_end, P.sh, r, pre);
 #pragma unroll
-  for (int k = 0; k < 4; k++) {
-    const uint32_t rel = tile_rel + 4 * tid + k;
-    r[k] = 0; pre[k] = 0;
-    if (rel < tile_end) {
-      const uint64_t p = sh.in_off + rel;
-      r[k] = role[p];
-      if (r[k] & 2) pre[k] = cmds[p >> P.sh].cmdPrefix;
-    }
-    nl += r[k] & 1; nc += (r[k] >> 2) & 1; nd += cmd_has_dist(r[k], pre[k]) ? 1 : 0;
-  }
+  for (int k = 0; k < 4; k++) { nl += r[k] & 1; nc += (r[k] >> 2) & 1; nd += cmd_has_dist(r[k], pre[k]) ? 1 : 0; }
   // block exclusive scan of the three counters (packed: 11 bits each is enough for 1024 positions)
   uint32_t packed = nl | (nc << 11) | (nd << 22), incl = packed;
   for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= (uint32_t)o) incl += y; }
