@@ -48,6 +48,7 @@ struct ClusterProb {
   uint32_t* state;        // [8]  0: live count, 1: round target (forced max per batch), 2: final cluster count, 3: batch survivors scratch base
   uint32_t* batch_cnt;    // [ceil(m / 64)] survivors per batch
   uint32_t m, alpha, stride, max_clusters;
+  uint32_t final_max;     // live clusters the all-pairs round accepts (<= CL_FINAL_MAX); the batch rounds merge down to it
 };
 
 __device__ __forceinline__ float flog2(float v) { return __log2f(v); }
@@ -130,7 +131,7 @@ __global__ void __launch_bounds__(256) k_cluster_batch(const ClusterProb* __rest
   const ClusterProb p = probs[blockIdx.y];
   if ((p.alpha > 256) != (NV > 2)) return;                 // the other instantiation's problem
   const uint32_t live = mode == 0 ? p.m : p.state[0];
-  if (mode == 1 && live <= CL_FINAL_MAX) return;           // the final round takes over
+  if (mode == 1 && live <= p.final_max) return;           // the final round takes over
   const uint32_t b0 = blockIdx.x * CL_BATCH;
   if (b0 >= live) return;
   const uint32_t n = min((uint32_t)CL_BATCH, live - b0);
@@ -255,7 +256,7 @@ __global__ void __launch_bounds__(256) k_cluster_batch(const ClusterProb* __rest
 __global__ void __launch_bounds__(32) k_cluster_gather(const ClusterProb* __restrict__ probs, int mode) {
   const ClusterProb p = probs[blockIdx.x];
   const uint32_t live = mode == 0 ? p.m : p.state[0];
-  if (mode == 1 && live <= CL_FINAL_MAX) return;
+  if (mode == 1 && live <= p.final_max) return;
   const uint32_t nb = (live + CL_BATCH - 1) / CL_BATCH;
   const uint32_t lane = threadIdx.x;
   uint32_t base = 0;
@@ -266,9 +267,9 @@ __global__ void __launch_bounds__(32) k_cluster_gather(const ClusterProb* __rest
   }
   if (lane == 0) {
     p.state[0] = base;
-    // next round: force every batch of 64 down far enough that <= ~224 clusters remain overall
+    // next round: force every batch of 64 down far enough that <= 7/8 of final_max clusters remain overall
     const uint32_t nb2 = (base + CL_BATCH - 1) / CL_BATCH;
-    p.state[1] = nb2 ? max(1u, 224u / nb2) : 1u;
+    p.state[1] = nb2 ? max(1u, (p.final_max - p.final_max / 8) / nb2) : 1u;
   }
 }
 
@@ -277,22 +278,28 @@ __global__ void __launch_bounds__(32) k_cluster_gather(const ClusterProb* __rest
 // sparse distance), rebuild the cluster histograms and reindex by first appearance (:278-314).
 // One CTA of 512 threads per problem; dynamic shared memory: 256 x 256 floats (pair matrix) + tables.
 constexpr uint32_t CL_FINAL_PAIRS = CL_FINAL_MAX * (CL_FINAL_MAX - 1) / 2;   // pair (i < j) at j (j - 1) / 2 + i
-constexpr uint32_t CL_FINAL_SMEM = CL_FINAL_PAIRS * 4 + CL_FINAL_MAX * (4 + 4 + 4 + 4 + 1) + 256;
+constexpr uint32_t cl_final_smem(uint32_t maxn) { return maxn * (maxn - 1) / 2 * 4 + maxn * (4 + 4 + 4 + 4 + 1) + 256; }
+constexpr uint32_t CL_FINAL_SMEM = cl_final_smem(CL_FINAL_MAX);
 __device__ __forceinline__ uint32_t tri(uint32_t i, uint32_t j) { return j * (j - 1) / 2 + i; }
 
+// MAXN = 256 for block clustering (up to 256 block types survive), 128 for context maps (at most 64 clusters
+// survive): a quarter of the pair matrix (32 KiB instead of 130 KiB of shared memory: two problems per SM
+// instead of one) and a quarter of the all-pairs evaluations.
+template <int MAXN>
 __global__ void __launch_bounds__(512) k_cluster_final(const ClusterProb* __restrict__ probs) {
+  constexpr uint32_t PAIRS = MAXN * (MAXN - 1) / 2;
   extern __shared__ __align__(16) uint8_t csm[];
   float* s_d = reinterpret_cast<float*>(csm);                       // triangular pair matrix
-  uint32_t* s_idx = reinterpret_cast<uint32_t*>(s_d + CL_FINAL_PAIRS);
-  float* s_cost = reinterpret_cast<float*>(s_idx + CL_FINAL_MAX);
-  uint32_t* s_tot = reinterpret_cast<uint32_t*>(s_cost + CL_FINAL_MAX);
-  uint32_t* s_size = s_tot + CL_FINAL_MAX;
-  uint8_t* s_live = reinterpret_cast<uint8_t*>(s_size + CL_FINAL_MAX);
+  uint32_t* s_idx = reinterpret_cast<uint32_t*>(s_d + PAIRS);
+  float* s_cost = reinterpret_cast<float*>(s_idx + MAXN);
+  uint32_t* s_tot = reinterpret_cast<uint32_t*>(s_cost + MAXN);
+  uint32_t* s_size = s_tot + MAXN;
+  uint8_t* s_live = reinterpret_cast<uint8_t*>(s_size + MAXN);
   __shared__ float s_rv[16]; __shared__ int s_ri[16]; __shared__ int s_best; __shared__ float s_combo;
   const ClusterProb p = probs[blockIdx.x];
   const uint32_t n = p.state[0];
   const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
-  if (n == 0 || n > CL_FINAL_MAX) { if (tid == 0) p.state[2] = 0; return; }
+  if (n == 0 || n > (uint32_t)MAXN) { if (tid == 0) p.state[2] = 0; return; }
   for (uint32_t k = tid; k < n; k += 512) {
     const uint32_t ci = p.list[k];
     s_idx[k] = ci; s_cost[k] = p.cost[ci]; s_tot[k] = p.total[ci]; s_size[k] = p.csize[ci]; s_live[k] = 1;

@@ -38,7 +38,7 @@ typedef struct bgpu_stream bgpu_stream;
  * parse unit per shard, bit-identical commands to src/encode/backward-references.ts:14-134). */
 typedef struct bgpu_tuning {
   uint32_t shard_bytes;     /* independent window, <= 4 MiB (default 4 MiB)      */
-  uint32_t segment_bytes;   /* greedy-parse unit inside a shard (default 16 KiB)                  */
+  uint32_t segment_bytes;   /* parse unit inside a shard (default 8 KiB for q5-9, 32 KiB for q10/11)  */
   uint32_t metablock_bytes; /* metablock size inside a shard (default = shard)                    */
   uint32_t flags;           /* BGPU_F_*                                                           */
   uint32_t lanes;           /* CUDA streams that encode groups of shards of one large input at once
