@@ -127,11 +127,18 @@ __global__ void __launch_bounds__(256) k_sort_scatter(const uint8_t* __restrict_
   const uint32_t base = tile * SORT_TILE;
   const uint8_t* sin = in + sh.in_off;
   uint32_t v[ROUNDS]; uint16_t rk[ROUNDS];
+  // all 16 loads of the thread first: the ranking rounds below are separated by __syncwarp, which keeps the
+  // compiler from hoisting a round's load above the previous round (r2i: long-scoreboard 15.5 per issue,
+  // issue active 26 %, one exposed global round trip per round)
+#pragma unroll
+  for (int r = 0; r < ROUNDS; r++) {
+    const uint32_t e = base + w * (SORT_TILE / 8) + r * 32 + lane;
+    v[r] = e < npos ? (PASS == 0 ? ld32u(sin, e) : __ldg(src_v + sh.in_off + e)) : 0;
+  }
 #pragma unroll
   for (int r = 0; r < ROUNDS; r++) {
     const uint32_t e = base + w * (SORT_TILE / 8) + r * 32 + lane;
     const bool valid = e < npos;
-    v[r] = valid ? (PASS == 0 ? ld32u(sin, e) : __ldg(src_v + sh.in_off + e)) : 0;
     const uint32_t d = valid ? sort_digit(v[r], bucket_bits, shift, nbits) : (0x10000u | lane);
     const uint32_t peers = __match_any_sync(0xffffffffu, d);
     const uint32_t before = __popc(peers & ((1u << lane) - 1));
@@ -244,13 +251,26 @@ __global__ void __launch_bounds__(256) k_probe_sorted(const uint8_t* __restrict_
   const uint32_t* sp = srt_pos + sh.in_off; const uint32_t* sv = srt_v + sh.in_off;
   const uint8_t* sin = in + sh.in_off;
   const uint32_t halo = (uint32_t)depth;  // multiple of 16, <= PROBE_HALO
-  for (uint32_t i = tid; i < PROBE_TILE + halo; i += 256) {
-    const int64_t g = (int64_t)g0 - halo + i;
-    const bool ok = g >= 0 && g < (int64_t)npos;
-    const uint32_t p = ok ? __ldg(sp + g) : 0;
-    s_p[i] = p;
-    s_v[i] = ok ? __ldg(sv + g) : 0;
-    s_x[i] = ok ? ld128u(sin, (uint64_t)p + 4) : make_uint4(0, 0, 0, 0);   // reads <= 24 bytes past p: inside the padded input
+  {
+    // staging in three sweeps so that the loads of all (up to 5) entries of a thread are in flight together:
+    // positions and key bytes, then the dependent 16 data bytes behind each position, then the stores
+    constexpr int NST = (PROBE_TILE + PROBE_HALO + 255) / 256;
+    uint32_t pp[NST], vv[NST]; uint4 xx[NST]; bool ok[NST];
+#pragma unroll
+    for (int t = 0; t < NST; t++) {
+      const uint32_t i = tid + 256 * t;
+      const int64_t g = (int64_t)g0 - halo + i;
+      ok[t] = i < PROBE_TILE + halo && g >= 0 && g < (int64_t)npos;
+      pp[t] = ok[t] ? __ldg(sp + g) : 0;
+      vv[t] = ok[t] ? __ldg(sv + g) : 0;
+    }
+#pragma unroll
+    for (int t = 0; t < NST; t++) xx[t] = ok[t] ? ld128u(sin, (uint64_t)pp[t] + 4) : make_uint4(0, 0, 0, 0);   // reads <= 24 bytes past p: inside the padded input
+#pragma unroll
+    for (int t = 0; t < NST; t++) {
+      const uint32_t i = tid + 256 * t;
+      if (i < PROBE_TILE + halo) { s_p[i] = pp[t]; s_v[i] = vv[t]; s_x[i] = xx[t]; }
+    }
   }
   __syncthreads();
   // lanes take entries 4 apart so that a warp's shared-memory reads stay spread over the banks
