@@ -95,7 +95,8 @@ struct bgpu_ctx {
   bgpu_tuning tune{0, 0, 0, 0, 0, 0};
   // lanes (lanes_host.inc): private sub-contexts that encode groups of shards concurrently
   std::vector<bgpu_ctx*> lanes; bool is_lane = false;
-  cudaEvent_t lane_ev = nullptr, fork_ev = nullptr;
+  cudaEvent_t lane_ev = nullptr, fork_ev = nullptr, h2d_ev = nullptr;
+  cudaStream_t copy_stream = nullptr;   // parent only: the groups' host->device copies, in group order
   uint32_t* h_sizes = nullptr; size_t h_sizes_cap = 0;   // pinned: shard sizes of the lane's current group
   uint8_t* pin = nullptr; size_t pin_cap = 0, pin_used = 0, pin_want = 0;   // pinned staging of descriptor uploads
   DBuf in, sa_pos, sa_v, sb_pos, sb_v, sort_hist, role, ins, cmds, out, shards, mbs, segs, tile_seg, seg_ncmd, seg_trail, hist, codes, tree_bits, tree_nbits,
@@ -454,6 +455,8 @@ void bgpu_ctx_destroy(bgpu_ctx* c) {
   c->lanes.clear();
   if (c->lane_ev) cudaEventDestroy(c->lane_ev);
   if (c->fork_ev) cudaEventDestroy(c->fork_ev);
+  if (c->h2d_ev) cudaEventDestroy(c->h2d_ev);
+  if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
   if (c->h_sizes) cudaFreeHost(c->h_sizes);
   if (c->pin) cudaFreeHost(c->pin);
   if (c->ev_ok) for (int i = 0; i <= bgpu_ctx::kMaxStages; i++) cudaEventDestroy(c->ev[i]);
