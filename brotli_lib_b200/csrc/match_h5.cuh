@@ -233,7 +233,10 @@ __device__ __forceinline__ uint32_t match_len16(const uint8_t* in, uint64_t a, u
 // whole warp paid for it).  Candidates that reach 20 bytes are deferred: their extension needs
 // input reads, is rare outside repetitive data, and runs afterwards with the reference's pruning
 // (a candidate that cannot beat the current best even at full length is skipped).
-__global__ void __launch_bounds__(256) k_probe_sorted(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
+#ifndef PROBE_MIN_BLOCKS
+#define PROBE_MIN_BLOCKS 4
+#endif
+__global__ void __launch_bounds__(256, PROBE_MIN_BLOCKS) k_probe_sorted(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
                                                       const uint32_t* __restrict__ srt_pos, const uint32_t* __restrict__ srt_v,
                                                       uint32_t* __restrict__ best, int depth, int bucket_bits) {
   extern __shared__ __align__(16) uint8_t smem[];
