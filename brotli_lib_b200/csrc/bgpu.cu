@@ -61,6 +61,11 @@ EncParams make_params(int quality, int lgwin, int mode) {
   p.k.bucket_bits = q < 7 ? 14 : 15;
   p.k.depth = 1 << (q - 1);
   p.k.num_last = q < 7 ? 4 : (q < 9 ? 10 : 16);
+  if (p.quality >= 1 && p.quality <= 4) {
+    // SimpleHasher (hash-simple.ts:10-11, 134-150): one slot per key, 16 bits at quality 2, else 17; only
+    // distanceCache[0] is probed (:79-97)
+    p.k.bucket_bits = p.quality == 2 ? 16 : 17; p.k.depth = 1; p.k.num_last = 1;
+  }
   p.k.sh = p.quality >= 10 ? 1 : 2;   // Zopfli emits 2- and 3-byte copies
   return p;
 }
@@ -268,7 +273,8 @@ int upload_plan(bgpu_ctx* ctx, const Job& job) {
 
 // storeMetaBlock (full modelling) unless the caller asked for storeMetaBlockTrivial everywhere.
 int run_backend_any(bgpu_ctx* ctx, const Job& job, const EncParams& P, const uint8_t* d_in) {
-  if (ctx->tune.flags & BGPU_F_TRIVIAL_METABLOCKS) return run_backend(ctx, job, P, d_in);
+  // metablock.ts:517-524: quality < 5 always stores trivial metablocks (as does encodeFast, encode.ts:169)
+  if ((ctx->tune.flags & BGPU_F_TRIVIAL_METABLOCKS) || P.quality < 5) return run_backend(ctx, job, P, d_in);
   return run_backend_full(ctx, job, P, d_in);
 }
 
@@ -298,8 +304,28 @@ int run_frontend(bgpu_ctx* ctx, const Job& job, const EncParams& P, const uint8_
   uint32_t* sa_pos = ctx->sa_pos.as<uint32_t>(); uint32_t* sa_v = ctx->sa_v.as<uint32_t>();
   uint32_t* sb_pos = ctx->sb_pos.as<uint32_t>(); uint32_t* sb_v = ctx->sb_v.as<uint32_t>();
   uint32_t* sh_hist = ctx->sort_hist.as<uint32_t>();
-  uint32_t* best = sa_pos;
-  if (job.max_shard_len >= 4) {
+  const bool simple = P.quality <= 4;
+  uint32_t* best = simple ? sb_pos : sa_pos;     // the array the last sort pass did not write
+  if (simple && job.max_shard_len >= 4) {
+    // quality 1..4: 16/17-bit key of 5 bytes, three LSD passes (6 + 6 + 4/5 bits), one-slot table probe
+    const uint32_t max_npos = job.max_shard_len - 3;
+    const dim3 gs((max_npos + SORT_TILE - 1) / SORT_TILE, n_shard), gp((max_npos + 255) / 256, n_shard);
+    const int bb = P.k.bucket_bits;
+    k_sort_hist<2><<<gs, 256, 0, st>>>(d_in, nullptr, d_sh, sh_hist, bb, 0, 6);
+    k_sort_scan<<<n_shard, 1024, 0, st>>>(d_sh, sh_hist, 1 << 6);
+    k_sort_scatter<2><<<gs, 256, 0, st>>>(d_in, nullptr, nullptr, d_sh, sh_hist, sa_pos, sa_v, bb, 0, 6);
+    ctx->launches += 3; stage_mark(ctx, "k_sort_pass0");
+    k_sort_hist<3><<<gs, 256, 0, st>>>(d_in, sa_v, d_sh, sh_hist, bb, 6, 6);
+    k_sort_scan<<<n_shard, 1024, 0, st>>>(d_sh, sh_hist, 1 << 6);
+    k_sort_scatter<3><<<gs, 256, 0, st>>>(d_in, sa_pos, sa_v, d_sh, sh_hist, sb_pos, sb_v, bb, 6, 6);
+    ctx->launches += 3; stage_mark(ctx, "k_sort_pass1");
+    k_sort_hist<3><<<gs, 256, 0, st>>>(d_in, sb_v, d_sh, sh_hist, bb, 12, bb - 12);
+    k_sort_scan<<<n_shard, 1024, 0, st>>>(d_sh, sh_hist, 1 << (bb - 12));
+    k_sort_scatter<3><<<gs, 256, 0, st>>>(d_in, sb_pos, sb_v, d_sh, sh_hist, sa_pos, sa_v, bb, 12, bb - 12);
+    ctx->launches += 3; stage_mark(ctx, "k_sort_pass2");
+    k_probe_simple<<<gp, 256, 0, st>>>(d_in, d_sh, sa_pos, sa_v, best);
+    ctx->launches++; stage_mark(ctx, "k_probe");
+  } else if (job.max_shard_len >= 4) {
     const uint32_t max_npos = job.max_shard_len - 3;
     const dim3 gs((max_npos + SORT_TILE - 1) / SORT_TILE, n_shard), gp((max_npos + PROBE_TILE - 1) / PROBE_TILE, n_shard);
     const int bb = P.k.bucket_bits, nb0 = 1 << SORT_LOW_BITS, nb1 = 1 << (bb - SORT_LOW_BITS);
@@ -420,7 +446,7 @@ int collect(bgpu_ctx* ctx, const Job& job, uint8_t* const* out, const size_t* ou
 
 #include "lanes_host.inc"
 
-int check_quality(const EncParams& P) { return (P.quality >= 1 && P.quality <= 4) ? BGPU_E_UNSUPPORTED : 0; }
+int check_quality(const EncParams&) { return 0; }   // every quality 0..11 has a path (0: host-only uncompressed)
 int check_quality_hq(const EncParams&) { return 0; }   // q10/q11: hq_host.inc
 
 }  // namespace
@@ -535,7 +561,7 @@ int bgpu_encode_part(bgpu_ctx* c, const uint8_t* in, size_t n, const uint8_t* pr
   const bool first = part_flags & BGPU_PART_FIRST, last = part_flags & BGPU_PART_LAST;
   if (!first && n && !prev2) return BGPU_E_INVALID;
   EncParams P = make_params(quality, lgwin, mode);
-  if (P.quality < 5) return BGPU_E_UNSUPPORTED;   // the host-only uncompressed path has no part form
+  if (P.quality < 1) return BGPU_E_UNSUPPORTED;   // the host-only uncompressed path has no part form
   int rc;
   if ((rc = check_quality_hq(P))) return rc;
   if (n == 0) {
@@ -622,7 +648,9 @@ extern "C" {
 int bgpu_stream_create(bgpu_ctx* c, int quality, int lgwin, int mode, bgpu_stream** s) {
   if (!c || !s) return BGPU_E_INVALID;
   EncParams P = make_params(quality, lgwin, mode);
-  if (P.quality < 5) return BGPU_E_UNSUPPORTED;   // streaming q0..4 uses SimpleHasher (encode.ts:343-344)
+  // streaming q0..4 uses SimpleHasher (encode.ts:343-344) and has no uncompressed path: quality 0 takes the
+  // hasher of quality 1 (same 17-bit table, same sparse stores, lgblock = lgwin for both)
+  if (P.quality < 1) P = make_params(1, lgwin, mode);
   int rc; if ((rc = check_quality_hq(P))) return rc;
   bgpu_stream* st = new bgpu_stream(); st->ctx = c; st->quality = P.quality; st->lgwin = P.lgwin; st->mode = mode;
   *s = st;
@@ -712,7 +740,7 @@ int bgpu_stage_match_candidates(bgpu_ctx* c, const uint8_t* in, size_t n, int qu
   if ((rc = upload_plan(c, job))) return rc;
   if ((rc = run_frontend(c, job, P, c->in.as<uint8_t>()))) return rc;
   std::vector<uint32_t> b(n);
-  CK(cudaMemcpyAsync(b.data(), c->sa_pos.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaMemcpyAsync(b.data(), P.quality <= 4 ? c->sb_pos.p : c->sa_pos.p, n * 4, cudaMemcpyDeviceToHost, c->stream));
   CK(cudaStreamSynchronize(c->stream));
   timing_end(c);
   for (size_t i = 0; i < n; i++) { len[i] = b[i] >> 24; dist[i] = (b[i] >> 24) ? (b[i] & 0xFFFFFF) : 0; }

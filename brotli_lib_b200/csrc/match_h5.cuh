@@ -37,6 +37,20 @@ constexpr uint32_t PROBE_HALO = 256;      // >= max depth (quality 9)
 __device__ __forceinline__ uint32_t sort_digit(uint32_t v, int bucket_bits, int shift, int nbits) {
   return (hash4(v, bucket_bits) >> shift) & ((1u << nbits) - 1);
 }
+// Sort passes.  PASS 0 / 1: entries carry the 4 input bytes v, the key is hash4(v) (hash-chain and H10 hashers).
+// PASS 2 / 3: SimpleHasher (hash-simple.ts:48-50, match.ts:174-189): the key hashes 5 bytes, so pass 2 computes
+// it from the input once and the entries carry the KEY; later passes (3) take digits of it directly.
+__device__ __forceinline__ uint32_t hash5(uint32_t v, uint32_t b4, int bits) { return ((v ^ (b4 << 24)) * 0x1E35A7BDu) >> (32 - bits); }
+template <int PASS>
+__device__ __forceinline__ uint32_t sort_load(const uint8_t* sin, const uint32_t* sv, uint32_t e, uint32_t shard_len, int bucket_bits) {
+  if (PASS == 0) return ld32u(sin, e);
+  if (PASS == 2) return hash5(ld32u(sin, e), e + 4 < shard_len ? (uint32_t)__ldg(sin + e + 4) : 0u, bucket_bits);   // data[pos + 4] | 0 past the end
+  return __ldg(sv + e);
+}
+template <int PASS>
+__device__ __forceinline__ uint32_t sort_digit_of(uint32_t v, int bucket_bits, int shift, int nbits) {
+  return PASS >= 2 ? (v >> shift) & ((1u << nbits) - 1) : sort_digit(v, bucket_bits, shift, nbits);
+}
 __device__ __forceinline__ uint32_t shard_npos(const ShardD& sh) { return sh.len >= 4 ? sh.len - 3 : 0; }
 __device__ __forceinline__ uint32_t shard_nstile(const ShardD& sh) { return (shard_npos(sh) + SORT_TILE - 1) / SORT_TILE; }
 
@@ -58,8 +72,8 @@ __global__ void __launch_bounds__(256) k_sort_hist(const uint8_t* __restrict__ i
   for (uint32_t k = 0; k < SORT_TILE / 256; k++) {
     const uint32_t e = base + k * 256 + threadIdx.x;
     if (e < npos) {
-      const uint32_t v = PASS == 0 ? ld32u(sin, e) : __ldg(sv + e);
-      atomicAdd(&s_h[sort_digit(v, bucket_bits, shift, nbits)], 1u);
+      const uint32_t v = sort_load<PASS>(sin, sv, e, sh.len, bucket_bits);
+      atomicAdd(&s_h[sort_digit_of<PASS>(v, bucket_bits, shift, nbits)], 1u);
     }
   }
   __syncthreads();
@@ -133,13 +147,13 @@ __global__ void __launch_bounds__(256) k_sort_scatter(const uint8_t* __restrict_
 #pragma unroll
   for (int r = 0; r < ROUNDS; r++) {
     const uint32_t e = base + w * (SORT_TILE / 8) + r * 32 + lane;
-    v[r] = e < npos ? (PASS == 0 ? ld32u(sin, e) : __ldg(src_v + sh.in_off + e)) : 0;
+    v[r] = e < npos ? sort_load<PASS>(sin, src_v + sh.in_off, e, sh.len, bucket_bits) : 0;
   }
 #pragma unroll
   for (int r = 0; r < ROUNDS; r++) {
     const uint32_t e = base + w * (SORT_TILE / 8) + r * 32 + lane;
     const bool valid = e < npos;
-    const uint32_t d = valid ? sort_digit(v[r], bucket_bits, shift, nbits) : (0x10000u | lane);
+    const uint32_t d = valid ? sort_digit_of<PASS>(v[r], bucket_bits, shift, nbits) : (0x10000u | lane);
     const uint32_t peers = __match_any_sync(0xffffffffu, d);
     const uint32_t before = __popc(peers & ((1u << lane) - 1));
     uint32_t b = 0;
@@ -169,10 +183,10 @@ __global__ void __launch_bounds__(256) k_sort_scatter(const uint8_t* __restrict_
     const uint32_t idx = w * (SORT_TILE / 8) + r * 32 + lane;
     const uint32_t e = base + idx;
     if (e < npos) {
-      const uint32_t d = sort_digit(v[r], bucket_bits, shift, nbits);
+      const uint32_t d = sort_digit_of<PASS>(v[r], bucket_bits, shift, nbits);
       const uint32_t lp = s_base[d] + s_cnt[w][d] + rk[r];
       s_v[lp] = v[r];
-      s_pos[lp] = PASS == 0 ? e : __ldg(src_pos + sh.in_off + e);
+      s_pos[lp] = (PASS == 0 || PASS == 2) ? e : __ldg(src_pos + sh.in_off + e);
     }
   }
   __syncthreads();
@@ -181,7 +195,7 @@ __global__ void __launch_bounds__(256) k_sort_scatter(const uint8_t* __restrict_
 #pragma unroll 4
   for (uint32_t j = tid; j < nvalid; j += 256) {
     const uint32_t vv = s_v[j];
-    const uint32_t d = sort_digit(vv, bucket_bits, shift, nbits);
+    const uint32_t d = sort_digit_of<PASS>(vv, bucket_bits, shift, nbits);
     const uint32_t dest = s_goff[d] + (j - s_base[d]);
     dp[dest] = s_pos[j]; dv[dest] = vv;
   }
@@ -386,6 +400,36 @@ __global__ void __launch_bounds__(256, PROBE_MIN_BLOCKS) k_probe_sorted(const ui
     const uint32_t e = e0 + k;
     if (g0 + e < npos) sbest[s_p[halo + e]] = (bLen[k] << 24) | bDist[k];
   }
+}
+
+
+// SimpleHasher table candidate (hash-simple.ts:64-128, quality 1..4).  The table has ONE slot per key and every
+// position is stored when it is visited or covered by a match (backward-references.ts:52-60, 99-110; exact for
+// quality 3-4, a superset of the every-4th-position stores of quality 1-2), so the slot read at position p holds
+// the newest earlier position with p's key = the entry before p in the key-sorted order; an empty slot reads as
+// position 0 (the zero-initialised Uint32Array).  One thread per sorted entry; the compare runs on the
+// (L2-resident) input in 16-byte steps.  best[p] = len << 24 | distance, 0 when the candidate is shorter than 4.
+__global__ void __launch_bounds__(256) k_probe_simple(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
+                                                      const uint32_t* __restrict__ srt_pos, const uint32_t* __restrict__ srt_key,
+                                                      uint32_t* __restrict__ best) {
+  const ShardD sh = shards[blockIdx.y];
+  const uint32_t npos = shard_npos(sh);
+  uint32_t* sbest = best + sh.in_off;
+  if (blockIdx.x == 0 && threadIdx.x < sh.len - npos) sbest[npos + threadIdx.x] = 0;
+  const uint32_t r = blockIdx.x * 256 + threadIdx.x;
+  if (r >= npos) return;
+  const uint32_t* sp = srt_pos + sh.in_off; const uint32_t* sk = srt_key + sh.in_off;
+  const uint8_t* sin = in + sh.in_off;
+  const uint32_t p = __ldg(sp + r);
+  uint32_t c = 0;
+  if (r > 0 && __ldg(sk + r - 1) == __ldg(sk + r)) c = __ldg(sp + r - 1);
+  const uint32_t backward = p - c;
+  uint32_t out = 0;
+  if (backward != 0 && backward <= MAX_BACKWARD) {     // hash-simple.ts:109-112 (maxBackward = min(p, 4 MiB - 16), c >= 0)
+    const uint32_t len = match_len16(sin, c, p, min(sh.len - p, 128u));
+    if (len >= 4) out = (len << 24) | backward;
+  }
+  sbest[p] = out;
 }
 
 }  // namespace bgpu

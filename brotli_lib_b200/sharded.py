@@ -62,8 +62,8 @@ def stitch(parts):
 def brotliEncodeSharded(data, options=None, *, group=None, dst=0, part_encoder=None, shard_bytes=SHARD_BYTES):
     """brotliEncode over every rank of `group` (torch.distributed).  Collective call: every rank passes
     the same input; rank `dst` returns the stream, the others None.  Inputs the reference handles on
-    the host (empty, < 64 bytes, quality 0: encode.ts:92-138) and qualities 1..4 are not sharded —
-    rank `dst` encodes them alone through brotliEncode."""
+    the host (empty, < 64 bytes, quality 0: encode.ts:92-138) are not sharded — rank `dst` encodes them
+    alone through brotliEncode."""
     import torch.distributed as dist
     o = dict(options or {})
     q = max(0, min(11, int(o.get("quality", 11))))
@@ -71,7 +71,7 @@ def brotliEncodeSharded(data, options=None, *, group=None, dst=0, part_encoder=N
     m = o.get("mode", EncoderMode.GENERIC)
     rank, world = dist.get_rank(group), dist.get_world_size(group)
     n = len(memoryview(data).cast("B"))
-    if n < 64 or q < 5:
+    if n < 64 or q < 1:
         if rank != dst:
             return None
         from .encode import brotliEncode

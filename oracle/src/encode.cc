@@ -66,11 +66,14 @@ static void MergeTrailingInsert(std::vector<Command>& commands, uint32_t lastIns
   } else if (commands.empty()) commands.push_back(CreateInsertCommand((uint32_t)metablockLen));
 }
 
-// Commands for one metablock of a one-shot encode (encode.ts:213-267), any quality >= 5.
+// Commands for one metablock of a one-shot encode (encode.ts:213-267; encode.ts:157-163 for quality 1), any quality >= 1.
 static void OneShotCommands(const Bytes& data, size_t pos, size_t metablockLen, const EncoderParams& p, size_t mask,
-                            HashChainHasher* hc, BinaryTreeHasher* bt, int32_t* distCache, std::vector<Command>& commands) {
+                            HashChainHasher* hc, BinaryTreeHasher* bt, int32_t* distCache, std::vector<Command>& commands,
+                            SimpleHasher* sh = nullptr) {
   size_t numLiterals = 0; uint32_t lastInsertLen = 0;
-  if (p.quality >= 11) CreateHqZopfliBackwardReferences(metablockLen, pos, data, mask, *bt, distCache, 0, p.npostfix, p.ndirect, commands, &numLiterals, &lastInsertLen);
+  if (p.quality <= 4) CreateBackwardReferences(metablockLen, pos, data, mask, *sh, distCache, 0, p.npostfix, p.ndirect, commands, &numLiterals, &lastInsertLen,
+                                               p.quality <= 2 ? 4 : 1);
+  else if (p.quality >= 11) CreateHqZopfliBackwardReferences(metablockLen, pos, data, mask, *bt, distCache, 0, p.npostfix, p.ndirect, commands, &numLiterals, &lastInsertLen);
   else if (p.quality >= 10) CreateZopfliBackwardReferences(metablockLen, pos, data, mask, p.quality, *bt, distCache, 0, p.npostfix, p.ndirect, commands, &numLiterals, &lastInsertLen);
   else CreateBackwardReferences(metablockLen, pos, data, mask, *hc, distCache, 0, p.npostfix, p.ndirect, commands, &numLiterals, &lastInsertLen);
   MergeTrailingInsert(commands, lastInsertLen, metablockLen);
@@ -87,20 +90,23 @@ static std::vector<uint8_t> EncodeStandard(const uint8_t* in, size_t n, const En
   BitWriter w(std::max<size_t>(1024, (size_t)((double)n * 1.2)));
   unsigned bits, value; EncodeWindowBits(p.lgwin, &bits, &value);
   if (partFirst) w.writeBits(bits, value);
-  std::unique_ptr<HashChainHasher> hc; std::unique_ptr<BinaryTreeHasher> bt;
-  if (p.quality <= 9) hc.reset(CreateHashChainHasher(p.quality, p.lgwin));
+  std::unique_ptr<HashChainHasher> hc; std::unique_ptr<BinaryTreeHasher> bt; std::unique_ptr<SimpleHasher> sh;
+  if (p.quality <= 4) sh.reset(CreateSimpleHasher(p.quality));           // encode.ts:149, 192-193
+  else if (p.quality <= 9) hc.reset(CreateHashChainHasher(p.quality, p.lgwin));
   else bt.reset(new BinaryTreeHasher(p.lgwin, n));
   int32_t distCache[16] = {4, 11, 15, 16};
   if (!partFirst) for (int i = 0; i < 16; i++) distCache[i] = 0;
   size_t mask = ((size_t)1 << p.lgwin) - 1;
   Bytes data{in, n};
-  const size_t maxMetablock = (size_t)1 << 24;
+  // quality 1 = encodeFast (encode.ts:140-179): blocks of 1 << lgblock, storeMetaBlockTrivial
+  if (p.quality == 1) forceTrivial = true;
+  const size_t maxMetablock = p.quality == 1 ? (size_t)1 << p.lgblock : (size_t)1 << 24;
   size_t pos = 0;
   while (pos < n) {
     size_t mlen = std::min(n - pos, maxMetablock);
     bool isLast = partLast && pos + mlen >= n;
     std::vector<Command> commands;
-    OneShotCommands(data, pos, mlen, p, mask, hc.get(), bt.get(), distCache, commands);
+    OneShotCommands(data, pos, mlen, p, mask, hc.get(), bt.get(), distCache, commands, sh.get());
     if (forceTrivial) StoreMetaBlockTrivial(w, in, pos, mlen, mask, isLast, commands, DistanceAlphabetSize(p), p.npostfix, p.ndirect);
     else StoreMetaBlock(w, data, pos, mlen, mask, isLast, commands, DistanceAlphabetSize(p), p.quality, p.npostfix, p.ndirect,
                         pos ? in[pos - 1] : prev1, pos > 1 ? in[pos - 2] : (pos ? prev1 : prev2), stats);
@@ -116,7 +122,6 @@ static int BrotliEncode(const uint8_t* in, size_t n, int quality, int lgwin, int
   EncoderParams p = MakeParams(quality, lgwin, mode);
   if (n == 0) { out = EncodeEmptyInput(); return 0; }
   if (p.quality == 0 || n < 64) { out = EncodeUncompressed(in, n); return 0; }
-  if (p.quality < 5) return -2;  // q1-4 (SimpleHasher / encodeFast) are outside the hot path
   out = EncodeStandard(in, n, p, forceTrivial, stats);
   return 0;
 }
@@ -125,7 +130,7 @@ static int BrotliEncode(const uint8_t* in, size_t n, int quality, int lgwin, int
 class BrotliEncoder {
  public:
   EncoderParams p; std::vector<uint8_t> ring; size_t mask; int32_t distCache[16] = {4, 11, 15, 16};
-  std::unique_ptr<HashChainHasher> hc; std::unique_ptr<BinaryTreeHasher> bt;
+  std::unique_ptr<HashChainHasher> hc; std::unique_ptr<BinaryTreeHasher> bt; std::unique_ptr<SimpleHasher> sh;
   size_t inputPos = 0, lastProcessedPos = 0; bool initialized = false, lastEmitted = false;
   BitWriter w; std::vector<uint8_t> outBuf;
   BrotliEncoder(int quality, int lgwin, int mode) : p(MakeParams(quality, lgwin, mode)), ring((size_t)1 << p.lgwin, 0), mask(ring.size() - 1), w(4096) {}
@@ -133,7 +138,8 @@ class BrotliEncoder {
     if (initialized) return;
     unsigned bits, value; EncodeWindowBits(p.lgwin, &bits, &value);
     w.writeBits(bits, value);
-    if (p.quality <= 9) hc.reset(CreateHashChainHasher(std::max(p.quality, 5), p.lgwin));
+    if (p.quality <= 4) sh.reset(CreateSimpleHasher(p.quality));          // encode.ts:343-344 (quality 0 included)
+    else if (p.quality <= 9) hc.reset(CreateHashChainHasher(p.quality, p.lgwin));
     else bt.reset(new BinaryTreeHasher(p.lgwin, (size_t)1 << p.lgwin));
     initialized = true;
   }
@@ -142,7 +148,8 @@ class BrotliEncoder {
     size_t pos = lastProcessedPos;
     Bytes data{ring.data(), ring.size()};
     std::vector<Command> commands; size_t numLiterals = 0; uint32_t lastInsertLen = 0;
-    if (hc) CreateBackwardReferences(blockLen, pos, data, mask, *hc, distCache, 0, p.npostfix, p.ndirect, commands, &numLiterals, &lastInsertLen);
+    if (sh) CreateBackwardReferences(blockLen, pos, data, mask, *sh, distCache, 0, p.npostfix, p.ndirect, commands, &numLiterals, &lastInsertLen, p.quality <= 2 ? 4 : 1);
+    else if (hc) CreateBackwardReferences(blockLen, pos, data, mask, *hc, distCache, 0, p.npostfix, p.ndirect, commands, &numLiterals, &lastInsertLen);
     else if (p.quality >= 11) CreateHqZopfliBackwardReferences(blockLen, pos, data, mask, *bt, distCache, 0, p.npostfix, p.ndirect, commands, &numLiterals, &lastInsertLen);
     else CreateZopfliBackwardReferences(blockLen, pos, data, mask, p.quality, *bt, distCache, 0, p.npostfix, p.ndirect, commands, &numLiterals, &lastInsertLen);
     MergeTrailingInsert(commands, lastInsertLen, blockLen);
@@ -200,7 +207,7 @@ int oracle_encode_stats(const uint8_t* in, size_t n, int quality, int lgwin, int
 int oracle_encode_part(const uint8_t* in, size_t n, const uint8_t* prev, int flags, int quality, int lgwin, int mode,
                        uint8_t* out, size_t cap, size_t* out_len) {
   EncoderParams p = MakeParams(quality, lgwin, mode);
-  if (p.quality < 5 || n == 0) return -2;
+  if (p.quality < 1 || n == 0) return -2;
   const bool first = flags & 1, last = flags & 2;
   std::vector<uint8_t> v = EncodeStandard(in, n, p, false, nullptr, first, last, first ? 0 : prev[1], first ? 0 : prev[0]);
   *out_len = v.size();
@@ -250,6 +257,21 @@ int oracle_h5_chain_best(const uint8_t* in, size_t n, int quality, int lgwin, ui
   return 0;
 }
 
+// hash-simple.ts table part alone ("candidate-exact" stage, quality 2..4): findLongestMatch with an empty
+// distance cache at every position in order (each call stores its position), same limits as above.
+int oracle_simple_table_best(const uint8_t* in, size_t n, int quality, int lgwin, uint32_t* len, uint32_t* dist) {
+  std::unique_ptr<SimpleHasher> h(CreateSimpleHasher(quality));
+  Bytes data{in, n}; size_t mask = ((size_t)1 << lgwin) - 1;
+  int32_t dc[16] = {0};
+  for (size_t p = 0; p < n; p++) { len[p] = 0; dist[p] = 0; }
+  for (size_t p = 0; p + 4 <= n; p++) {
+    HasherSearchResult r;
+    h->findLongestMatch(data, mask, dc, p, (uint32_t)std::min<size_t>(n - p, 128), std::min<size_t>(p, ((size_t)1 << 22) - 16), r);
+    len[p] = r.len; dist[p] = r.distance;
+  }
+  return 0;
+}
+
 // hash-binary-tree.ts findAllMatches for EVERY position of a single-window input (no skipping of
 // positions covered by long matches — that is caller logic, backward-references-hq.ts:520-540):
 // offsets[i]..offsets[i+1] index (dist, len) of position i; maxLength = n - i, maxBackward = min(i, 4M-16).
@@ -271,12 +293,13 @@ int oracle_h10_all_matches(const uint8_t* in, size_t n, int lgwin, uint32_t* off
 // Commands of the one-shot encode of a single-metablock input (encode.ts:213-267).
 int oracle_commands(const uint8_t* in, size_t n, int quality, int lgwin, int mode, Command* cmds, size_t cap, size_t* ncmd) {
   EncoderParams p = MakeParams(quality, lgwin, mode);
-  if (p.quality < 5 || n == 0 || n > ((size_t)1 << 24)) return -2;
-  std::unique_ptr<HashChainHasher> hc; std::unique_ptr<BinaryTreeHasher> bt;
-  if (p.quality <= 9) hc.reset(CreateHashChainHasher(p.quality, p.lgwin)); else bt.reset(new BinaryTreeHasher(p.lgwin, n));
+  if (p.quality < 1 || n == 0 || n > ((size_t)1 << (p.quality == 1 ? p.lgblock : 24))) return -2;
+  std::unique_ptr<HashChainHasher> hc; std::unique_ptr<BinaryTreeHasher> bt; std::unique_ptr<SimpleHasher> sh;
+  if (p.quality <= 4) sh.reset(CreateSimpleHasher(p.quality));
+  else if (p.quality <= 9) hc.reset(CreateHashChainHasher(p.quality, p.lgwin)); else bt.reset(new BinaryTreeHasher(p.lgwin, n));
   int32_t distCache[16] = {4, 11, 15, 16};
   std::vector<Command> commands;
-  OneShotCommands(Bytes{in, n}, 0, n, p, ((size_t)1 << p.lgwin) - 1, hc.get(), bt.get(), distCache, commands);
+  OneShotCommands(Bytes{in, n}, 0, n, p, ((size_t)1 << p.lgwin) - 1, hc.get(), bt.get(), distCache, commands, sh.get());
   *ncmd = commands.size();
   if (commands.size() > cap) return -1;
   memcpy(cmds, commands.data(), commands.size() * sizeof(Command));
@@ -323,8 +346,6 @@ const uint8_t* oracle_context_lut(void) { return ContextLookupTable(); }
 const double* oracle_log2_table(void) { return kLog2Table(); }
 
 void* oracle_stream_create(int quality, int lgwin, int mode) {
-  EncoderParams p = MakeParams(quality, lgwin, mode);
-  if (p.quality >= 1 && p.quality < 5) return nullptr;
   return new BrotliEncoder(quality, lgwin, mode);
 }
 // Returns the bytes completed by this call; the pointer is valid until the next call.

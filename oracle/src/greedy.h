@@ -1,5 +1,5 @@
-// ORACLE (test infrastructure) — restates match.ts, hash-chains.ts:19-153,240-261 and
-// backward-references.ts:14-158.
+// ORACLE (test infrastructure) — restates match.ts, hash-chains.ts:19-153,240-261,
+// hash-simple.ts:10-150 and backward-references.ts:14-158.
 #pragma once
 #include "common.h"
 #include "command.h"
@@ -99,6 +99,54 @@ static inline HashChainHasher* CreateHashChainHasher(int quality, int lgwin) {
   return new HashChainHasher(15, quality - 1, lgwin, 16);
 }
 
+// match.ts:174-189 hashBytes8, hashLen == 5 path (the only one hash-simple.ts uses)
+static inline uint32_t HashBytes5(const Bytes& d, size_t pos, int bucketBits) {
+  uint32_t h32 = d.at0(pos) | (d.at0(pos + 1) << 8) | (d.at0(pos + 2) << 16) | (d.at0(pos + 3) << 24);
+  uint32_t b4 = d.at0(pos + 4);
+  return ((h32 ^ (b4 << 24)) * 0x1E35A7BDu) >> (32 - bucketBits);
+}
+
+// hash-simple.ts:20-128: one slot per bucket, zero-initialised (so an empty bucket reads as position 0)
+class SimpleHasher {
+ public:
+  std::vector<uint32_t> buckets; int bucketBits;
+  explicit SimpleHasher(int bucketBits_) : buckets((size_t)1 << bucketBits_, 0), bucketBits(bucketBits_) {}
+  // :52-55
+  void store(const Bytes& data, size_t mask, size_t ix) { buckets[HashBytes5(data, ix & mask, bucketBits)] = (uint32_t)ix; }
+  // :64-128
+  void findLongestMatch(const Bytes& data, size_t ringBufferMask, int32_t* distanceCache, size_t curIx,
+                        uint32_t maxLength, size_t maxBackward, HasherSearchResult& out) {
+    size_t cur = curIx & ringBufferMask;
+    uint32_t bestLen = out.len; int64_t bestScore = out.score;
+    uint32_t key = HashBytes5(data, cur, bucketBits);
+    out.lenCodeDelta = 0;
+    int64_t cachedBackward = distanceCache[0];
+    if (cachedBackward > 0 && cachedBackward <= (int64_t)maxBackward) {
+      size_t prevIx = (curIx - (size_t)cachedBackward) & ringBufferMask;
+      if (data.at(prevIx + bestLen) == data.at(cur + bestLen)) {
+        uint32_t len = FindMatchLength(data.p, prevIx, cur, maxLength);
+        if (len >= 4) {
+          int64_t score = BackwardReferenceScoreUsingLastDistance(len);
+          if (score > bestScore) { bestLen = len; out.len = len; out.distance = (uint32_t)cachedBackward; out.score = score; bestScore = score; }
+        }
+      }
+    }
+    size_t prevIx = buckets[key];
+    buckets[key] = (uint32_t)curIx;
+    size_t backward = curIx - prevIx;
+    if (backward == 0 || backward > maxBackward) return;
+    prevIx &= ringBufferMask;
+    if (data.at(prevIx + bestLen) != data.at(cur + bestLen)) return;
+    uint32_t len = FindMatchLength(data.p, prevIx, cur, maxLength);
+    if (len >= 4) {
+      int64_t score = BackwardReferenceScore(len, (uint32_t)backward);
+      if (score > bestScore) { out.len = len; out.distance = (uint32_t)backward; out.score = score; }
+    }
+  }
+};
+// hash-simple.ts:134-150 (quality 2: 16 bits; 1, 3, 4: 17 bits)
+static inline SimpleHasher* CreateSimpleHasher(int quality) { return new SimpleHasher(quality == 2 ? 16 : 17); }
+
 // backward-references.ts:136-158
 static inline uint32_t DistanceToCode(uint32_t distance, const int32_t* distCache) {
   static const uint8_t idx[16] = {0, 1, 2, 3, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 1, 1};
@@ -112,12 +160,13 @@ static inline uint32_t DistanceToCode(uint32_t distance, const int32_t* distCach
   return distance + 16 - 1;
 }
 
-// backward-references.ts:14-134 (hash-chain instantiation; quality > 2 so every covered
-// position is stored).  distCache must have 16 slots.
+// backward-references.ts:14-134.  storeStride = 1 for quality > 2 (every covered position is stored),
+// 4 for quality <= 2 (:99-104).  distCache must have 16 slots.
+template <class Hasher>
 static inline void CreateBackwardReferences(size_t numBytes, size_t position, const Bytes& rb, size_t mask,
-                                            HashChainHasher& hasher, int32_t* distCache, uint32_t lastInsertLen,
+                                            Hasher& hasher, int32_t* distCache, uint32_t lastInsertLen,
                                             uint32_t npostfix, uint32_t ndirect, std::vector<Command>& commands,
-                                            size_t* numLiteralsOut, uint32_t* lastInsertLenOut) {
+                                            size_t* numLiteralsOut, uint32_t* lastInsertLenOut, size_t storeStride = 1) {
   size_t numLiterals = 0; uint32_t insertLen = lastInsertLen;
   size_t pos = position; const size_t posEnd = position + numBytes;
   const size_t maxWindowBackward = ((size_t)1 << 22) - 16;
@@ -136,7 +185,7 @@ static inline void CreateBackwardReferences(size_t numBytes, size_t position, co
       numLiterals += insertLen;
       if (distCode > 0) { distCache[3] = distCache[2]; distCache[2] = distCache[1]; distCache[1] = distCache[0]; distCache[0] = (int32_t)distance; }
       size_t storeEnd = std::min(pos + matchLen, posEnd >= 4 ? posEnd - 4 : 0);
-      for (size_t i = pos + 1; i < storeEnd; i++) hasher.store(rb, mask, i);
+      for (size_t i = pos + 1; i < storeEnd; i += storeStride) hasher.store(rb, mask, i);
       pos += matchLen;
       insertLen = 0;
     } else { insertLen++; pos++; }

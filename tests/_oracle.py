@@ -45,6 +45,7 @@ def lib():
         L.oracle_encode_shards.argtypes = [u8p, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, szp]
         L.oracle_encode_part.argtypes = [u8p, C.c_size_t, u8p, C.c_int, C.c_int, C.c_int, C.c_int, u8p, C.c_size_t, szp]
         L.oracle_h5_chain_best.argtypes = [u8p, C.c_size_t, C.c_int, C.c_int, u8p, u8p]
+        L.oracle_simple_table_best.argtypes = [u8p, C.c_size_t, C.c_int, C.c_int, u8p, u8p]
         L.oracle_h10_all_matches.argtypes = [u8p, C.c_size_t, C.c_int, u8p, u8p, u8p, C.c_size_t, szp]
         L.oracle_commands.argtypes = [u8p, C.c_size_t, C.c_int, C.c_int, C.c_int, u8p, C.c_size_t, szp]
         L.oracle_store_trivial.argtypes = [u8p, C.c_size_t, u8p, C.c_size_t, C.c_int, C.c_int, C.c_uint, C.c_uint,
@@ -128,6 +129,15 @@ def h5_chain_best(data, quality=5, lgwin=22):
     ln = np.zeros(a.size, dtype=np.uint32)
     ds = np.zeros(a.size, dtype=np.uint32)
     lib().oracle_h5_chain_best(p, a.size, quality, lgwin, ln.ctypes.data, ds.ctypes.data)
+    return ln, ds
+
+
+def simple_table_best(data, quality=4, lgwin=22):
+    """hash-simple.ts table candidate of every position (all earlier positions stored, empty distance cache)."""
+    a, p = _buf(data)
+    ln = np.zeros(a.size, dtype=np.uint32)
+    ds = np.zeros(a.size, dtype=np.uint32)
+    lib().oracle_simple_table_best(p, a.size, quality, lgwin, ln.ctypes.data, ds.ctypes.data)
     return ln, ds
 
 

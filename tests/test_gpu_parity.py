@@ -135,18 +135,87 @@ def test_end_to_end_default_roundtrip_and_size(gpu_ctx, name):
 def test_fuzz_matrix_all_supported_qualities(gpu_ctx):
     # test/brotli.test.ts:264-281
     for name, data in fuzz_inputs():
-        for q in (0, 5, 6, 7, 8, 9, 10, 11):
+        for q in range(12):
             s = gpu_ctx.encode(data, q)
             _rt(s, data)
             if len(data) < 64 or q == 0:
                 assert s == O.encode(data, q)   # host-only paths are byte-identical
 
 
-def test_unsupported_qualities_fail_loudly(gpu_ctx):
+def test_unsupported_calls_fail_loudly(gpu_ctx):
+    # no silent fallback: what the GPU path does not implement is an error (quality 0 has no part form)
     import brotli_lib_b200._lib as L
+    with pytest.raises((L.BgpuError, RuntimeError)):
+        gpu_ctx.encode_part(bytes(1000), b"", True, False, 0, 22, 0)
+
+
+# ---- quality 1..4: SimpleHasher (hash-simple.ts) + trivial metablocks (metablock.ts:517-524, encode.ts:140-179) ----
+SIMPLE_INPUTS = ["alice29.txt", "enc-ttf.bin", "zeros", "quickfox_repeated", "backward65536", "random_org_10k.bin", "monkey",
+                 "html-content.bin", "abc1000", "font4k"]
+
+
+@pytest.mark.parametrize("name", SIMPLE_INPUTS)
+@pytest.mark.parametrize("quality", [2, 3, 4])
+def test_simple_table_candidates_bit_exact(gpu_ctx, name, quality):
+    """The one-slot table candidate of every position (16-bit keys at quality 2, 17-bit at 3/4)."""
+    data = load_input(name)
+    ln, ds = gpu_ctx.stage_match_candidates(data, quality, 22)
+    oln, ods = O.simple_table_best(data, quality, 22)
+    assert np.array_equal(ln, oln)
+    assert np.array_equal(ds, ods)
+
+
+@pytest.mark.parametrize("name", SIMPLE_INPUTS)
+@pytest.mark.parametrize("quality,mode", [(3, 0), (4, 0), (4, 2)])
+def test_simple_commands_and_stream_bit_exact_in_exact_parse_mode(gpu_ctx, name, quality, mode):
+    """Quality 3/4 store every position, so the precomputed table candidates are the reference's: same commands and,
+    with the (always trivial) metablock, the same bytes as the oracle."""
+    data = load_input(name)
+    gpu_ctx.set_tuning(segment_bytes=EXACT)
+    try:
+        cm = gpu_ctx.stage_commands(data, quality, 22, mode)
+        s = gpu_ctx.encode(data, quality, 22, mode)
+    finally:
+        gpu_ctx.set_tuning()
+    ocm = O.commands(data, quality, 22, mode)
+    assert len(cm) == len(ocm)
+    assert cm.tobytes() == ocm.tobytes()
+    if len(data) >= 64:
+        assert s == O.encode(data, quality, 22, mode)
+    _rt(s, data)
+
+
+@pytest.mark.parametrize("name", CORPUS + SYNTH)
+def test_simple_default_roundtrip_and_size(gpu_ctx, name):
+    """Default (segment-parallel) mode at quality 1..4.  Quality 1/2: the reference stores only every 4th position
+    under a match (backward-references.ts:99-104), the GPU table holds all of them, so streams differ; sizes are
+    held to the oracle's + 0.5 % (+ 64 bytes for tiny inputs)."""
+    data = load_input(name)
     for q in (1, 2, 3, 4):
-        with pytest.raises(L.BgpuError):
-            gpu_ctx.encode(bytes(1000), q)
+        for mode in (0, 2):
+            s = gpu_ctx.encode(data, q, 22, mode)
+            _rt(s, data)
+            ref = len(O.encode(data, q, 22, mode))
+            assert len(s) <= ref * 1.005 + 64, (name, q, mode, len(s), ref)
+
+
+def test_simple_stitched_shards_and_parts(gpu_ctx):
+    parts = [load_input("alice29.txt"), bytes(70001), load_input("enc-ttf.bin")[:150003], load_input("quickfox_repeated")[:50000],
+             load_input("random_org_10k.bin")]
+    data = b"".join(parts)
+    gpu_ctx.set_tuning(shard_bytes=65536, segment_bytes=4096)
+    try:
+        for q in (1, 2, 3, 4):
+            _rt(gpu_ctx.encode(data, q, 22, 0), data)
+            cut = [0, 100001, 100002, len(data) // 2, len(data)]
+            out = b""
+            for i in range(len(cut) - 1):
+                out += gpu_ctx.encode_part(data[cut[i]:cut[i + 1]], data[max(0, cut[i] - 2):cut[i]], i == 0, i == len(cut) - 2, q, 22, 0)
+            _rt(out, data)
+    finally:
+        gpu_ctx.set_tuning()
+    for q in (1, 3):
+        _rt(gpu_ctx.encode(data[:1000], q, 10, 0), data[:1000])     # small window, input inside it
 
 
 @pytest.mark.parametrize("shard,seg,mb", [(65536, 16384, 0), (100000, 4096, 8192), (1 << 20, 65536, 131072), (4096, 1024, 1024)])
@@ -183,7 +252,7 @@ def test_batch_of_independent_streams(gpu_ctx):
 def test_streaming_api(gpu_ctx):
     import brotli_lib_b200 as B
     # test/brotli.test.ts:283-312
-    for q in (5, 9):
+    for q in (0, 1, 2, 3, 4, 5, 9):
         g = Xorshift32(0x12345678)
         data = g.bytes(4096)
         enc = B.BrotliEncoder({"quality": q}, context=gpu_ctx)
@@ -198,10 +267,11 @@ def test_streaming_api(gpu_ctx):
     data = load_input("alice29.txt")
     gpu_ctx.set_tuning(shard_bytes=32768)
     try:
-        enc = B.BrotliEncoder(quality=5, context=gpu_ctx)
-        parts = [enc.update(data[i:i + 10000]) for i in range(0, len(data), 10000)] + [enc.finish()]
-        assert sum(1 for p in parts[:-1] if p) >= 3
-        _rt(b"".join(parts), data)
+        for q in (5, 0, 2, 4):
+            enc = B.BrotliEncoder(quality=q, context=gpu_ctx)
+            parts = [enc.update(data[i:i + 10000]) for i in range(0, len(data), 10000)] + [enc.finish()]
+            assert sum(1 for p in parts[:-1] if p) >= 3
+            _rt(b"".join(parts), data)
     finally:
         gpu_ctx.set_tuning()
     enc = B.BrotliEncoder(quality=5, context=gpu_ctx)

@@ -57,10 +57,44 @@ def test_ratio_assertion_abcdefghij():
 
 
 def test_fuzz_matrix():
-    # test/brotli.test.ts:264-281 (qualities 1..4 are outside the hot path: SimpleHasher)
+    # test/brotli.test.ts:264-281
     for name, data in fuzz_inputs():
-        for q in (0, 5, 6, 7, 8, 9, 10, 11):
+        for q in range(12):
             _roundtrip(O.encode(data, q), data)
+
+
+@pytest.mark.parametrize("name", CORPUS + SYNTH)
+def test_roundtrip_corpus_simple_hasher(name):
+    # q1 (encodeFast, encode.ts:140-179) and q2-4 (SimpleHasher, hash-simple.ts): valid streams, and more
+    # effort never loses much: q4 <= q2 * 1.02, q5 <= q4 * 1.02 on every corpus file
+    data = load_input(name)
+    size = {}
+    for q in (1, 2, 3, 4):
+        for mode in (0, 2):
+            s = O.encode(data, q, 22, mode)
+            _roundtrip(s, data)
+            if mode == 0:
+                size[q] = len(s)
+    # small windows only with inputs that fit them (the reference masks one-shot input positions with the
+    # window mask, so larger inputs do not survive there at any quality)
+    _roundtrip(O.encode(data[:1000], 1, 10, 0), data[:1000])
+    _roundtrip(O.encode(data[:60000], 3, 16, 0), data[:60000])
+    if len(data) >= 4096:
+        assert size[4] <= size[2] * 1.02 + 16
+        assert len(O.encode(data, 5, 22, 0)) <= size[4] * 1.02 + 16
+
+
+def test_simple_table_candidates():
+    # the stage entry point agrees with the parse on what a table candidate is
+    data = load_input("alice29.txt")[:30000]
+    for q in (2, 4):
+        ln, ds = O.simple_table_best(data, q)
+        assert ln.max() <= 128 and (ds[ln > 0] > 0).all() and (ln[ln > 0] >= 4).all()
+        pos = np.nonzero(ln)[0]
+        assert (ds[pos] <= pos).all()
+        for p in pos[:200]:
+            c = p - ds[p]
+            assert data[c:c + ln[p]] == data[p:p + ln[p]]
 
 
 def test_font_vs_generic():
@@ -72,7 +106,7 @@ def test_font_vs_generic():
 
 def test_streaming_matrix():
     # test/brotli.test.ts:283-312: seed 0x12345678, 4096 random bytes, chunk sizes 1..257
-    for q in (5, 6, 7, 8, 9, 10, 11):
+    for q in range(12):
         g = Xorshift32(0x12345678)
         data = g.bytes(4096)
         enc = O.StreamEncoder(q)
@@ -92,6 +126,10 @@ def test_streaming_multiblock_and_empty():
     _roundtrip(b"".join(parts), data)
     enc = O.StreamEncoder(5)
     _roundtrip(enc.finish(), b"")
+    for q in (0, 1, 3, 4):      # SimpleHasher carried across blocks of 1 << lgblock (encode.ts:343-344, 366-373)
+        enc = O.StreamEncoder(q)
+        parts = [enc.update(data[i:i + 50000]) for i in range(0, len(data), 50000)] + [enc.finish()]
+        _roundtrip(b"".join(parts), data)
 
 
 def test_tables_against_reference_literals():
