@@ -134,7 +134,7 @@ def time_oracle(sample, quality, lgwin, mode, threads):
 # n = input bytes, M = output bytes, S = sum of H10 matches.  Command-record terms (16 C) are left out
 # (C is not known on the host), so the figures are lower bounds.  A stage groups the kernels that
 # §8(d) judges as one unit (K1+K2+K3 = key sort + probe; K4 = H10 sort + short scan + tree).
-STAGE_OF = {"k_sort_pass0": "match_finding", "k_sort_pass1": "match_finding", "k_probe": "match_finding",
+STAGE_OF = {"k_sort_pass0": "match_finding", "k_sort_pass1": "match_finding", "k_sort_pass2": "match_finding", "k_probe": "match_finding",
             "k_h10_sort": "h10_matches", "k_h10_short": "h10_matches", "k_h10_tree": "h10_matches", "k_h10_tree_hot": "h10_matches",
             "k_parse": "parse", "k_stitch": "parse",
             "k_zop_model1": "zopfli", "k_zop_dp1": "zopfli", "k_zop_model2": "zopfli", "k_zop_dp2": "zopfli",
@@ -407,6 +407,8 @@ def main():
     if args.quality:
         wl["quality"] = args.quality
         wl["metric"] = f"input_GBps_q{args.quality}"
+        wl["label"] = f"[--quality {args.quality} override: " + ("SimpleHasher one-slot table + trivial metablocks" if args.quality < 5 else
+                                                               "hash-chain matcher" if args.quality < 10 else "H10 + Zopfli") + "] " + wl["label"]
     if args.lgwin:
         wl["lgwin"] = args.lgwin
     rank = int(os.environ.get("RANK", "0"))

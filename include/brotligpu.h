@@ -19,7 +19,7 @@ extern "C" {
 #define BGPU_OK 0
 #define BGPU_E_INVALID (-1)          /* NULL pointer / bad argument */
 #define BGPU_E_OUTPUT_TOO_SMALL (-2) /* *out_len is set to the size needed */
-#define BGPU_E_UNSUPPORTED (-3)      /* quality 1..4 (SimpleHasher / encodeFast: outside the hot path) */
+#define BGPU_E_UNSUPPORTED (-3)      /* a call the GPU path has no form for (bgpu_encode_part at quality 0) */
 #define BGPU_E_NO_DEVICE (-4)
 #define BGPU_E_CUDA (-5)             /* bgpu_last_cuda_error() has the text */
 #define BGPU_E_NOMEM (-6)
@@ -64,7 +64,9 @@ size_t bgpu_max_compressed_size(size_t n);
  * Options are clamped, never rejected (encode.ts:57-62); TEXT == GENERIC; FONT sets
  * npostfix=1/ndirect=12 at quality >= 4 (enc-constants.ts:121-126).  n == 0 -> A1 01
  * (encode.ts:92-103); quality 0 or n < 64 -> uncompressed metablocks (encode.ts:105-138); both
- * are produced on the host (no kernel).  quality 1..4 -> BGPU_E_UNSUPPORTED.
+ * are produced on the host (no kernel).  quality 1 = encodeFast (encode.ts:140-179) and quality 2..4
+ * (encode.ts:192-193, 238-244) use the one-slot SimpleHasher (src/encode/hash-simple.ts) and always store
+ * trivial metablocks (metablock.ts:517-524); quality 5..9 the hash-chain hasher, 10..11 H10 + Zopfli.
  * `in`/`out` are host buffers owned by the caller. */
 int bgpu_encode(bgpu_ctx* ctx, const uint8_t* in, size_t n, int quality, int lgwin, int mode,
                 uint8_t* out, size_t out_cap, size_t* out_len);
@@ -85,7 +87,7 @@ int bgpu_encode_batch(bgpu_ctx* ctx, int count, const uint8_t* const* in, const 
  * prev2[0..1] = the two input bytes before `in` (in stream order); a part without LAST ends with an
  * empty metadata block (RFC 7932 section 9.2) so that it is byte-aligned.  The concatenation of the
  * parts of an input, in order, is one valid stream.  Parts should be multiples of the 4 MiB shard.
- * quality >= 5 only (BGPU_E_UNSUPPORTED below). */
+ * quality >= 1 (quality 0, the host-only uncompressed path, has no part form: BGPU_E_UNSUPPORTED). */
 #define BGPU_PART_FIRST 1u
 #define BGPU_PART_LAST 2u
 int bgpu_encode_part(bgpu_ctx* ctx, const uint8_t* in, size_t n, const uint8_t* prev2, unsigned part_flags,
@@ -100,7 +102,8 @@ int bgpu_encode_device(bgpu_ctx* ctx, const void* d_in, size_t n, int quality, i
 
 /* new BrotliEncoder(opts) / update(chunk) / finish()     src/encode/encode.ts:290-409
  * update copies the chunk (encode.ts:360-363) and returns the bytes completed so far (possibly
- * none); *out stays valid until the next call on the same stream. */
+ * none); *out stays valid until the next call on the same stream.  Every quality 0..11 (the streaming
+ * class has no uncompressed path: quality 0..4 run the SimpleHasher, encode.ts:343-344). */
 int bgpu_stream_create(bgpu_ctx* ctx, int quality, int lgwin, int mode, bgpu_stream** s);
 int bgpu_stream_update(bgpu_stream* s, const uint8_t* chunk, size_t n, const uint8_t** out, size_t* out_len);
 int bgpu_stream_finish(bgpu_stream* s, const uint8_t** out, size_t* out_len);
