@@ -125,9 +125,23 @@ def time_oracle(sample, quality, lgwin, mode, threads):
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import _oracle as O
     t = time.perf_counter()
-    total = O.encode_shards_total(sample, 1 << 22, quality, lgwin, mode, threads)
+    sizes = O.encode_shards_sizes(sample, 1 << 22, quality, lgwin, mode, threads)
     dt = time.perf_counter() - t
-    return sample.size / dt / 1e9, total, dt
+    return sample.size / dt / 1e9, sizes, dt
+
+
+def size_delta(sample, ref_sizes, quality, lgwin, mode, device):
+    """SURVEY.md section 8(d) ratio accounting: the shards of the CPU sample, each as its own stream, through the
+    GPU library vs the reference restatement at the same quality / lgwin: delta = (M_gpu - M_ref) / M_ref."""
+    import brotli_lib_b200 as B
+    ctx = B.Context(device)
+    items = [sample[o:o + (1 << 22)] for o in range(0, sample.size, 1 << 22)]
+    gpu = [len(s) for s in ctx.encode_batch(items, quality, lgwin, mode)]
+    ctx.close()
+    ref = [int(x) for x in ref_sizes]
+    d = [(g - r) / r for g, r in zip(gpu, ref)]
+    return {"shards": len(d), "total": round((sum(gpu) - sum(ref)) / sum(ref), 5), "max": round(max(d), 5), "mean": round(sum(d) / len(d), 5),
+            "gate_total": 0.005, "per_shard": [round(x, 5) for x in d], "reference": "oracle/ restatement, same shards as independent streams"}
 
 
 # ALGORITHMIC (compulsory) HBM bytes of each stage per launch: SURVEY.md §8(d) / DESIGN.md §4.
@@ -366,15 +380,17 @@ def run_gpu(args, wl, rank, world, local_rank):
         if world == 1 and not args.no_cpu:
             threads = host_threads()
             sample, what = cpu_sample(wl, threads)
-            gbps, total, dt = time_oracle(sample, wl["quality"], wl["lgwin"], wl["mode"], threads)
+            gbps, sizes, dt = time_oracle(sample, wl["quality"], wl["lgwin"], wl["mode"], threads)
             line["cpu_baseline"] = {"value": gbps, "unit": UNIT, "cores": threads, "kind": "port",
                                     "sample": f"oracle/ C++ restatement of brotli-lib, {what}, {dt:.1f} s"}
+            line["size_delta"] = size_delta(sample, sizes, wl["quality"], wl["lgwin"], wl["mode"], local_rank)
             if q11 is not None:
                 w3 = WORKLOADS["config3"]
                 sample, what = cpu_sample(w3, threads)
-                gbps, total, dt = time_oracle(sample, w3["quality"], w3["lgwin"], w3["mode"], threads)
+                gbps, sizes, dt = time_oracle(sample, w3["quality"], w3["lgwin"], w3["mode"], threads)
                 line["q11"]["cpu_baseline"] = {"value": gbps, "unit": UNIT, "cores": threads, "kind": "port",
                                                "sample": f"oracle/ C++ restatement of brotli-lib, {what}, {dt:.1f} s"}
+                line["q11"]["size_delta"] = size_delta(sample, sizes, w3["quality"], w3["lgwin"], w3["mode"], local_rank)
         print(json.dumps(line))
     if dist is not None:
         dist.barrier()

@@ -212,6 +212,21 @@ __device__ __forceinline__ uint4 ld128u(const uint8_t* base, uint64_t off) {
   const uint32_t a = __ldg(w), b = __ldg(w + 1), c = __ldg(w + 2), d = __ldg(w + 3), e = __ldg(w + 4);
   return make_uint4(__funnelshift_r(a, b, sh), __funnelshift_r(b, c, sh), __funnelshift_r(c, d, sh), __funnelshift_r(d, e, sh));
 }
+// 16 unaligned bytes as two aligned 16-byte loads (2 LSU instructions instead of the 5 of ld128u; the words are
+// picked with selects).  `p` may have any alignment; reads stay inside the two 16-byte lines that hold p .. p + 15.
+__device__ __forceinline__ uint4 ld128v(const uint8_t* p) {
+  const uintptr_t a = reinterpret_cast<uintptr_t>(p);
+  const uint4* q = reinterpret_cast<const uint4*>(a & ~(uintptr_t)15);
+  const uint4 lo = __ldg(q), hi = __ldg(q + 1);
+  const uint32_t k = (uint32_t)(a >> 2) & 3u, sh = (uint32_t)(a & 3) * 8;
+  const uint32_t w0 = k == 0 ? lo.x : k == 1 ? lo.y : k == 2 ? lo.z : lo.w;
+  const uint32_t w1 = k == 0 ? lo.y : k == 1 ? lo.z : k == 2 ? lo.w : hi.x;
+  const uint32_t w2 = k == 0 ? lo.z : k == 1 ? lo.w : k == 2 ? hi.x : hi.y;
+  const uint32_t w3 = k == 0 ? lo.w : k == 1 ? hi.x : k == 2 ? hi.y : hi.z;
+  const uint32_t w4 = k == 0 ? hi.x : k == 1 ? hi.y : k == 2 ? hi.z : hi.w;
+  return make_uint4(__funnelshift_r(w0, w1, sh), __funnelshift_r(w1, w2, sh), __funnelshift_r(w2, w3, sh), __funnelshift_r(w3, w4, sh));
+}
+
 // number of equal leading bytes of two 16-byte blocks (16 if identical)
 __device__ __forceinline__ uint32_t prefix16(const uint4& x, const uint4& y) {
   // branch-free: the first differing word by selects, then its first differing byte
@@ -282,7 +297,11 @@ __global__ void __launch_bounds__(256, PROBE_MIN_BLOCKS) k_probe_sorted(const ui
       vv[t] = ok[t] ? __ldg(sv + g) : 0;
     }
 #pragma unroll
+#ifdef PROBE_LD128V
+    for (int t = 0; t < NST; t++) xx[t] = ok[t] ? ld128v(sin + pp[t] + 4) : make_uint4(0, 0, 0, 0);   // reads <= 36 bytes past p: inside the padded input
+#else
     for (int t = 0; t < NST; t++) xx[t] = ok[t] ? ld128u(sin, (uint64_t)pp[t] + 4) : make_uint4(0, 0, 0, 0);   // reads <= 24 bytes past p: inside the padded input
+#endif
 #pragma unroll
     for (int t = 0; t < NST; t++) {
       const uint32_t i = tid + 256 * t;
@@ -407,8 +426,10 @@ __global__ void __launch_bounds__(256, PROBE_MIN_BLOCKS) k_probe_sorted(const ui
 // position is stored when it is visited or covered by a match (backward-references.ts:52-60, 99-110; exact for
 // quality 3-4, a superset of the every-4th-position stores of quality 1-2), so the slot read at position p holds
 // the newest earlier position with p's key = the entry before p in the key-sorted order; an empty slot reads as
-// position 0 (the zero-initialised Uint32Array).  One thread per sorted entry; the compare runs on the
-// (L2-resident) input in 16-byte steps.  best[p] = len << 24 | distance, 0 when the candidate is shorter than 4.
+// position 0 (the zero-initialised Uint32Array).  One thread per sorted entry.  The first 16 bytes of every
+// position are fetched ONCE (a random 16-byte gather from the L2-resident input) and handed to the next lane,
+// whose candidate it is; only matches that reach 16 bytes go back to the input.
+// best[p] = len << 24 | distance, 0 when the candidate is shorter than 4.
 __global__ void __launch_bounds__(256) k_probe_simple(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
                                                       const uint32_t* __restrict__ srt_pos, const uint32_t* __restrict__ srt_key,
                                                       uint32_t* __restrict__ best) {
@@ -416,17 +437,34 @@ __global__ void __launch_bounds__(256) k_probe_simple(const uint8_t* __restrict_
   const uint32_t npos = shard_npos(sh);
   uint32_t* sbest = best + sh.in_off;
   if (blockIdx.x == 0 && threadIdx.x < sh.len - npos) sbest[npos + threadIdx.x] = 0;
+  if (blockIdx.x * 256 >= npos) return;                 // whole CTA out of range (warps stay whole below)
   const uint32_t r = blockIdx.x * 256 + threadIdx.x;
-  if (r >= npos) return;
+  const bool valid = r < npos;
+  const uint32_t lane = threadIdx.x & 31;
   const uint32_t* sp = srt_pos + sh.in_off; const uint32_t* sk = srt_key + sh.in_off;
   const uint8_t* sin = in + sh.in_off;
-  const uint32_t p = __ldg(sp + r);
-  uint32_t c = 0;
-  if (r > 0 && __ldg(sk + r - 1) == __ldg(sk + r)) c = __ldg(sp + r - 1);
+  const uint32_t p = valid ? __ldg(sp + r) : 0u;
+  const uint32_t key = valid ? __ldg(sk + r) : 0xFFFFFFFFu;
+  const uint4 xp = valid ? ld128v(sin + p) : make_uint4(0, 0, 0, 0);
+  // the previous sorted entry: lane - 1, or a load for the first lane of the warp
+  uint32_t pc = __shfl_up_sync(0xffffffffu, p, 1), kc = __shfl_up_sync(0xffffffffu, key, 1);
+  uint4 xc;
+  xc.x = __shfl_up_sync(0xffffffffu, xp.x, 1); xc.y = __shfl_up_sync(0xffffffffu, xp.y, 1);
+  xc.z = __shfl_up_sync(0xffffffffu, xp.z, 1); xc.w = __shfl_up_sync(0xffffffffu, xp.w, 1);
+  if (lane == 0) {
+    if (valid && r > 0) { pc = __ldg(sp + r - 1); kc = __ldg(sk + r - 1); xc = ld128v(sin + pc); }
+    else kc = 0xFFFFFFFEu;
+  }
+  if (!valid) return;
+  uint32_t c = pc;
+  if (kc != key) { c = 0; xc = ld128v(sin); }         // empty slot: position 0 (same address for every lane)
   const uint32_t backward = p - c;
   uint32_t out = 0;
   if (backward != 0 && backward <= MAX_BACKWARD) {     // hash-simple.ts:109-112 (maxBackward = min(p, 4 MiB - 16), c >= 0)
-    const uint32_t len = match_len16(sin, c, p, min(sh.len - p, 128u));
+    const uint32_t limit = min(sh.len - p, 128u);
+    uint32_t len = prefix16(xp, xc);
+    if (len == 16 && limit > 16) len = 16 + match_len16(sin, (uint64_t)c + 16, (uint64_t)p + 16, limit - 16);
+    len = min(len, limit);
     if (len >= 4) out = (len << 24) | backward;
   }
   sbest[p] = out;

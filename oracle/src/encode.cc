@@ -216,9 +216,9 @@ int oracle_encode_part(const uint8_t* in, size_t n, const uint8_t* prev, int fla
   return 0;
 }
 
-// Encode `count` independent shards on `threads` host threads (CPU-baseline helper).
-// Returns the total compressed size in *total_out; out buffers are discarded.
-int oracle_encode_shards(const uint8_t* in, size_t n, size_t shard, int quality, int lgwin, int mode, int threads, size_t* total_out) {
+// Encode `count` independent shards on `threads` host threads (CPU-baseline helper): sizes[i] (may be NULL) = the
+// compressed size of shard i, *total_out their sum; the streams themselves are discarded.
+int oracle_encode_shards_sizes(const uint8_t* in, size_t n, size_t shard, int quality, int lgwin, int mode, int threads, size_t* total_out, size_t* sizes) {
   size_t count = (n + shard - 1) / shard;
   std::atomic<size_t> next(0), total(0); std::atomic<int> err(0);
   auto work = [&]() {
@@ -230,6 +230,7 @@ int oracle_encode_shards(const uint8_t* in, size_t n, size_t shard, int quality,
       int rc = BrotliEncode(in + off, len, quality, lgwin, mode, false, v);
       if (rc) err = rc;
       total += v.size();
+      if (sizes) sizes[i] = v.size();
     }
   };
   std::vector<std::thread> th;
@@ -238,6 +239,9 @@ int oracle_encode_shards(const uint8_t* in, size_t n, size_t shard, int quality,
   for (auto& t : th) t.join();
   *total_out = total;
   return err;
+}
+int oracle_encode_shards(const uint8_t* in, size_t n, size_t shard, int quality, int lgwin, int mode, int threads, size_t* total_out) {
+  return oracle_encode_shards_sizes(in, n, shard, quality, lgwin, mode, threads, total_out, nullptr);
 }
 
 // hash-chains.ts chain part alone ("candidate-exact" stage): for every position p with at

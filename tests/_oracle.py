@@ -43,6 +43,7 @@ def lib():
         L.oracle_encode.argtypes = [u8p, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, u8p, C.c_size_t, szp]
         L.oracle_encode_stats.argtypes = [u8p, C.c_size_t, C.c_int, C.c_int, C.c_int, szp, C.POINTER(C.c_int)]
         L.oracle_encode_shards.argtypes = [u8p, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, szp]
+        L.oracle_encode_shards_sizes.argtypes = [u8p, C.c_size_t, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, szp, u8p]
         L.oracle_encode_part.argtypes = [u8p, C.c_size_t, u8p, C.c_int, C.c_int, C.c_int, C.c_int, u8p, C.c_size_t, szp]
         L.oracle_h5_chain_best.argtypes = [u8p, C.c_size_t, C.c_int, C.c_int, u8p, u8p]
         L.oracle_simple_table_best.argtypes = [u8p, C.c_size_t, C.c_int, C.c_int, u8p, u8p]
@@ -122,6 +123,17 @@ def encode_shards_total(data, shard, quality, lgwin=22, mode=0, threads=1):
     if rc:
         raise RuntimeError(f"oracle_encode_shards rc={rc}")
     return n.value
+
+
+def encode_shards_sizes(data, shard, quality, lgwin=22, mode=0, threads=1):
+    """Per-shard compressed sizes of `data` cut into independent `shard`-byte streams (threaded)."""
+    a, p = _buf(data)
+    n = C.c_size_t(0)
+    sizes = np.zeros((a.size + shard - 1) // shard, dtype=np.uint64)
+    rc = lib().oracle_encode_shards_sizes(p, a.size, shard, quality, lgwin, mode, threads, C.byref(n), sizes.ctypes.data)
+    if rc:
+        raise RuntimeError(f"oracle_encode_shards_sizes rc={rc}")
+    return sizes
 
 
 def h5_chain_best(data, quality=5, lgwin=22):

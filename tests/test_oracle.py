@@ -173,3 +173,7 @@ def test_stage_functions_consistent():
         assert np.array_equal(d, tab["cmdDepths"]) and np.array_equal(b, tab["cmdBits"])
     ln, ds = O.h5_chain_best(data[:20000], 5)
     assert ln.max() <= 128 and (ds[ln > 0] > 0).all()
+    # threaded per-shard sizes (bench.py size_delta) = the one-shot encoder on each shard
+    sizes = O.encode_shards_sizes(data, 50000, 4, 22, 0, threads=3)
+    assert [int(x) for x in sizes] == [len(O.encode(data[o:o + 50000], 4, 22, 0)) for o in range(0, len(data), 50000)]
+    assert int(sizes.sum()) == O.encode_shards_total(data, 50000, 4, 22, 0, threads=2)
