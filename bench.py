@@ -357,7 +357,7 @@ def run_gpu(args, wl, rank, world, local_rank):
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     ctx = B.Context(local_rank)
-    tune = {"segment_bytes": args.segment_kb << 10, "lanes": args.lanes, "group_shards": args.group_shards}
+    tune = {"segment_bytes": args.segment_kb << 10, "lanes": args.lanes, "group_shards": args.group_shards, "flags": args.flags}
     ctx.set_tuning(**tune)
     warm = max(args.warmup, 3)
     line = measure(args, wl, ctx, torch, dist, dev, rank, world, local_rank, args.steps, warm, not args.no_verify, tune)
@@ -412,6 +412,7 @@ def main():
     ap.add_argument("--group-shards", type=int, default=0, help="shards per lane group (0 = library default)")
     ap.add_argument("--q11-lanes", type=int, default=0)
     ap.add_argument("--q11-group-shards", type=int, default=0)
+    ap.add_argument("--flags", type=int, default=0, help="bgpu_tuning.flags (BGPU_F_*) for A/B runs")
     ap.add_argument("--no-verify", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-q11", action="store_true", help="skip the config-3 (q11) measurement that accompanies the default run")

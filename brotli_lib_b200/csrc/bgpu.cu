@@ -104,7 +104,7 @@ struct bgpu_ctx {
   cudaStream_t copy_stream = nullptr;   // parent only: the groups' host->device copies, in group order
   uint32_t* h_sizes = nullptr; size_t h_sizes_cap = 0;   // pinned: shard sizes of the lane's current group
   uint8_t* pin = nullptr; size_t pin_cap = 0, pin_used = 0, pin_want = 0;   // pinned staging of descriptor uploads
-  DBuf in, sa_pos, sa_v, sb_pos, sb_v, sort_hist, role, ins, cmds, out, shards, mbs, segs, tile_seg, seg_ncmd, seg_trail, hist, codes, tree_bits, tree_nbits,
+  DBuf in, sa_pos, sa_v, sb_pos, sb_v, sort_hist, role, ins, cmds, out, shards, mbs, segs, tile_seg, seg_ncmd, seg_trail, seg_ring, hist, codes, tree_bits, tree_nbits,
       tile_bits, tile_off, tile_model, warp_base, thr_off, shard_bytes, huff_meta, model_arena, misc_arena, d_models, d_splits, d_cb, d_cx, d_bh_ptrs, d_bh_strides, d_cx_outs,
       h10_bstart, h10_bend, h10_short, h10_forest, h10_m, h10_off, h10_cnt, h10_cursor, h10_full, h10_hot,
       zop_bytehist, zop_model, zop_lc, zop_nodes, zop_ring;
@@ -300,6 +300,7 @@ int run_frontend(bgpu_ctx* ctx, const Job& job, const EncParams& P, const uint8_
   if ((rc = reserve_front(ctx, job, P))) return rc;
   if ((rc = ctx->seg_ncmd.reserve((size_t)n_seg * 4))) return rc;
   if ((rc = ctx->seg_trail.reserve((size_t)n_seg * 4))) return rc;
+  if ((rc = ctx->seg_ring.reserve((size_t)n_seg * 16))) return rc;
   const ShardD* d_sh = ctx->shards.as<ShardD>(); const MbD* d_mb = ctx->mbs.as<MbD>(); const SegD* d_sg = ctx->segs.as<SegD>();
   uint32_t* sa_pos = ctx->sa_pos.as<uint32_t>(); uint32_t* sa_v = ctx->sa_v.as<uint32_t>();
   uint32_t* sb_pos = ctx->sb_pos.as<uint32_t>(); uint32_t* sb_v = ctx->sb_v.as<uint32_t>();
@@ -345,10 +346,11 @@ int run_frontend(bgpu_ctx* ctx, const Job& job, const EncParams& P, const uint8_
   }
   CK(cudaMemsetAsync(ctx->role.p, 0, N, st));
   k_parse<PARSE_G><<<(n_seg * PARSE_G + 127) / 128, 128, 0, st>>>(d_in, d_sh, d_sg, n_seg, best, ctx->role.as<uint8_t>(), ctx->ins.as<uint32_t>(),
-                                           ctx->cmds.as<Cmd>(), ctx->seg_ncmd.as<uint32_t>(), ctx->seg_trail.as<uint32_t>(), P.k);
+                                           ctx->cmds.as<Cmd>(), ctx->seg_ncmd.as<uint32_t>(), ctx->seg_trail.as<uint32_t>(), ctx->seg_ring.as<int4>(), P.k);
   ctx->launches++; stage_mark(ctx, "k_parse");
   k_stitch<<<(n_mb + 63) / 64, 64, 0, st>>>(d_sh, d_mb, d_sg, n_mb, ctx->role.as<uint8_t>(), ctx->ins.as<uint32_t>(), ctx->cmds.as<Cmd>(),
-                                            ctx->seg_ncmd.as<uint32_t>(), ctx->seg_trail.as<uint32_t>(), P.k);
+                                            ctx->seg_ncmd.as<uint32_t>(), ctx->seg_trail.as<uint32_t>(), P.k,
+                                            (ctx->tune.flags & BGPU_F_NO_RING_HANDOVER) ? nullptr : ctx->seg_ring.as<int4>());
   ctx->launches++; stage_mark(ctx, "k_stitch");
   CK(cudaGetLastError());
   return 0;
@@ -472,7 +474,7 @@ void bgpu_ctx_destroy(bgpu_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
   DBuf* all[] = {&c->in, &c->sa_pos, &c->sa_v, &c->sb_pos, &c->sb_v, &c->sort_hist, &c->role, &c->ins, &c->cmds, &c->out, &c->shards, &c->mbs, &c->segs, &c->tile_seg, &c->seg_ncmd,
-                 &c->seg_trail, &c->hist, &c->codes, &c->tree_bits, &c->tree_nbits, &c->tile_bits, &c->tile_off, &c->tile_model, &c->warp_base, &c->thr_off, &c->shard_bytes, &c->huff_meta,
+                 &c->seg_trail, &c->seg_ring, &c->hist, &c->codes, &c->tree_bits, &c->tree_nbits, &c->tile_bits, &c->tile_off, &c->tile_model, &c->warp_base, &c->thr_off, &c->shard_bytes, &c->huff_meta,
                  &c->model_arena, &c->misc_arena, &c->d_models, &c->d_splits, &c->d_cb, &c->d_cx, &c->d_bh_ptrs, &c->d_bh_strides, &c->d_cx_outs,
                  &c->h10_bstart, &c->h10_bend, &c->h10_short, &c->h10_forest, &c->h10_m, &c->h10_off, &c->h10_cnt, &c->h10_cursor, &c->h10_full, &c->h10_hot,
                  &c->zop_bytehist, &c->zop_model, &c->zop_lc, &c->zop_nodes, &c->zop_ring};

@@ -98,7 +98,7 @@ __global__ void __launch_bounds__(128) k_parse(const uint8_t* __restrict__ in, c
                                                const SegD* __restrict__ segs, uint32_t n_seg,
                                                const uint32_t* __restrict__ best, uint8_t* __restrict__ role,
                                                uint32_t* __restrict__ ins_at, Cmd* __restrict__ cmds,
-                                               uint32_t* __restrict__ seg_ncmd, uint32_t* __restrict__ seg_trail, Params P) {
+                                               uint32_t* __restrict__ seg_ncmd, uint32_t* __restrict__ seg_trail, int4* __restrict__ seg_ring, Params P) {
   const uint32_t seg = (blockIdx.x * 128 + threadIdx.x) / G;
   if (seg >= n_seg) return;
   const uint32_t wl = threadIdx.x & 31;
@@ -160,7 +160,18 @@ __global__ void __launch_bounds__(128) k_parse(const uint8_t* __restrict__ in, c
     if (code > 0) { ring[3] = ring[2]; ring[2] = ring[1]; ring[1] = ring[0]; ring[0] = (int)mdist; }
     pos = qf + mlen; ins_start = pos; ncmd++;
   }
-  if (lane == 0) { seg_ncmd[seg] = ncmd; seg_trail[seg] = ins_start; }
+  if (lane == 0) { seg_ncmd[seg] = ncmd; seg_trail[seg] = ins_start; seg_ring[seg] = make_int4(ring[0], ring[1], ring[2], ring[3]); }
+}
+
+// Inverse of dist_prefix (command.ts:111-135): the backward distance a stored explicit distance code stands for.
+__device__ __forceinline__ uint32_t distance_of_explicit(uint32_t dp, uint32_t extra, uint32_t ndirect, uint32_t npostfix) {
+  const uint32_t c = dp & 0x3FF;
+  if (c < 16 + ndirect) return c - 15;
+  const uint32_t v = c - 16 - ndirect;
+  const uint32_t postfix = v & ((1u << npostfix) - 1), t = v >> npostfix, prefix = t & 1, nbits = (t >> 1) + 1;
+  const uint32_t bucket = nbits + npostfix, offset = (2 + prefix) << bucket;
+  const uint32_t dist = offset + (extra << npostfix) + postfix;
+  return dist - (1u << (npostfix + 2)) + 16 + ndirect - 15;
 }
 
 // Joins the segments of a metablock: literals left over at the end of a segment become part of the
@@ -168,13 +179,22 @@ __global__ void __launch_bounds__(128) k_parse(const uint8_t* __restrict__ in, c
 // encode.ts:253-267 / command.ts:183-208.
 __global__ void k_stitch(const ShardD* __restrict__ shards, const MbD* __restrict__ mbs, const SegD* __restrict__ segs,
                          uint32_t n_mb, uint8_t* __restrict__ role, uint32_t* __restrict__ ins_at, Cmd* __restrict__ cmds,
-                         const uint32_t* __restrict__ seg_ncmd, const uint32_t* __restrict__ seg_trail, Params P) {
+                         const uint32_t* __restrict__ seg_ncmd, const uint32_t* __restrict__ seg_trail, Params P,
+                         const int4* __restrict__ seg_ring = nullptr) {
   const uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;
   if (m >= n_mb) return;
   const MbD mb = mbs[m];
   const ShardD sh = shards[mb.shard];
   uint8_t* srole = role + sh.in_off;
   int64_t carry = -1;  // start of the pending (not yet terminated) literal run, shard-relative
+  // Distance-ring hand-over (seg_ring != nullptr, greedy parse only).  A segment that does not open the stream was
+  // parsed with an unknown ring, so its first copies carry explicit distance codes even where the decoder's ring
+  // holds the distance.  R follows the ring the DECODER has at the segment start (known once a segment made >= 4
+  // ring updates, or from the stream start); the segment's first commands, up to the point where its own view V
+  // of the ring is complete (4 updates, after which V == R), are re-coded against R.  Only the first command of
+  // a segment can lose its update (explicit -> code 0), which leaves every later short code pointing at the same
+  // value, so the commands that are not visited stay valid as they are.
+  int R[4] = {0, 0, 0, 0}; bool Rk = false;
   for (uint32_t s = mb.first_seg; s < mb.first_seg + mb.n_seg; s++) {
     const SegD sg = segs[s];
     const uint32_t seg_end = sg.rel_pos + sg.len;
@@ -192,6 +212,33 @@ __global__ void k_stitch(const ShardD* __restrict__ shards, const MbD* __restric
       }
     }
     if (nc > 0 || carry < 0) carry = trail < seg_end ? (int64_t)trail : -1;
+    if (seg_ring && nc > 0) {
+      if (sg.ring_known) { R[0] = 4; R[1] = 11; R[2] = 15; R[3] = 16; Rk = true; }
+      const int4 e = seg_ring[s];
+      if (Rk && !sg.ring_known) {
+        const int8_t off[16] = {0, 0, 0, 0, -1, 1, -2, 2, -3, 3, -1, 1, -2, 2, -3, 3};
+        int V[4] = {0, 0, 0, 0};
+        uint32_t p = sg.rel_pos;
+        for (uint32_t k = 0; k < nc && V[3] == 0; k++) {
+          const uint32_t il = ins_at[(sh.in_off + p) >> P.sh];
+          Cmd* c = &cmds[(sh.in_off + p + il) >> P.sh];
+          const uint32_t dp = c->distPrefix, oc = dp & 0x3FF;
+          const uint32_t dist = oc < 16 ? (uint32_t)((oc < 4 ? V[oc] : (oc < 10 ? V[0] : V[1])) + off[oc]) : distance_of_explicit(dp, c->distExtra, P.ndirect, P.npostfix);
+          const uint32_t nc_code = distance_to_code(dist, R);
+          if (nc_code != (oc < 16 ? oc : dist + 15)) {
+            uint32_t extra; const uint32_t ndp = dist_prefix(nc_code, P.ndirect, P.npostfix, &extra);
+            c->distPrefix = (uint16_t)ndp; c->distExtra = extra;
+            c->cmdPrefix = (uint16_t)combine_codes(ins_code(c->insertLen), copy_code(c->copyLen & 0x1FFFFFF), (ndp & 0x3FF) == 0);
+          }
+          if (nc_code > 0) { R[3] = R[2]; R[2] = R[1]; R[1] = R[0]; R[0] = (int)dist; }
+          if (oc > 0) { V[3] = V[2]; V[2] = V[1]; V[1] = V[0]; V[0] = (int)dist; }
+          p += il + (c->copyLen & 0x1FFFFFF);
+        }
+      }
+      // the segment's own end view is the decoder's ring whenever it is complete; otherwise R was carried through
+      // all of its commands above (or stays unknown)
+      if (e.w != 0) { R[0] = e.x; R[1] = e.y; R[2] = e.z; R[3] = e.w; Rk = true; }
+    }
   }
   if (carry >= 0) {
     srole[carry] |= 8;
