@@ -91,6 +91,16 @@ HD uint32_t dist_prefix(uint32_t distanceCode, uint32_t ndirect, uint32_t npostf
   *extra = (dist - offset) >> npostfix;
   return (nbits << 10) | (16 + ndirect + ((2 * (nbits - 1) + prefix) << npostfix) + postfix);
 }
+// Inverse of dist_prefix (command.ts:111-135): the backward distance a stored explicit distance code stands for.
+HD uint32_t distance_of_explicit(uint32_t dp, uint32_t extra, uint32_t ndirect, uint32_t npostfix) {
+  const uint32_t c = dp & 0x3FF;
+  if (c < 16 + ndirect) return c - 15;
+  const uint32_t v = c - 16 - ndirect;
+  const uint32_t postfix = v & ((1u << npostfix) - 1), t = v >> npostfix, prefix = t & 1, nbits = (t >> 1) + 1;
+  const uint32_t bucket = nbits + npostfix, offset = (2 + prefix) << bucket;
+  const uint32_t dist = offset + (extra << npostfix) + postfix;
+  return dist - (1u << (npostfix + 2)) + 16 + ndirect - 15;
+}
 // command.ts:146-179 (copyLenCodeDelta is always 0 on this path: no dictionary matches)
 HD Cmd make_cmd(uint32_t insertLen, uint32_t copyLen, uint32_t distanceCode, uint32_t ndirect, uint32_t npostfix) {
   Cmd c;

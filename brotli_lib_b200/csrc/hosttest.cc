@@ -32,6 +32,9 @@ void bgpu_hosttest_make_cmd(uint32_t insertLen, uint32_t copyLen, uint32_t dista
   *out = make_cmd(insertLen, copyLen, distanceCode, ndirect, npostfix);
 }
 void bgpu_hosttest_make_insert_cmd(uint32_t insertLen, Cmd* out) { *out = make_insert_cmd(insertLen); }
+uint32_t bgpu_hosttest_distance_of_explicit(uint32_t distPrefix, uint32_t distExtra, uint32_t ndirect, uint32_t npostfix) {
+  return distance_of_explicit(distPrefix, distExtra, ndirect, npostfix);
+}
 uint32_t bgpu_hosttest_cmd_extra(uint32_t insertLen, uint32_t copyLenField, uint64_t* value) { return cmd_extra(insertLen, copyLenField, value); }
 
 }

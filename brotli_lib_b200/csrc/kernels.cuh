@@ -163,17 +163,6 @@ __global__ void __launch_bounds__(128) k_parse(const uint8_t* __restrict__ in, c
   if (lane == 0) { seg_ncmd[seg] = ncmd; seg_trail[seg] = ins_start; seg_ring[seg] = make_int4(ring[0], ring[1], ring[2], ring[3]); }
 }
 
-// Inverse of dist_prefix (command.ts:111-135): the backward distance a stored explicit distance code stands for.
-__device__ __forceinline__ uint32_t distance_of_explicit(uint32_t dp, uint32_t extra, uint32_t ndirect, uint32_t npostfix) {
-  const uint32_t c = dp & 0x3FF;
-  if (c < 16 + ndirect) return c - 15;
-  const uint32_t v = c - 16 - ndirect;
-  const uint32_t postfix = v & ((1u << npostfix) - 1), t = v >> npostfix, prefix = t & 1, nbits = (t >> 1) + 1;
-  const uint32_t bucket = nbits + npostfix, offset = (2 + prefix) << bucket;
-  const uint32_t dist = offset + (extra << npostfix) + postfix;
-  return dist - (1u << (npostfix + 2)) + 16 + ndirect - 15;
-}
-
 // Joins the segments of a metablock: literals left over at the end of a segment become part of the
 // next segment's first command; what remains at the metablock end is the insert-only command of
 // encode.ts:253-267 / command.ts:183-208.
@@ -187,7 +176,9 @@ __global__ void k_stitch(const ShardD* __restrict__ shards, const MbD* __restric
   const ShardD sh = shards[mb.shard];
   uint8_t* srole = role + sh.in_off;
   int64_t carry = -1;  // start of the pending (not yet terminated) literal run, shard-relative
-  // Distance-ring hand-over (seg_ring != nullptr, greedy parse only).  A segment that does not open the stream was
+  // Distance-ring hand-over (seg_ring != nullptr: BGPU_F_RING_HANDOVER, greedy parse only; OFF by default — measured on config 2
+  // (gpurun r3d): compressed ratio 0.4558 with and without, k_stitch 1.4 -> 9.5 ms per GiB: what a segment start loses is the
+  // PARSE's use of the last distance (different matches are chosen), not the coding of the matches it did choose).  A segment that does not open the stream was
   // parsed with an unknown ring, so its first copies carry explicit distance codes even where the decoder's ring
   // holds the distance.  R follows the ring the DECODER has at the segment start (known once a segment made >= 4
   // ring updates, or from the stream start); the segment's first commands, up to the point where its own view V

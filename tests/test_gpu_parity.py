@@ -369,3 +369,33 @@ def test_hq_batch_font_mode_and_streaming(gpu_ctx):
             pos += k
         out.append(enc.finish())
         _rt(b"".join(out), data)
+
+
+@pytest.mark.parametrize("quality,mode", [(5, 0), (9, 2), (3, 0)])
+def test_ring_handover_across_parse_segments(gpu_ctx, quality, mode):
+    """k_stitch re-codes the first copies of every parse segment against the ring the decoder has there: the stream
+    stays valid for every segment size and is never larger than with the explicit codes (BGPU_F_RING_HANDOVER = 4, opt-in)."""
+    from brotli_lib_b200 import workloads as W
+    data = np.concatenate([W.mixed_segment(6, 0)[: 1 << 20], W.text(300000, 5), W.records(200000, 6),
+                           np.frombuffer(load_input("quickfox_repeated")[:60000], dtype=np.uint8)]).tobytes()
+    for seg in (1024, 4096, 0):
+        for shard, mb in ((0, 0), (1 << 18, 1 << 16)):
+            gpu_ctx.set_tuning(segment_bytes=seg, shard_bytes=shard, metablock_bytes=mb)
+            try:
+                plain = gpu_ctx.encode(data, quality, 22, mode)
+                gpu_ctx.set_tuning(segment_bytes=seg, shard_bytes=shard, metablock_bytes=mb, flags=4)
+                s = gpu_ctx.encode(data, quality, 22, mode)
+            finally:
+                gpu_ctx.set_tuning()
+            _rt(plain, data)
+            _rt(s, data)
+            assert len(s) <= len(plain), (seg, shard, mb, len(s), len(plain))
+    # exact-parse mode has one segment per shard: nothing to hand over, same bytes
+    gpu_ctx.set_tuning(segment_bytes=EXACT, flags=4)
+    try:
+        a = gpu_ctx.encode(data, quality, 22, mode)
+        gpu_ctx.set_tuning(segment_bytes=EXACT)
+        b = gpu_ctx.encode(data, quality, 22, mode)
+    finally:
+        gpu_ctx.set_tuning()
+    assert a == b

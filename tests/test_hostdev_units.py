@@ -98,3 +98,18 @@ def test_product_does_not_reference_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cc", ".h")):
                 text = open(os.path.join(dirpath, f), errors="ignore").read()
                 assert "liboracle" not in text and "_oracle" not in text and "oracle/" not in text.replace("the oracle", ""), f
+
+
+def test_distance_of_explicit_inverts_dist_prefix():
+    """k_stitch's ring hand-over re-codes commands from their stored (prefix, extra bits): the inverse of
+    command.ts:111-135 must return the distance make_cmd was given, in GENERIC and FONT distance parameters."""
+    H = _hosttest()
+    H.bgpu_hosttest_distance_of_explicit.restype = C.c_uint32
+    out = np.zeros(1, dtype=O.CMD_DTYPE)
+    rng = np.random.default_rng(3)
+    dists = list(range(1, 300)) + [2 ** k + d for k in range(8, 22) for d in (-1, 0, 1)] + [int(x) for x in rng.integers(1, (1 << 22) - 16, 2000)] + [(1 << 22) - 16]
+    for ndirect, npostfix in ((0, 0), (12, 1)):
+        for d in dists:
+            H.bgpu_hosttest_make_cmd(3, 7, d + 15, ndirect, npostfix, out.ctypes.data)
+            got = H.bgpu_hosttest_distance_of_explicit(int(out["distPrefix"][0]), int(out["distExtra"][0]), ndirect, npostfix)
+            assert got == d, (ndirect, npostfix, d, got)
