@@ -67,6 +67,7 @@ EncParams make_params(int quality, int lgwin, int mode) {
     p.k.bucket_bits = p.quality == 2 ? 16 : 17; p.k.depth = 1; p.k.num_last = 1;
   }
   p.k.sh = p.quality >= 10 ? 1 : 2;   // Zopfli emits 2- and 3-byte copies
+  p.k.hint = 0;
   return p;
 }
 
@@ -344,14 +345,20 @@ int run_frontend(bgpu_ctx* ctx, const Job& job, const EncParams& P, const uint8_
   } else {
     CK(cudaMemsetAsync(best, 0, N * 4, st));
   }
+  Params Pk = P.k; Pk.hint = (ctx->tune.flags & BGPU_F_RING_HANDOVER) ? 1 : 0;
   CK(cudaMemsetAsync(ctx->role.p, 0, N, st));
   k_parse<PARSE_G><<<(n_seg * PARSE_G + 127) / 128, 128, 0, st>>>(d_in, d_sh, d_sg, n_seg, best, ctx->role.as<uint8_t>(), ctx->ins.as<uint32_t>(),
-                                           ctx->cmds.as<Cmd>(), ctx->seg_ncmd.as<uint32_t>(), ctx->seg_trail.as<uint32_t>(), ctx->seg_ring.as<int4>(), P.k);
+                                           ctx->cmds.as<Cmd>(), ctx->seg_ncmd.as<uint32_t>(), ctx->seg_trail.as<uint32_t>(), ctx->seg_ring.as<int4>(), Pk);
   ctx->launches++; stage_mark(ctx, "k_parse");
   k_stitch<<<(n_mb + 63) / 64, 64, 0, st>>>(d_sh, d_mb, d_sg, n_mb, ctx->role.as<uint8_t>(), ctx->ins.as<uint32_t>(), ctx->cmds.as<Cmd>(),
-                                            ctx->seg_ncmd.as<uint32_t>(), ctx->seg_trail.as<uint32_t>(), P.k,
-                                            (ctx->tune.flags & BGPU_F_RING_HANDOVER) ? ctx->seg_ring.as<int4>() : nullptr);
-  ctx->launches++; stage_mark(ctx, "k_stitch");
+                                            ctx->seg_ncmd.as<uint32_t>(), ctx->seg_trail.as<uint32_t>(), Pk);
+  ctx->launches++;
+  if (Pk.hint) {
+    k_ring_handover<<<(n_seg + 127) / 128, 128, 0, st>>>(d_sh, d_sg, n_seg, ctx->ins.as<uint32_t>(), ctx->cmds.as<Cmd>(), ctx->seg_ncmd.as<uint32_t>(),
+                                                       ctx->seg_ring.as<int4>(), Pk);
+    ctx->launches++;
+  }
+  stage_mark(ctx, "k_stitch");
   CK(cudaGetLastError());
   return 0;
 }

@@ -46,6 +46,7 @@ struct Params {
   int bucket_bits, depth, num_last;
   uint32_t npostfix, ndirect, dist_alphabet;
   int sh;  // command slot shift
+  int hint;  // BGPU_F_RING_HANDOVER: parse segments guess the last distance at their start (k_parse) and k_ring_handover re-codes
 };
 
 // ---------------------------------------------------------------------------------------
@@ -115,6 +116,12 @@ __global__ void __launch_bounds__(128) k_parse(const uint8_t* __restrict__ in, c
   if (sg.ring_known) { ring[0] = 4; ring[1] = 11; ring[2] = 15; ring[3] = 16; }
   else { ring[0] = ring[1] = ring[2] = ring[3] = 0; }
   uint32_t pos = sg.rel_pos, ins_start = sg.rel_pos, ncmd = 0;
+  // A segment that does not open the stream cannot know the decoder's ring, but the copy that is probably running
+  // across its start has the distance of the table candidate one byte earlier: until the first command, that
+  // distance is probed like distanceCache[0] (bonus score, so a long copy continues instead of switching to a nearer
+  // source) and emitted with an explicit code; k_ring_handover turns it into code 0 when the guess was right.
+  int hint = 0;
+  if (P.hint && !sg.ring_known && sg.rel_pos > 0) { const uint32_t hb = sbest[sg.rel_pos - 1]; if ((hb >> 24) >= 4) hint = (int)(hb & 0xFFFFFFu); }
   while (pos < seg_end) {
     const uint32_t q = pos + lane;
     uint32_t blen = 0, bdist = 0; int bscore = 0;
@@ -135,6 +142,11 @@ __global__ void __launch_bounds__(128) k_parse(const uint8_t* __restrict__ in, c
         uint32_t len = 4 + match_len(sin, q + 4, q - d + 4, maxLen - 4);
         int score = 135 * (int)len + 975;
         if (score > bscore) { bscore = score; blen = len; bdist = (uint32_t)d; }
+      }
+      if (hint > 0 && ring[0] == 0 && (uint32_t)hint <= maxBackward && ld32u(sin, q - hint) == v) {
+        const uint32_t len = 4 + match_len(sin, q + 4, q - hint + 4, maxLen - 4);
+        const int score = 135 * (int)len + 975;
+        if (score > bscore) { bscore = score; blen = len; bdist = (uint32_t)hint; }
       }
       // chain best from K3 (truncated at the segment end)
       uint32_t clen = min(b >> 24, maxLen), cdist = b & 0xFFFFFFu;
@@ -168,24 +180,13 @@ __global__ void __launch_bounds__(128) k_parse(const uint8_t* __restrict__ in, c
 // encode.ts:253-267 / command.ts:183-208.
 __global__ void k_stitch(const ShardD* __restrict__ shards, const MbD* __restrict__ mbs, const SegD* __restrict__ segs,
                          uint32_t n_mb, uint8_t* __restrict__ role, uint32_t* __restrict__ ins_at, Cmd* __restrict__ cmds,
-                         const uint32_t* __restrict__ seg_ncmd, const uint32_t* __restrict__ seg_trail, Params P,
-                         const int4* __restrict__ seg_ring = nullptr) {
+                         const uint32_t* __restrict__ seg_ncmd, const uint32_t* __restrict__ seg_trail, Params P) {
   const uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;
   if (m >= n_mb) return;
   const MbD mb = mbs[m];
   const ShardD sh = shards[mb.shard];
   uint8_t* srole = role + sh.in_off;
   int64_t carry = -1;  // start of the pending (not yet terminated) literal run, shard-relative
-  // Distance-ring hand-over (seg_ring != nullptr: BGPU_F_RING_HANDOVER, greedy parse only; OFF by default — measured on config 2
-  // (gpurun r3d): compressed ratio 0.4558 with and without, k_stitch 1.4 -> 9.5 ms per GiB: what a segment start loses is the
-  // PARSE's use of the last distance (different matches are chosen), not the coding of the matches it did choose).  A segment that does not open the stream was
-  // parsed with an unknown ring, so its first copies carry explicit distance codes even where the decoder's ring
-  // holds the distance.  R follows the ring the DECODER has at the segment start (known once a segment made >= 4
-  // ring updates, or from the stream start); the segment's first commands, up to the point where its own view V
-  // of the ring is complete (4 updates, after which V == R), are re-coded against R.  Only the first command of
-  // a segment can lose its update (explicit -> code 0), which leaves every later short code pointing at the same
-  // value, so the commands that are not visited stay valid as they are.
-  int R[4] = {0, 0, 0, 0}; bool Rk = false;
   for (uint32_t s = mb.first_seg; s < mb.first_seg + mb.n_seg; s++) {
     const SegD sg = segs[s];
     const uint32_t seg_end = sg.rel_pos + sg.len;
@@ -203,37 +204,51 @@ __global__ void k_stitch(const ShardD* __restrict__ shards, const MbD* __restric
       }
     }
     if (nc > 0 || carry < 0) carry = trail < seg_end ? (int64_t)trail : -1;
-    if (seg_ring && nc > 0) {
-      if (sg.ring_known) { R[0] = 4; R[1] = 11; R[2] = 15; R[3] = 16; Rk = true; }
-      const int4 e = seg_ring[s];
-      if (Rk && !sg.ring_known) {
-        const int8_t off[16] = {0, 0, 0, 0, -1, 1, -2, 2, -3, 3, -1, 1, -2, 2, -3, 3};
-        int V[4] = {0, 0, 0, 0};
-        uint32_t p = sg.rel_pos;
-        for (uint32_t k = 0; k < nc && V[3] == 0; k++) {
-          const uint32_t il = ins_at[(sh.in_off + p) >> P.sh];
-          Cmd* c = &cmds[(sh.in_off + p + il) >> P.sh];
-          const uint32_t dp = c->distPrefix, oc = dp & 0x3FF;
-          const uint32_t dist = oc < 16 ? (uint32_t)((oc < 4 ? V[oc] : (oc < 10 ? V[0] : V[1])) + off[oc]) : distance_of_explicit(dp, c->distExtra, P.ndirect, P.npostfix);
-          const uint32_t nc_code = distance_to_code(dist, R);
-          if (nc_code != (oc < 16 ? oc : dist + 15)) {
-            uint32_t extra; const uint32_t ndp = dist_prefix(nc_code, P.ndirect, P.npostfix, &extra);
-            c->distPrefix = (uint16_t)ndp; c->distExtra = extra;
-            c->cmdPrefix = (uint16_t)combine_codes(ins_code(c->insertLen), copy_code(c->copyLen & 0x1FFFFFF), (ndp & 0x3FF) == 0);
-          }
-          if (nc_code > 0) { R[3] = R[2]; R[2] = R[1]; R[1] = R[0]; R[0] = (int)dist; }
-          if (oc > 0) { V[3] = V[2]; V[2] = V[1]; V[1] = V[0]; V[0] = (int)dist; }
-          p += il + (c->copyLen & 0x1FFFFFF);
-        }
-      }
-      // the segment's own end view is the decoder's ring whenever it is complete; otherwise R was carried through
-      // all of its commands above (or stays unknown)
-      if (e.w != 0) { R[0] = e.x; R[1] = e.y; R[2] = e.z; R[3] = e.w; Rk = true; }
-    }
   }
   if (carry >= 0) {
     srole[carry] |= 8;
     ins_at[(sh.in_off + (uint32_t)carry) >> P.sh] = mb.rel_pos + mb.len - (uint32_t)carry;
+  }
+}
+
+
+// Distance-ring hand-over (BGPU_F_RING_HANDOVER, greedy parse only; runs after k_stitch).  A segment that does not open
+// the stream was parsed with an unknown ring, so its first copies carry explicit distance codes even where the
+// decoder's ring holds the distance.  When the previous segment of the shard made >= 4 ring updates, its end view of
+// the ring (seg_ring, written by k_parse) IS the decoder's ring R at this segment's start, whatever came before.  The
+// segment's first commands, up to the point where its own view V is complete (4 updates, after which V == R), are
+// re-coded against R.  Only the first command of a segment can lose its update (explicit -> code 0), which leaves every
+// later short code pointing at the same value, so the commands that are not visited stay valid as they are, and so
+// does the end view the next segment relies on.  One thread per segment.
+__global__ void k_ring_handover(const ShardD* __restrict__ shards, const SegD* __restrict__ segs, uint32_t n_seg,
+                                const uint32_t* __restrict__ ins_at, Cmd* __restrict__ cmds,
+                                const uint32_t* __restrict__ seg_ncmd, const int4* __restrict__ seg_ring, Params P) {
+  const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
+  if (s >= n_seg || s == 0) return;
+  const SegD sg = segs[s];
+  const uint32_t nc = seg_ncmd[s];
+  if (sg.ring_known || nc == 0 || segs[s - 1].shard != sg.shard) return;
+  const int4 e = seg_ring[s - 1];
+  if (e.w == 0) return;
+  const ShardD sh = shards[sg.shard];
+  int R[4] = {e.x, e.y, e.z, e.w};
+  const int8_t off[16] = {0, 0, 0, 0, -1, 1, -2, 2, -3, 3, -1, 1, -2, 2, -3, 3};
+  int V[4] = {0, 0, 0, 0};
+  uint32_t p = sg.rel_pos;
+  for (uint32_t k = 0; k < nc && V[3] == 0; k++) {
+    const uint32_t il = ins_at[(sh.in_off + p) >> P.sh];
+    Cmd* c = &cmds[(sh.in_off + p + il) >> P.sh];
+    const uint32_t dp = c->distPrefix, oc = dp & 0x3FF;
+    const uint32_t dist = oc < 16 ? (uint32_t)((oc < 4 ? V[oc] : (oc < 10 ? V[0] : V[1])) + off[oc]) : distance_of_explicit(dp, c->distExtra, P.ndirect, P.npostfix);
+    const uint32_t nc_code = distance_to_code(dist, R);
+    if (nc_code != (oc < 16 ? oc : dist + 15)) {
+      uint32_t extra; const uint32_t ndp = dist_prefix(nc_code, P.ndirect, P.npostfix, &extra);
+      c->distPrefix = (uint16_t)ndp; c->distExtra = extra;
+      c->cmdPrefix = (uint16_t)combine_codes(ins_code(c->insertLen), copy_code(c->copyLen & 0x1FFFFFF), (ndp & 0x3FF) == 0);
+    }
+    if (nc_code > 0) { R[3] = R[2]; R[2] = R[1]; R[1] = R[0]; R[0] = (int)dist; }
+    if (oc > 0) { V[3] = V[2]; V[2] = V[1]; V[1] = V[0]; V[0] = (int)dist; }
+    p += il + (c->copyLen & 0x1FFFFFF);
   }
 }
 

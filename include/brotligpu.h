@@ -46,7 +46,7 @@ typedef struct bgpu_tuning {
   uint32_t group_shards;    /* shards per group (default: shards / lanes, clamped to 16..64)       */
 } bgpu_tuning;
 #define BGPU_F_KEEP_DEVICE_OUTPUT 1u /* bench: skip the device->host gather (device-resident timing) */
-#define BGPU_F_RING_HANDOVER 4u      /* greedy parse: k_stitch re-codes the first copies of every parse segment against the decoder's ring (off by default: r3d measured no size gain for +8 ms per GiB) */
+#define BGPU_F_RING_HANDOVER 4u      /* greedy parse: segments guess the last distance at their start and k_ring_handover re-codes their first copies against the decoder's ring */
 #define BGPU_F_TRIVIAL_METABLOCKS 2u /* storeMetaBlockTrivial for every metablock (metablock.ts:290-389): no block split, no context map */
 
 /* Context: owns the CUDA device, stream, scratch arenas.  Not thread-safe; one per thread.
