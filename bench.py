@@ -130,11 +130,13 @@ def time_oracle(sample, quality, lgwin, mode, threads):
     return sample.size / dt / 1e9, sizes, dt
 
 
-def size_delta(sample, ref_sizes, quality, lgwin, mode, device):
+def size_delta(sample, ref_sizes, quality, lgwin, mode, device, tune=None):
     """SURVEY.md section 8(d) ratio accounting: the shards of the CPU sample, each as its own stream, through the
     GPU library vs the reference restatement at the same quality / lgwin: delta = (M_gpu - M_ref) / M_ref."""
     import brotli_lib_b200 as B
     ctx = B.Context(device)
+    if tune:
+        ctx.set_tuning(**tune)
     items = [sample[o:o + (1 << 22)] for o in range(0, sample.size, 1 << 22)]
     gpu = [len(s) for s in ctx.encode_batch(items, quality, lgwin, mode)]
     ctx.close()
@@ -383,14 +385,14 @@ def run_gpu(args, wl, rank, world, local_rank):
             gbps, sizes, dt = time_oracle(sample, wl["quality"], wl["lgwin"], wl["mode"], threads)
             line["cpu_baseline"] = {"value": gbps, "unit": UNIT, "cores": threads, "kind": "port",
                                     "sample": f"oracle/ C++ restatement of brotli-lib, {what}, {dt:.1f} s"}
-            line["size_delta"] = size_delta(sample, sizes, wl["quality"], wl["lgwin"], wl["mode"], local_rank)
+            line["size_delta"] = size_delta(sample, sizes, wl["quality"], wl["lgwin"], wl["mode"], local_rank, tune)
             if q11 is not None:
                 w3 = WORKLOADS["config3"]
                 sample, what = cpu_sample(w3, threads)
                 gbps, sizes, dt = time_oracle(sample, w3["quality"], w3["lgwin"], w3["mode"], threads)
                 line["q11"]["cpu_baseline"] = {"value": gbps, "unit": UNIT, "cores": threads, "kind": "port",
                                                "sample": f"oracle/ C++ restatement of brotli-lib, {what}, {dt:.1f} s"}
-                line["q11"]["size_delta"] = size_delta(sample, sizes, w3["quality"], w3["lgwin"], w3["mode"], local_rank)
+                line["q11"]["size_delta"] = size_delta(sample, sizes, w3["quality"], w3["lgwin"], w3["mode"], local_rank, tune11)
         print(json.dumps(line))
     if dist is not None:
         dist.barrier()
