@@ -14,7 +14,7 @@ from conftest import CORPUS, SYNTH, load_input  # noqa: E402
 gold = {}
 for name in CORPUS + SYNTH:
     data = load_input(name)
-    for q in (5, 9, 10, 11):
+    for q in (1, 2, 3, 4, 5, 9, 10, 11):
         for lgwin, mode in ((22, 0), (22, 2), (24, 1)):
             s = O.encode(data, q, lgwin, mode)
             assert O.decode(s, len(data)) == data
