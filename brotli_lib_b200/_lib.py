@@ -13,7 +13,7 @@ SYMBOLS = [
     "bgpu_ctx_create", "bgpu_ctx_destroy", "bgpu_ctx_set_tuning", "bgpu_ctx_set_stream", "bgpu_max_compressed_size", "bgpu_encode",
     "bgpu_encode_batch", "bgpu_encode_part", "bgpu_encode_device", "bgpu_stream_create", "bgpu_stream_update", "bgpu_stream_finish",
     "bgpu_stream_destroy", "bgpu_stage_match_candidates", "bgpu_stage_commands", "bgpu_stage_store_trivial",
-    "bgpu_stage_huffman", "bgpu_stage_h10_matches", "bgpu_stage_timings", "bgpu_last_launch_count", "bgpu_last_counter", "bgpu_strerror", "bgpu_last_cuda_error",
+    "bgpu_stage_huffman", "bgpu_stage_h10_matches", "bgpu_stage_histograms", "bgpu_stage_context_map", "bgpu_stage_store_metablock", "bgpu_stage_timings", "bgpu_last_launch_count", "bgpu_last_counter", "bgpu_strerror", "bgpu_last_cuda_error",
     "bgpu_version",
 ]
 
@@ -21,6 +21,15 @@ SYMBOLS = [
 class Tuning(C.Structure):
     _fields_ = [("shard_bytes", C.c_uint32), ("segment_bytes", C.c_uint32), ("metablock_bytes", C.c_uint32),
                 ("flags", C.c_uint32), ("lanes", C.c_uint32), ("group_shards", C.c_uint32)]
+
+
+class BlockSplit(C.Structure):
+    _fields_ = [("num_types", C.c_uint32), ("num_blocks", C.c_uint32), ("types", C.c_void_p), ("lengths", C.c_void_p)]
+
+
+class MbModel(C.Structure):
+    _fields_ = [("split", BlockSplit * 3), ("context_mode", C.c_int), ("literal_context_map", C.c_void_p),
+                ("num_literal_clusters", C.c_uint32), ("distance_context_map", C.c_void_p), ("num_distance_clusters", C.c_uint32)]
 
 
 _lib = None
@@ -57,6 +66,9 @@ def load():
                                            C.POINTER(C.c_uint64), vp]
     L.bgpu_stage_huffman.argtypes = [vp, vp, i, i, vp, vp, vp, vp]
     L.bgpu_stage_h10_matches.argtypes = [vp, vp, sz, i, vp, vp, vp, sz, szp]
+    L.bgpu_stage_histograms.argtypes = [vp, vp, sz, vp, sz, i, vp, C.POINTER(MbModel), vp, vp, vp, C.POINTER(i)]
+    L.bgpu_stage_context_map.argtypes = [vp, vp, sz, C.c_uint32, vp, sz, C.POINTER(C.c_uint64)]
+    L.bgpu_stage_store_metablock.argtypes = [vp, vp, sz, vp, sz, i, i, C.c_uint, C.c_uint, vp, C.POINTER(MbModel), vp, sz, szp]
     L.bgpu_stage_timings.argtypes = [vp, C.POINTER(C.c_char_p), C.POINTER(C.c_float), i]
     L.bgpu_last_launch_count.argtypes = [vp]
     L.bgpu_last_counter.argtypes = [vp, i]

@@ -455,9 +455,6 @@ int collect(bgpu_ctx* ctx, const Job& job, uint8_t* const* out, const size_t* ou
 
 #include "lanes_host.inc"
 
-int check_quality(const EncParams&) { return 0; }   // every quality 0..11 has a path (0: host-only uncompressed)
-int check_quality_hq(const EncParams&) { return 0; }   // q10/q11: hq_host.inc
-
 }  // namespace
 
 extern "C" {
@@ -518,7 +515,6 @@ int bgpu_encode_batch(bgpu_ctx* c, int count, const uint8_t* const* in, const si
   if (!c || count < 0 || (count && (!in || !n || !out || !out_cap || !out_len))) return BGPU_E_INVALID;
   EncParams P = make_params(quality, lgwin, mode);
   int rc;
-  if ((rc = check_quality(P))) return rc;
   CK(cudaSetDevice(c->device));
   // host-only special cases first; the rest goes to the device in one job
   std::vector<int> map; std::vector<size_t> lens; std::vector<const uint8_t*> ptrs;
@@ -532,7 +528,6 @@ int bgpu_encode_batch(bgpu_ctx* c, int count, const uint8_t* const* in, const si
     } else { map.push_back(i); lens.push_back(n[i]); ptrs.push_back(in[i]); }
   }
   if (map.empty()) return result;
-  if ((rc = check_quality_hq(P))) return rc;
   {
     uint32_t L; size_t gb;
     if (lens.size() == 1 && lanes_apply(c, P, lens[0], &L, &gb)) {
@@ -572,7 +567,6 @@ int bgpu_encode_part(bgpu_ctx* c, const uint8_t* in, size_t n, const uint8_t* pr
   EncParams P = make_params(quality, lgwin, mode);
   if (P.quality < 1) return BGPU_E_UNSUPPORTED;   // the host-only uncompressed path has no part form
   int rc;
-  if ((rc = check_quality_hq(P))) return rc;
   if (n == 0) {
     // nothing to code: the header (FIRST) and / or ISLAST + ISEMPTY (LAST), encode.ts:399-405
     HostBits w;
@@ -613,8 +607,6 @@ int bgpu_encode_device(bgpu_ctx* c, const void* d_in, size_t n, int quality, int
   EncParams P = make_params(quality, lgwin, mode);
   int rc;
   if (P.quality == 0) return BGPU_E_INVALID;
-  if ((rc = check_quality(P))) return rc;
-  if ((rc = check_quality_hq(P))) return rc;
   CK(cudaSetDevice(c->device));
   {
     uint32_t L; size_t gb;
@@ -660,7 +652,6 @@ int bgpu_stream_create(bgpu_ctx* c, int quality, int lgwin, int mode, bgpu_strea
   // streaming q0..4 uses SimpleHasher (encode.ts:343-344) and has no uncompressed path: quality 0 takes the
   // hasher of quality 1 (same 17-bit table, same sparse stores, lgblock = lgwin for both)
   if (P.quality < 1) P = make_params(1, lgwin, mode);
-  int rc; if ((rc = check_quality_hq(P))) return rc;
   bgpu_stream* st = new bgpu_stream(); st->ctx = c; st->quality = P.quality; st->lgwin = P.lgwin; st->mode = mode;
   *s = st;
   return 0;
@@ -770,7 +761,7 @@ static void rebuild_commands(const std::vector<uint8_t>& role, const std::vector
 int bgpu_stage_commands(bgpu_ctx* c, const uint8_t* in, size_t n, int quality, int lgwin, int mode, void* cmds_out, size_t cmd_cap, size_t* ncmd) {
   if (!c || !in || !ncmd || n == 0 || n > ((size_t)1 << 22)) return BGPU_E_INVALID;
   EncParams P = make_params(quality, lgwin, mode);
-  int rc; if ((rc = check_quality_hq(P))) return rc;
+  int rc;
   CK(cudaSetDevice(c->device));
   Job job; size_t lens[1] = {n}; plan_job(c, P, lens, 1, job);
   if (job.shards.size() != 1) return BGPU_E_INVALID;
@@ -794,6 +785,32 @@ int bgpu_stage_commands(bgpu_ctx* c, const uint8_t* in, size_t n, int quality, i
   return 0;
 }
 
+// roles / ins / cmds arrays (kernels.cuh layout) of a caller-supplied command list covering exactly n bytes.
+// counts (optional): literals, commands, commands that code a distance.
+static int roles_from_commands(const Cmd* cl, size_t ncmd, size_t n, int sh, std::vector<uint8_t>& role, std::vector<uint32_t>& ins,
+                               std::vector<Cmd>& cm, uint32_t* counts) {
+  const size_t slots = (n >> sh) + 2;
+  role.assign(n + IN_PAD, 0); ins.assign(slots, 0); cm.resize(slots);
+  memset(cm.data(), 0, slots * sizeof(Cmd));
+  size_t pos = 0; uint32_t nl = 0, nd = 0;
+  for (size_t i = 0; i < ncmd; i++) {
+    const Cmd& k = cl[i];
+    uint32_t copyLen = k.copyLen & 0x1FFFFFF;
+    if (pos + k.insertLen + copyLen > n) return -1;
+    size_t start = pos;
+    for (uint32_t j = 0; j < k.insertLen; j++) role[pos + j] = 1;
+    pos += k.insertLen; nl += k.insertLen;
+    if (copyLen) { role[pos] |= 2; cm[pos >> sh] = k; if (k.cmdPrefix >= 128) nd++; }
+    else if (i + 1 != ncmd) return -1;  // an insert-only command must be last
+    role[start] |= 4 | (copyLen ? 0 : 8);
+    ins[start >> sh] = k.insertLen;
+    pos += copyLen;
+  }
+  if (pos != n) return -1;
+  if (counts) { counts[0] = nl; counts[1] = (uint32_t)ncmd; counts[2] = nd; }
+  return 0;
+}
+
 int bgpu_stage_store_trivial(bgpu_ctx* c, const uint8_t* in, size_t n, const void* cmds_in, size_t ncmd, int is_last, int mode,
                              unsigned start_nbits, unsigned start_value, uint8_t* out, size_t out_cap, size_t* out_len, uint64_t* out_bits,
                              void* tables) {
@@ -810,26 +827,9 @@ int bgpu_stage_store_trivial(bgpu_ctx* c, const uint8_t* in, size_t n, const voi
   sh.flags = (start_nbits ? 1u : 0u) | 2u;   // never append the padding block here
   sh.start_nbits = start_nbits; sh.start_value = start_value;
   job.mbs[0].is_last = is_last ? 1 : 0;
-  // roles / ins / cmds from the caller's command list
-  const Cmd* cl = (const Cmd*)cmds_in;
   size_t slots = (n >> P.k.sh) + 2;
-  std::vector<uint8_t> role(n + IN_PAD, 0); std::vector<uint32_t> ins(slots, 0); std::vector<Cmd> cm(slots);
-  memset(cm.data(), 0, slots * sizeof(Cmd));
-  size_t pos = 0;
-  for (size_t i = 0; i < ncmd; i++) {
-    const Cmd& k = cl[i];
-    uint32_t copyLen = k.copyLen & 0x1FFFFFF;
-    if (pos + k.insertLen + copyLen > n) return BGPU_E_INVALID;
-    size_t start = pos;
-    for (uint32_t j = 0; j < k.insertLen; j++) role[pos + j] = 1;
-    pos += k.insertLen;
-    if (copyLen) { role[pos] |= 2; cm[pos >> P.k.sh] = k; }
-    else if (i + 1 != ncmd) return BGPU_E_INVALID;  // an insert-only command must be last
-    role[start] |= 4 | (copyLen ? 0 : 8);
-    ins[start >> P.k.sh] = k.insertLen;
-    pos += copyLen;
-  }
-  if (pos != n) return BGPU_E_INVALID;
+  std::vector<uint8_t> role; std::vector<uint32_t> ins; std::vector<Cmd> cm;
+  if (roles_from_commands((const Cmd*)cmds_in, ncmd, n, P.k.sh, role, ins, cm, nullptr)) return BGPU_E_INVALID;
   int rc;
   if ((rc = c->in.reserve(job.in_bytes + IN_PAD))) return rc;
   if ((rc = reserve_front(c, job, P))) return rc;
@@ -862,6 +862,157 @@ int bgpu_stage_store_trivial(bgpu_ctx* c, const uint8_t* in, size_t n, const voi
       }
   }
   return rc;
+}
+
+// Shared front half of bgpu_stage_histograms / bgpu_stage_store_metablock: one metablock = the whole input, roles from
+// the caller's commands, symbol streams (part A), then the caller's block splits and context mode in place of parts B / C,
+// then the per-context histograms (part D1) — the same host phases and kernels run_backend_full goes through.
+static int stage_full_front(bgpu_ctx* c, const uint8_t* in, size_t n, const void* cmds_in, size_t ncmd, int is_last, int mode,
+                            unsigned start_nbits, unsigned start_value, const uint8_t* prev2, const bgpu_mb_model* model,
+                            Job& job, EncParams& P, FullBackend& F, uint8_t** d_in_out) {
+  if (!c || !in || !cmds_in || !model || n == 0 || n > ((size_t)1 << 22) || ncmd == 0) return BGPU_E_INVALID;
+  P = make_params(9, 24, mode);
+  P.k.sh = 1;  // caller-supplied commands may hold 2- and 3-byte copies (Zopfli)
+  CK(cudaSetDevice(c->device));
+  const size_t lead = prev2 ? 256 : 0;
+  bgpu_tuning saved = c->tune; c->tune.shard_bytes = 1u << 22; c->tune.segment_bytes = 0xFFFFFFFFu; c->tune.metablock_bytes = 0;
+  size_t lens[1] = {n}; uint32_t pf[1] = {(prev2 ? 0u : BGPU_PART_FIRST) | BGPU_PART_LAST};
+  plan_job(c, P, lens, 1, job, pf, lead);
+  c->tune = saved;
+  ShardD& sh = job.shards[0];
+  sh.start_nbits = prev2 ? 0 : start_nbits; sh.start_value = start_value;   // a stage call with prev2 never opens the stream
+  job.mbs[0].is_last = is_last ? 1 : 0;
+  std::vector<uint8_t> role; std::vector<uint32_t> ins; std::vector<Cmd> cm; uint32_t counts[3];
+  if (roles_from_commands((const Cmd*)cmds_in, ncmd, n, P.k.sh, role, ins, cm, counts)) return BGPU_E_INVALID;
+  // validate the model against the symbol counts
+  uint32_t max_blocks = 1, max_types = 1;
+  for (int k = 0; k < 3; k++) {
+    const bgpu_block_split& sp = model->split[k];
+    if (sp.num_types < 1 || sp.num_types > 256 || sp.num_blocks > 65535u || (sp.num_blocks && (!sp.types || !sp.lengths))) return BGPU_E_INVALID;
+    uint64_t sum = 0;
+    for (uint32_t b = 0; b < sp.num_blocks; b++) { if (sp.types[b] >= sp.num_types || sp.lengths[b] == 0) return BGPU_E_INVALID; sum += sp.lengths[b]; }
+    // block-splitter.ts:419-421 counts the distance symbol of a trailing insert-only command whose prefix is >= 128
+    // although no distance is ever coded for it (metablock.ts:619, 741): the reference's last distance block is then
+    // one symbol longer than what the emit loop consumes; its declared length is what the header codes.
+    const Cmd& lastc = ((const Cmd*)cmds_in)[ncmd - 1];
+    const bool phantom = k == 2 && (lastc.copyLen & 0x1FFFFFF) == 0 && lastc.cmdPrefix >= 128;
+    if (sp.num_blocks && sum != counts[k] && !(phantom && sum == (uint64_t)counts[k] + 1)) return BGPU_E_INVALID;
+    if (!sp.num_blocks && sp.num_types != 1) return BGPU_E_INVALID;
+    max_blocks = std::max(max_blocks, sp.num_blocks); max_types = std::max(max_types, sp.num_types);
+  }
+  if (model->context_mode > 3) return BGPU_E_INVALID;
+  int rc;
+  if ((rc = c->in.reserve(job.in_bytes + IN_PAD))) return rc;
+  if ((rc = reserve_front(c, job, P))) return rc;
+  timing_begin(c);
+  uint8_t* d_in = c->in.as<uint8_t>();
+  if (lead) {
+    CK(cudaMemsetAsync(d_in, 0, lead, c->stream));
+    CK(cudaMemcpyAsync(d_in + lead - 2, prev2, 2, cudaMemcpyHostToDevice, c->stream));
+  }
+  CK(cudaMemcpyAsync(d_in + lead, in, n, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemsetAsync(d_in + lead + n, 0, job.in_bytes + IN_PAD - lead - n, c->stream));
+  const size_t slots = (n >> P.k.sh) + 2;
+  CK(cudaMemsetAsync(c->role.p, 0, lead, c->stream));
+  CK(cudaMemcpyAsync(c->role.as<uint8_t>() + lead, role.data(), n + IN_PAD - lead, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(c->ins.as<uint32_t>() + (lead >> P.k.sh), ins.data(), slots * 4, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(c->cmds.as<Cmd>() + (lead >> P.k.sh), cm.data(), slots * sizeof(Cmd), cudaMemcpyHostToDevice, c->stream));
+  if ((rc = upload_plan(c, job))) return rc;
+  if ((rc = full_setup(c, job, P, F, max_blocks + 1, max_types))) return rc;
+  if ((rc = full_symbols(c, P, d_in, F))) return rc;
+  // the caller's block lists and context mode take the place of full_split (parts B and C)
+  const MbModel& M = F.mp.models[0];
+  for (int k = 0; k < 3; k++) {
+    const bgpu_block_split& sp = model->split[k];
+    const uint32_t nb = sp.num_blocks ? sp.num_blocks : (counts[k] ? 1u : 0u);   // lengths may sum to counts[k] + 1 (phantom distance, above)
+    std::vector<uint32_t> bs(nb + 1, 0); std::vector<uint8_t> bt(std::max<uint32_t>(nb, 1), 0);
+    for (uint32_t b = 0; b < nb; b++) { bs[b + 1] = bs[b] + (sp.num_blocks ? sp.lengths[b] : counts[k]); bt[b] = sp.num_blocks ? sp.types[b] : 0; }
+    const uint32_t st3[3] = {0, nb, sp.num_types};
+    CK(cudaMemcpyAsync(M.blk_start[k], bs.data(), (nb + 1) * 4, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(M.blk_type[k], bt.data(), bt.size(), cudaMemcpyHostToDevice, c->stream));
+    CK(cudaMemcpyAsync(M.sstate[k], st3, sizeof st3, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaStreamSynchronize(c->stream));   // the staging vectors die with this iteration
+  }
+  const uint32_t zero = 0, cm_mode = (uint32_t)model->context_mode;
+  if (model->context_mode >= 0) CK(cudaMemcpyAsync(M.cnt + 3, &cm_mode, 4, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(M.cnt + 4, &zero, 4, cudaMemcpyHostToDevice, c->stream));   // never the trivial writer
+  CK(cudaStreamSynchronize(c->stream));
+  if ((rc = full_ctx_hist(c, F))) return rc;
+  *d_in_out = d_in;
+  return 0;
+}
+
+int bgpu_stage_histograms(bgpu_ctx* c, const uint8_t* in, size_t n, const void* cmds_in, size_t ncmd, int mode, const uint8_t* prev2,
+                          const bgpu_mb_model* model, uint32_t* lit_hist, uint32_t* cmd_hist, uint32_t* dist_hist, int* context_mode_out) {
+  Job job; EncParams P; FullBackend F; uint8_t* d_in = nullptr;
+  int rc = stage_full_front(c, in, n, cmds_in, ncmd, 1, mode, 0, 0, prev2, model, job, P, F, &d_in);
+  if (rc) return rc;
+  const MbModel& M = F.mp.models[0];
+  const uint32_t nt_l = model->split[0].num_types, nt_c = model->split[1].num_types, nt_d = model->split[2].num_types, da = P.k.dist_alphabet;
+  if (lit_hist) CK(cudaMemcpyAsync(lit_hist, M.ctx_hist[LIT], (size_t)nt_l * 64 * 256 * 4, cudaMemcpyDeviceToHost, c->stream));
+  if (cmd_hist) CK(cudaMemcpyAsync(cmd_hist, M.ctx_hist[CMD], (size_t)nt_c * ALPHA_CMD * 4, cudaMemcpyDeviceToHost, c->stream));
+  std::vector<uint32_t> dh((size_t)nt_d * 4 * ALPHA_DIST_MAX);
+  CK(cudaMemcpyAsync(dh.data(), M.ctx_hist[DIST], dh.size() * 4, cudaMemcpyDeviceToHost, c->stream));
+  uint32_t cm_mode = 0;
+  CK(cudaMemcpyAsync(&cm_mode, M.cnt + 3, 4, cudaMemcpyDeviceToHost, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  timing_end(c);
+  if (dist_hist) for (size_t r = 0; r < (size_t)nt_d * 4; r++) memcpy(dist_hist + r * da, dh.data() + r * ALPHA_DIST_MAX, da * 4);
+  if (context_mode_out) *context_mode_out = (int)cm_mode;
+  return 0;
+}
+
+int bgpu_stage_store_metablock(bgpu_ctx* c, const uint8_t* in, size_t n, const void* cmds_in, size_t ncmd, int is_last, int mode,
+                               unsigned start_nbits, unsigned start_value, const uint8_t* prev2, const bgpu_mb_model* model,
+                               uint8_t* out, size_t out_cap, size_t* out_len) {
+  if (!out_len || !model || !model->literal_context_map || !model->distance_context_map) return BGPU_E_INVALID;
+  if (model->num_literal_clusters < 1 || model->num_literal_clusters > MAX_CTX_CLUSTERS || model->num_distance_clusters < 1 ||
+      model->num_distance_clusters > MAX_CTX_CLUSTERS)
+    return BGPU_E_INVALID;
+  const size_t nlm = (size_t)model->split[0].num_types * 64, ndm = (size_t)model->split[2].num_types * 4;
+  for (size_t i = 0; i < nlm && nlm <= 256 * 64; i++) if (model->literal_context_map[i] >= model->num_literal_clusters) return BGPU_E_INVALID;
+  for (size_t i = 0; i < ndm && ndm <= 256 * 4; i++) if (model->distance_context_map[i] >= model->num_distance_clusters) return BGPU_E_INVALID;
+  Job job; EncParams P; FullBackend F; uint8_t* d_in = nullptr;
+  int rc = stage_full_front(c, in, n, cmds_in, ncmd, is_last, mode, start_nbits, start_value, prev2, model, job, P, F, &d_in);
+  if (rc) return rc;
+  // the caller's context maps take the place of full_ctx_cluster (part D2): ClusterProb.sym / state[2]
+  const ClusterProb& XL = F.mp.cx[0]; const ClusterProb& XD = F.mp.cx[1];
+  CK(cudaMemcpyAsync(XL.sym, model->literal_context_map, nlm * 4, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(XL.state + 2, &model->num_literal_clusters, 4, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(XD.sym, model->distance_context_map, ndm * 4, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemcpyAsync(XD.state + 2, &model->num_distance_clusters, 4, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaStreamSynchronize(c->stream));
+  if ((rc = full_emit(c, P, d_in, F))) return rc;
+  uint8_t* outs[1] = {out}; size_t caps[1] = {out_cap};
+  rc = collect(c, job, outs, caps, out_len, nullptr, 1);
+  timing_end(c);
+  return rc;
+}
+
+int bgpu_stage_context_map(bgpu_ctx* c, const uint32_t* map, size_t size, uint32_t num_clusters, uint8_t* bits, size_t cap_bytes, uint64_t* nbits) {
+  if (!c || !map || !bits || !nbits || size == 0 || size > 256 * 64 || num_clusters < 1 || num_clusters > 256) return BGPU_E_INVALID;
+  for (size_t i = 0; i < size; i++) if (map[i] >= num_clusters) return BGPU_E_INVALID;
+  CK(cudaSetDevice(c->device));
+  const size_t words = size + 1024;   // <= 8 + 6 bits per entry + one prefix code
+  DBuf dm, ds, dout, dn;
+  auto done = [&](int r) { dm.release(); ds.release(); dout.release(); dn.release(); return r; };
+  int rc;
+  if ((rc = dm.reserve(size * 4)) || (rc = ds.reserve(size * 4)) || (rc = dout.reserve(words * 4)) || (rc = dn.reserve(16))) return done(rc);
+  cudaError_t e = cudaMemcpyAsync(dm.p, map, size * 4, cudaMemcpyHostToDevice, c->stream);
+  if (e == cudaSuccess) e = cudaMemsetAsync(dout.p, 0, words * 4, c->stream);
+  uint32_t nb = 0; std::vector<uint8_t> host(words * 4);
+  if (e == cudaSuccess) {
+    k_stage_context_map<<<1, 32, 0, c->stream>>>(dm.as<uint32_t>(), (uint32_t)size, num_clusters, ds.as<uint32_t>(), dout.as<uint32_t>(), dn.as<uint32_t>());
+    e = cudaMemcpyAsync(&nb, dn.p, 4, cudaMemcpyDeviceToHost, c->stream);
+  }
+  if (e == cudaSuccess) e = cudaMemcpyAsync(host.data(), dout.p, words * 4, cudaMemcpyDeviceToHost, c->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+  if (e != cudaSuccess) { g_cuda_err = cudaGetErrorString(e); return done(BGPU_E_CUDA); }
+  *nbits = nb;
+  const size_t need = ((size_t)nb + 7) >> 3;
+  if (need > cap_bytes) return done(BGPU_E_OUTPUT_TOO_SMALL);
+  memcpy(bits, host.data(), need);
+  return done(0);
 }
 
 int bgpu_stage_huffman(bgpu_ctx* c, const uint32_t* hist, int count, int alphabet, uint8_t* depths, uint16_t* bits, uint8_t* tree_bits,

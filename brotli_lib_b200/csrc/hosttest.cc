@@ -35,6 +35,14 @@ void bgpu_hosttest_make_insert_cmd(uint32_t insertLen, Cmd* out) { *out = make_i
 uint32_t bgpu_hosttest_distance_of_explicit(uint32_t distPrefix, uint32_t distExtra, uint32_t ndirect, uint32_t npostfix) {
   return distance_of_explicit(distPrefix, distExtra, ndirect, npostfix);
 }
+// encodeContextMap (context-map.ts:114-170) exactly as k_mb_header / k_stage_context_map run it.  words: zeroed, size + 1024.
+uint32_t bgpu_hosttest_context_map(const uint32_t* cmap, uint32_t size, uint32_t ncl, uint32_t* words) {
+  std::vector<uint32_t> scratch(size + 1);
+  static SerialHuff S;
+  BitSink w{words, 0};
+  encode_context_map(w, S, cmap, size, ncl, scratch.data());
+  return w.pos;
+}
 uint32_t bgpu_hosttest_cmd_extra(uint32_t insertLen, uint32_t copyLenField, uint64_t* value) { return cmd_extra(insertLen, copyLenField, value); }
 
 }

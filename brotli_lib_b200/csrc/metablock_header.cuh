@@ -15,85 +15,14 @@ __device__ __forceinline__ uint32_t block_len_code(uint32_t len) {   // metabloc
   while (code < 25 && len >= c_blen_offset[code + 1]) code++;
   return code;
 }
-__device__ __forceinline__ void put_varlen8(BitSink& w, uint32_t n) {  // context-map.ts:524-533
-  if (n == 0) { w.put(1, 0); return; }
-  const uint32_t nbits = log2_floor(n);
-  w.put(1, 1); w.put(3, nbits); w.put(nbits, n - (1u << nbits));
-}
-
-constexpr int SH_MAX = 272;   // largest alphabet built serially: block types + 2 <= 258
-struct SerialHuff {
-  uint16_t sorted[SH_MAX]; uint32_t cnt[2 * SH_MAX + 2]; uint16_t lt[2 * SH_MAX + 2], rt[2 * SH_MAX + 2];
-  uint8_t nd[2 * SH_MAX + 2]; uint8_t rs[SH_MAX + 8], re[SH_MAX + 8];
-  uint32_t hist[SH_MAX]; uint8_t depth[SH_MAX]; uint16_t bits[SH_MAX];
-};
-// buildAndStoreHuffmanTree (context-map.ts:215-264) of S.hist, one thread.
-__device__ void huff_serial_store(BitSink& w, SerialHuff& S, int alphabet) {
-  uint16_t s4[4] = {0, 0, 0, 0}; int n = 0;
-  for (int i = 0; i < alphabet; i++) { S.depth[i] = 0; S.bits[i] = 0; if (S.hist[i]) { if (n < 4) s4[n] = (uint16_t)i; n++; } }
-  if (n <= 1) { tree_store_single(w, alphabet, s4[0]); return; }
-  for (uint32_t limit = 1;; limit *= 2) {
-    huff_sort_serial(S.hist, alphabet, limit, S.sorted);
-    if (huff_depths_from_sorted(S.hist, S.sorted, n, limit, 15, S.cnt, S.lt, S.rt, S.nd, S.depth)) break;
-    for (int i = 0; i < alphabet; i++) S.depth[i] = 0;
-  }
-  huff_codes(S.depth, alphabet, S.bits);
-  tree_store(w, S.depth, alphabet, n, s4, S.rs, S.re);
-}
-
-// encodeContextMap (context-map.ts:114-170).  scratch: `size` u32.
-__device__ void encode_context_map(BitSink& w, SerialHuff& S, const uint32_t* cmap, uint32_t size, uint32_t ncl, uint32_t* scratch) {
-  put_varlen8(w, ncl - 1);
-  if (ncl == 1) return;
-  // moveToFrontTransform (:13-50)
-  uint8_t mtf[256];
-  uint32_t maxv = 0;
-  for (uint32_t i = 0; i < size; i++) maxv = max(maxv, cmap[i]);
-  for (uint32_t i = 0; i <= maxv; i++) mtf[i] = (uint8_t)i;
-  for (uint32_t i = 0; i < size; i++) {
-    const uint32_t v = cmap[i]; uint32_t idx = 0;
-    while (mtf[idx] != v) idx++;
-    scratch[i] = idx;
-    for (uint32_t j = idx; j > 0; j--) mtf[j] = mtf[j - 1];
-    mtf[0] = (uint8_t)v;
-  }
-  // runLengthCodeZeros (:55-111), in place (the output never overtakes the input)
-  uint32_t maxReps = 0;
-  for (uint32_t i = 0; i < size;) {
-    uint32_t reps = 0;
-    while (i < size && scratch[i] != 0) i++;
-    while (i < size && scratch[i] == 0) { reps++; i++; }
-    maxReps = max(maxReps, reps);
-  }
-  uint32_t maxPrefix = maxReps > 0 ? (uint32_t)log2_floor(maxReps) : 0;
-  maxPrefix = min(maxPrefix, 6u);
-  uint32_t nout = 0;
-  for (uint32_t i = 0; i < size;) {
-    if (scratch[i] != 0) { scratch[nout++] = scratch[i] + maxPrefix; i++; }
-    else {
-      uint32_t reps = 1;
-      for (uint32_t k = i + 1; k < size && scratch[k] == 0; k++) reps++;
-      i += reps;
-      while (reps != 0) {
-        if (reps < (2u << maxPrefix)) { const uint32_t pfx = log2_floor(reps); scratch[nout++] = pfx | ((reps - (1u << pfx)) << 9); break; }
-        scratch[nout++] = maxPrefix | (((1u << maxPrefix) - 1) << 9);
-        reps -= (2u << maxPrefix) - 1;
-      }
-    }
-  }
-  const int alphabet = (int)(ncl + maxPrefix);
-  for (int i = 0; i < alphabet; i++) S.hist[i] = 0;
-  for (uint32_t i = 0; i < nout; i++) S.hist[scratch[i] & 511]++;
-  const bool useRle = maxPrefix > 0;
-  w.put(1, useRle ? 1 : 0);
-  if (useRle) w.put(4, maxPrefix - 1);
-  huff_serial_store(w, S, alphabet);
-  for (uint32_t i = 0; i < nout; i++) {
-    const uint32_t sym = scratch[i] & 511, extra = scratch[i] >> 9;
-    w.put(S.depth[sym], S.bits[sym]);
-    if (sym > 0 && sym <= maxPrefix) w.put(sym, extra);
-  }
-  w.put(1, 1);   // IMTF
+// encodeContextMap alone (bgpu_stage_context_map): the same device function k_mb_header calls.  out must be zeroed.
+__global__ void __launch_bounds__(32) k_stage_context_map(const uint32_t* __restrict__ cmap, uint32_t size, uint32_t ncl, uint32_t* scratch,
+                                                          uint32_t* __restrict__ out, uint32_t* __restrict__ nbits) {
+  __shared__ SerialHuff S;
+  if (threadIdx.x != 0) return;
+  BitSink w{out, 0};
+  encode_context_map(w, S, cmap, size, ncl, scratch);
+  *nbits = w.pos;
 }
 
 // One CTA per metablock; thread 0 does the serial work.  M.misc must be zeroed.

@@ -169,6 +169,61 @@ class Context:
         return d, b, tb, tn
 
 
+    # full-metablock stages: `model` is a dict {"context_mode", "splits": [(num_types, types u8[], lengths u32[]) x 3],
+    # "literal_map", "literal_clusters", "distance_map", "distance_clusters"} (include/brotligpu.h bgpu_mb_model)
+    def _mb_model(self, model):
+        keep = []
+        m = _lib.MbModel()
+        for k, (nt, types, lengths) in enumerate(model["splits"]):
+            t = np.ascontiguousarray(types, dtype=np.uint8)
+            ln = np.ascontiguousarray(lengths, dtype=np.uint32)
+            keep += [t, ln]
+            m.split[k].num_types = int(nt); m.split[k].num_blocks = int(t.size)
+            m.split[k].types = _ptr(t); m.split[k].lengths = _ptr(ln)
+        m.context_mode = int(model.get("context_mode", -1))
+        lm = np.ascontiguousarray(model.get("literal_map", np.zeros(0)), dtype=np.uint32)
+        dm = np.ascontiguousarray(model.get("distance_map", np.zeros(0)), dtype=np.uint32)
+        keep += [lm, dm]
+        m.literal_context_map = _ptr(lm); m.num_literal_clusters = int(model.get("literal_clusters", 1))
+        m.distance_context_map = _ptr(dm); m.num_distance_clusters = int(model.get("distance_clusters", 1))
+        return m, keep
+
+    def stage_histograms(self, data, cmds, model, mode=0, prev2=None):
+        """(lit [types*64][256], cmd [types][704], dist [types*4][A], context_mode): metablock.ts:558-637 on the device."""
+        a = _as_u8(data)
+        cm = np.ascontiguousarray(cmds, dtype=CMD_DTYPE)
+        m, keep = self._mb_model(model)
+        da = 124 if int(mode) == 2 else 64
+        lh = np.zeros((m.split[0].num_types * 64, 256), dtype=np.uint32)
+        ch = np.zeros((m.split[1].num_types, 704), dtype=np.uint32)
+        dh = np.zeros((m.split[2].num_types * 4, da), dtype=np.uint32)
+        pv = _as_u8(prev2) if prev2 is not None else None
+        cmode = C.c_int(-1)
+        _lib.check(self._L.bgpu_stage_histograms(self._h, _ptr(a), a.size, cm.ctypes.data, cm.size, int(mode), _ptr(pv) if pv is not None else None,
+                                                 C.byref(m), lh.ctypes.data, ch.ctypes.data, dh.ctypes.data, C.byref(cmode)))
+        return lh, ch, dh, cmode.value
+
+    def stage_context_map(self, cmap, num_clusters):
+        """(bytes, nbits) of encodeContextMap (context-map.ts:114-170) on the device."""
+        mp = np.ascontiguousarray(cmap, dtype=np.uint32)
+        out = np.zeros(mp.size * 4 + 4096, dtype=np.uint8)
+        nb = C.c_uint64(0)
+        _lib.check(self._L.bgpu_stage_context_map(self._h, mp.ctypes.data, mp.size, int(num_clusters), out.ctypes.data, out.size, C.byref(nb)))
+        return out[: (nb.value + 7) // 8].tobytes(), nb.value
+
+    def stage_store_metablock(self, data, cmds, model, is_last=True, mode=0, start_nbits=0, start_value=0, prev2=None):
+        a = _as_u8(data)
+        cm = np.ascontiguousarray(cmds, dtype=CMD_DTYPE)
+        m, keep = self._mb_model(model)
+        cap = self._L.bgpu_max_compressed_size(a.size) + 65536
+        out = np.zeros(cap, dtype=np.uint8)
+        n = C.c_size_t(0)
+        pv = _as_u8(prev2) if prev2 is not None else None
+        _lib.check(self._L.bgpu_stage_store_metablock(self._h, _ptr(a), a.size, cm.ctypes.data, cm.size, int(is_last), int(mode), start_nbits, start_value,
+                                                      _ptr(pv) if pv is not None else None, C.byref(m), out.ctypes.data, cap, C.byref(n)))
+        return out[: n.value].tobytes()
+
+
 CMD_DTYPE = np.dtype([("insertLen", "<u4"), ("copyLen", "<u4"), ("distExtra", "<u4"), ("cmdPrefix", "<u2"), ("distPrefix", "<u2")])
 TRIVIAL_DTYPE = np.dtype([("litHisto", "<u4", 256), ("cmdHisto", "<u4", 704), ("distHisto", "<u4", 544),
                           ("litDepths", "u1", 256), ("cmdDepths", "u1", 704), ("distDepths", "u1", 544),

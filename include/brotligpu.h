@@ -143,6 +143,45 @@ int bgpu_stage_store_trivial(bgpu_ctx* ctx, const uint8_t* in, size_t n, const v
 int bgpu_stage_huffman(bgpu_ctx* ctx, const uint32_t* hist, int count, int alphabet,
                        uint8_t* depths, uint16_t* bits, uint8_t* tree_bits, uint32_t* tree_nbits);
 
+/* ---- full-metablock stages (storeMetaBlock, src/encode/metablock.ts:504-761), cut at the model boundary ----
+ * The float-driven decisions (block splits block-splitter.ts:394-464, context maps metablock.ts:763-797) are INPUTS
+ * here, so that the integer stages behind them can be compared bit for bit with the reference's on identical inputs. */
+typedef struct bgpu_block_split {       /* block-splitter.ts BlockSplit */
+  uint32_t num_types, num_blocks;       /* num_blocks == 0: one implicit block of type 0 */
+  const uint8_t* types;                 /* [num_blocks] */
+  const uint32_t* lengths;              /* [num_blocks], summing to the category's symbol count */
+} bgpu_block_split;
+typedef struct bgpu_mb_model {
+  bgpu_block_split split[3];            /* literal, command, distance */
+  int context_mode;                     /* context.ts ContextMode 0..3; -1: chooseContextMode (context.ts:179-227) on the device */
+  const uint32_t* literal_context_map;  /* [split[0].num_types * 64] cluster of every (block type, context) */
+  uint32_t num_literal_clusters;        /* <= 64 (metablock.ts:789) */
+  const uint32_t* distance_context_map; /* [split[2].num_types * 4] */
+  uint32_t num_distance_clusters;
+} bgpu_mb_model;
+
+/* Per-context BuildHistograms of storeMetaBlock            src/encode/metablock.ts:558-637
+ * One metablock = the whole input (n <= 4 MiB) under the caller's commands, block splits and context mode (the maps of
+ * `model` are not read).  prev2 (may be NULL = stream start, contexts 0, 0) holds the two bytes before `in`.
+ * lit_hist [split[0].num_types * 64][256], cmd_hist [split[1].num_types][704], dist_hist [split[2].num_types * 4][A]
+ * with A = 64 (GENERIC/TEXT) or 124 (FONT); *context_mode_out (optional) the mode used. */
+int bgpu_stage_histograms(bgpu_ctx* ctx, const uint8_t* in, size_t n, const void* cmds, size_t ncmd, int mode, const uint8_t* prev2,
+                          const bgpu_mb_model* model, uint32_t* lit_hist, uint32_t* cmd_hist, uint32_t* dist_hist, int* context_mode_out);
+
+/* encodeContextMap (moveToFront + zero-run RLE + prefix code)   src/encode/context-map.ts:114-170
+ * map: `size` cluster ids < num_clusters (<= 256); bits: LSB-first output, cap_bytes large; *nbits the bit count. */
+int bgpu_stage_context_map(bgpu_ctx* ctx, const uint32_t* map, size_t size, uint32_t num_clusters, uint8_t* bits, size_t cap_bytes,
+                           uint64_t* nbits);
+
+/* storeMetaBlock emit: header, block-split codes, context maps, prefix codes, commands with block switches
+ * src/encode/metablock.ts:651-760 (BlockEncoder :392-501, buildAndStoreBlockSplitCode :161-202, storeBlockSwitch :204-220)
+ * on caller-supplied commands + splits + context mode + context maps; histograms and prefix codes are derived on the
+ * device exactly as the default bgpu_encode path derives them (same kernels).  start_nbits/start_value as in
+ * bgpu_stage_store_trivial; prev2 as in bgpu_stage_histograms. */
+int bgpu_stage_store_metablock(bgpu_ctx* ctx, const uint8_t* in, size_t n, const void* cmds, size_t ncmd, int is_last, int mode,
+                               unsigned start_nbits, unsigned start_value, const uint8_t* prev2, const bgpu_mb_model* model,
+                               uint8_t* out, size_t out_cap, size_t* out_len);
+
 /* BinaryTreeHasher.findAllMatches for every position    src/encode/hash-binary-tree.ts:57-227
  * (17-bit buckets, <= 64 tree levels, 128-byte tree compare, 63-position short scan), called in
  * position order with maxLength = n - p and maxBackward = min(p, 4 MiB - 16) as pass 0 of

@@ -329,6 +329,91 @@ int oracle_store_trivial(const uint8_t* in, size_t n, const Command* cmds, size_
   return 0;
 }
 
+// ---- full-metablock stage entry points (metablock.ts:504-761 cut at the model boundary) ----
+// Flat model layout shared with the tests: hdr[0] context mode, hdr[1..3] numTypes (literal, command,
+// distance), hdr[4..6] numBlocks, hdr[7] literal clusters, hdr[8] distance clusters; types / lengths hold
+// three runs of cap_blocks entries; lit_map has numTypes[0] * 64 entries, dist_map numTypes[2] * 4.
+static void FlatToModel(const uint32_t* hdr, const uint8_t* types, const uint32_t* lengths, size_t cap, const uint32_t* lit_map,
+                        const uint32_t* dist_map, MetaBlockModel& M) {
+  BlockSplit* sp[3] = {&M.literalSplit, &M.commandSplit, &M.distanceSplit};
+  M.contextMode = (int)hdr[0];
+  for (int c = 0; c < 3; c++) {
+    sp[c]->numTypes = hdr[1 + c]; sp[c]->numBlocks = hdr[4 + c];
+    sp[c]->types.assign(types + c * cap, types + c * cap + hdr[4 + c]);
+    sp[c]->lengths.assign(lengths + c * cap, lengths + c * cap + hdr[4 + c]);
+  }
+  M.numLiteralClusters = hdr[7]; M.numDistanceClusters = hdr[8];
+  if (lit_map) M.literalContextMap.assign(lit_map, lit_map + (size_t)hdr[1] * 64);
+  if (dist_map) M.distanceContextMap.assign(dist_map, dist_map + (size_t)hdr[3] * 4);
+}
+
+// splitBlock + chooseContextMode + histograms + context-map clustering of ONE metablock = the whole input.
+// Returns 1 when the reference would store the metablock trivially (no model), -1 when cap_blocks is too small.
+int oracle_metablock_model(const uint8_t* in, size_t n, const Command* cmds, size_t ncmd, int quality, int mode_font, int prev1, int prev2,
+                           uint32_t* hdr, uint8_t* types, uint32_t* lengths, size_t cap_blocks, uint32_t* lit_map, uint32_t* dist_map) {
+  uint32_t npostfix = mode_font ? 1 : 0, ndirect = mode_font ? 12 : 0;
+  std::vector<Command> commands(cmds, cmds + ncmd);
+  MetaBlockModel M;
+  if (!ComputeMetaBlockModel(Bytes{in, n}, 0, n, ~(size_t)0, commands, 16 + ndirect + (48u << npostfix), quality, (uint8_t)prev1, (uint8_t)prev2, M)) return 1;
+  const BlockSplit* sp[3] = {&M.literalSplit, &M.commandSplit, &M.distanceSplit};
+  hdr[0] = (uint32_t)M.contextMode; hdr[7] = M.numLiteralClusters; hdr[8] = M.numDistanceClusters;
+  for (int c = 0; c < 3; c++) {
+    hdr[1 + c] = sp[c]->numTypes; hdr[4 + c] = sp[c]->numBlocks;
+    if (sp[c]->numBlocks > cap_blocks) return -1;
+    for (uint32_t b = 0; b < sp[c]->numBlocks; b++) { types[c * cap_blocks + b] = sp[c]->types[b]; lengths[c * cap_blocks + b] = sp[c]->lengths[b]; }
+  }
+  memcpy(lit_map, M.literalContextMap.data(), M.literalContextMap.size() * 4);
+  memcpy(dist_map, M.distanceContextMap.data(), M.distanceContextMap.size() * 4);
+  return 0;
+}
+
+// metablock.ts:558-637 alone, under caller-supplied splits and context mode.  lit_hist [numTypes[0] * 64][256],
+// cmd_hist [numTypes[1]][704], dist_hist [numTypes[2] * 4][64 | 124].
+int oracle_context_histograms(const uint8_t* in, size_t n, const Command* cmds, size_t ncmd, int mode_font, int prev1, int prev2,
+                              const uint32_t* hdr, const uint8_t* types, const uint32_t* lengths, size_t cap_blocks,
+                              uint32_t* lit_hist, uint32_t* cmd_hist, uint32_t* dist_hist) {
+  uint32_t npostfix = mode_font ? 1 : 0, ndirect = mode_font ? 12 : 0, da = 16 + ndirect + (48u << npostfix);
+  std::vector<Command> commands(cmds, cmds + ncmd);
+  MetaBlockModel M; FlatToModel(hdr, types, lengths, cap_blocks, nullptr, nullptr, M);
+  BuildContextHistograms(in, 0, n, ~(size_t)0, commands, da, (uint8_t)prev1, (uint8_t)prev2, M);
+  for (size_t i = 0; i < M.literalHistograms.size(); i++) memcpy(lit_hist + i * 256, M.literalHistograms[i].data(), 256 * 4);
+  for (size_t i = 0; i < M.commandHistograms.size(); i++) memcpy(cmd_hist + i * 704, M.commandHistograms[i].data(), 704 * 4);
+  for (size_t i = 0; i < M.distanceHistograms.size(); i++) memcpy(dist_hist + i * da, M.distanceHistograms[i].data(), da * 4);
+  return 0;
+}
+
+// metablock.ts:651-760: the full-metablock writer on caller-supplied commands, splits, context mode and context
+// maps (histograms and prefix codes are re-derived from them, as storeMetaBlock does), preceded by start_nbits header bits.
+int oracle_store_metablock(const uint8_t* in, size_t n, const Command* cmds, size_t ncmd, int is_last, int mode_font,
+                           unsigned start_nbits, unsigned start_value, int prev1, int prev2,
+                           const uint32_t* hdr, const uint8_t* types, const uint32_t* lengths, size_t cap_blocks,
+                           const uint32_t* lit_map, const uint32_t* dist_map, uint8_t* out, size_t cap, size_t* out_len, uint64_t* out_bits) {
+  uint32_t npostfix = mode_font ? 1 : 0, ndirect = mode_font ? 12 : 0, da = 16 + ndirect + (48u << npostfix);
+  std::vector<Command> commands(cmds, cmds + ncmd);
+  MetaBlockModel M; FlatToModel(hdr, types, lengths, cap_blocks, lit_map, dist_map, M);
+  BuildContextHistograms(in, 0, n, ~(size_t)0, commands, da, (uint8_t)prev1, (uint8_t)prev2, M);
+  BitWriter w(n + n / 2 + 65536);
+  w.writeBits(start_nbits, start_value);
+  EmitMetaBlock(w, in, 0, n, ~(size_t)0, is_last != 0, commands, da, npostfix, ndirect, (uint8_t)prev1, (uint8_t)prev2, M);
+  *out_bits = w.pos;
+  std::vector<uint8_t> v = w.finish();
+  *out_len = v.size();
+  if (v.size() > cap) return -1;
+  memcpy(out, v.data(), v.size());
+  return 0;
+}
+
+// encodeContextMap alone (context-map.ts:114-170).
+int oracle_encode_context_map(const uint32_t* map, size_t size, uint32_t num_clusters, uint8_t* out, size_t cap, uint64_t* out_bits) {
+  BitWriter w(size * 4 + 1024);
+  EncodeContextMap(w, map, size, num_clusters);
+  *out_bits = w.pos;
+  std::vector<uint8_t> v = w.finish();
+  if (v.size() > cap) return -1;
+  memcpy(out, v.data(), v.size());
+  return 0;
+}
+
 int oracle_huffman(const uint32_t* hist, size_t n, int tree_limit, uint8_t* depths, uint16_t* bits) {
   CreateHuffmanTree(hist, n, tree_limit, depths, bits);
   return 0;

@@ -222,30 +222,28 @@ static inline std::vector<std::vector<uint32_t>> BuildClusteredHistograms(const 
 
 struct MetaBlockStats { bool trivial = true; uint32_t litTypes = 1, cmdTypes = 1, distTypes = 1, litClusters = 1, distClusters = 1; int contextMode = 0; };
 
-// metablock.ts:504-761.  prev1/prev2: literal-context bytes before startPos (0,0 in the TS;
-// a stitched shard k>0 passes the true preceding bytes, SURVEY §8e rule 4).
-static inline void StoreMetaBlock(BitWriter& w, const Bytes& data, size_t startPos, size_t length, size_t mask, bool isLast,
-                                  const std::vector<Command>& commands, uint32_t distAlphabetSize, int quality,
-                                  uint32_t npostfix, uint32_t ndirect, uint8_t prev1 = 0, uint8_t prev2 = 0,
-                                  MetaBlockStats* stats = nullptr) {
-  const uint8_t* input = data.p;
-  if (length < 128 || quality < 5 || commands.size() < 6) {
-    StoreMetaBlockTrivial(w, input, startPos, length, mask, isLast, commands, distAlphabetSize, npostfix, ndirect);
-    return;
-  }
+// Everything storeMetaBlock decides before it writes a bit (metablock.ts:527-661): the three block
+// splits, the context mode, the per-(block type, context) histograms and the two context maps.
+// Stage-parity tests hand this to the GPU writer so that both sides emit from identical inputs.
+struct MetaBlockModel {
   BlockSplit literalSplit, commandSplit, distanceSplit;
-  SplitBlock(commands, input, startPos, mask, quality, literalSplit, commandSplit, distanceSplit);
-  if (literalSplit.numTypes <= 1 && commandSplit.numTypes <= 1 && distanceSplit.numTypes <= 1) {
-    StoreMetaBlockTrivial(w, input, startPos, length, mask, isLast, commands, distAlphabetSize, npostfix, ndirect);
-    return;
-  }
-  int contextMode = ChooseContextMode(data, startPos, std::min<size_t>(length, 4096));
-  const uint8_t* lut = GetContextLut(contextMode);
+  int contextMode = 0;
+  std::vector<std::vector<uint32_t>> literalHistograms, commandHistograms, distanceHistograms;
+  std::vector<uint32_t> literalContextMap, distanceContextMap;
+  uint32_t numLiteralClusters = 1, numDistanceClusters = 1;
+};
+
+// metablock.ts:558-637: per-context histograms of the commands under the model's splits and context mode.
+static inline void BuildContextHistograms(const uint8_t* input, size_t startPos, size_t length, size_t mask,
+                                          const std::vector<Command>& commands, uint32_t distAlphabetSize,
+                                          uint8_t prev1, uint8_t prev2, MetaBlockModel& M) {
+  const BlockSplit& literalSplit = M.literalSplit; const BlockSplit& commandSplit = M.commandSplit; const BlockSplit& distanceSplit = M.distanceSplit;
+  const uint8_t* lut = GetContextLut(M.contextMode);
   size_t numLiteralContexts = (size_t)literalSplit.numTypes * 64;
-  std::vector<std::vector<uint32_t>> literalHistograms(numLiteralContexts, std::vector<uint32_t>(256, 0));
-  std::vector<std::vector<uint32_t>> commandHistograms(commandSplit.numTypes, std::vector<uint32_t>(704, 0));
+  M.literalHistograms.assign(numLiteralContexts, std::vector<uint32_t>(256, 0));
+  M.commandHistograms.assign(commandSplit.numTypes, std::vector<uint32_t>(704, 0));
   size_t numDistanceContexts = (size_t)distanceSplit.numTypes * 4;
-  std::vector<std::vector<uint32_t>> distanceHistograms(numDistanceContexts, std::vector<uint32_t>(distAlphabetSize, 0));
+  M.distanceHistograms.assign(numDistanceContexts, std::vector<uint32_t>(distAlphabetSize, 0));
 
   size_t pos = startPos;
   size_t litBlockIdx = 0; uint32_t litBlockLen = literalSplit.numBlocks > 0 ? literalSplit.lengths[0] : (uint32_t)length;
@@ -259,7 +257,7 @@ static inline void StoreMetaBlock(BitWriter& w, const Bytes& data, size_t startP
     while (cmdCount >= cmdBlockLen && cmdBlockIdx + 1 < commandSplit.numBlocks) {
       cmdBlockIdx++; cmdBlockType = commandSplit.types[cmdBlockIdx]; cmdBlockLen = commandSplit.lengths[cmdBlockIdx]; cmdCount = 0;
     }
-    commandHistograms[cmdBlockType][cmd.cmdPrefix]++;
+    M.commandHistograms[cmdBlockType][cmd.cmdPrefix]++;
     cmdCount++;
     for (uint32_t j = 0; j < cmd.insertLen; j++) {
       while (litCount >= litBlockLen && litBlockIdx + 1 < literalSplit.numBlocks) {
@@ -267,7 +265,7 @@ static inline void StoreMetaBlock(BitWriter& w, const Bytes& data, size_t startP
       }
       uint8_t literal = input[(pos + j) & mask];
       uint32_t context = GetContext(prevByte1, prevByte2, lut);
-      literalHistograms[litBlockType * 64 + context][literal]++;
+      M.literalHistograms[litBlockType * 64 + context][literal]++;
       litCount++;
       prevByte2 = prevByte1; prevByte1 = literal;
     }
@@ -278,7 +276,7 @@ static inline void StoreMetaBlock(BitWriter& w, const Bytes& data, size_t startP
         distBlockIdx++; distBlockType = distanceSplit.types[distBlockIdx]; distBlockLen = distanceSplit.lengths[distBlockIdx]; distCount = 0;
       }
       uint32_t distContext = copyLen > 4 ? 3 : copyLen - 2;
-      distanceHistograms[distBlockType * 4 + distContext][cmd.distPrefix & 0x3FF]++;
+      M.distanceHistograms[distBlockType * 4 + distContext][cmd.distPrefix & 0x3FF]++;
       distCount++;
     }
     if (copyLen > 0) {
@@ -288,16 +286,34 @@ static inline void StoreMetaBlock(BitWriter& w, const Bytes& data, size_t startP
     }
     pos += copyLen;
   }
-  std::vector<uint32_t> literalContextMap(numLiteralContexts, 0), distanceContextMap(numDistanceContexts, 0);
-  uint32_t numLiteralClusters = ClusterAndBuildContextMap(literalHistograms, numLiteralContexts, 256, literalContextMap);
-  uint32_t numDistanceClusters = ClusterAndBuildContextMap(distanceHistograms, numDistanceContexts, distAlphabetSize, distanceContextMap);
-  auto clusteredLit = BuildClusteredHistograms(literalHistograms, literalContextMap, numLiteralClusters, 256);
-  auto clusteredDist = BuildClusteredHistograms(distanceHistograms, distanceContextMap, numDistanceClusters, distAlphabetSize);
-  if (stats) {
-    stats->trivial = false; stats->litTypes = literalSplit.numTypes; stats->cmdTypes = commandSplit.numTypes;
-    stats->distTypes = distanceSplit.numTypes; stats->litClusters = numLiteralClusters; stats->distClusters = numDistanceClusters;
-    stats->contextMode = contextMode;
-  }
+}
+
+// metablock.ts:527-661.  Returns false when the metablock takes the trivial writer (:518, :531).
+static inline bool ComputeMetaBlockModel(const Bytes& data, size_t startPos, size_t length, size_t mask,
+                                         const std::vector<Command>& commands, uint32_t distAlphabetSize, int quality,
+                                         uint8_t prev1, uint8_t prev2, MetaBlockModel& M) {
+  if (length < 128 || quality < 5 || commands.size() < 6) return false;
+  SplitBlock(commands, data.p, startPos, mask, quality, M.literalSplit, M.commandSplit, M.distanceSplit);
+  if (M.literalSplit.numTypes <= 1 && M.commandSplit.numTypes <= 1 && M.distanceSplit.numTypes <= 1) return false;
+  M.contextMode = ChooseContextMode(data, startPos, std::min<size_t>(length, 4096));
+  BuildContextHistograms(data.p, startPos, length, mask, commands, distAlphabetSize, prev1, prev2, M);
+  size_t numLiteralContexts = (size_t)M.literalSplit.numTypes * 64, numDistanceContexts = (size_t)M.distanceSplit.numTypes * 4;
+  M.literalContextMap.assign(numLiteralContexts, 0); M.distanceContextMap.assign(numDistanceContexts, 0);
+  M.numLiteralClusters = ClusterAndBuildContextMap(M.literalHistograms, numLiteralContexts, 256, M.literalContextMap);
+  M.numDistanceClusters = ClusterAndBuildContextMap(M.distanceHistograms, numDistanceContexts, distAlphabetSize, M.distanceContextMap);
+  return true;
+}
+
+// metablock.ts:651-760: header, block-split codes, context maps, prefix codes and the emit loop, from a
+// model whose histograms are already built.
+static inline void EmitMetaBlock(BitWriter& w, const uint8_t* input, size_t startPos, size_t length, size_t mask, bool isLast,
+                                 const std::vector<Command>& commands, uint32_t distAlphabetSize, uint32_t npostfix, uint32_t ndirect,
+                                 uint8_t prev1, uint8_t prev2, const MetaBlockModel& M) {
+  const BlockSplit& literalSplit = M.literalSplit; const BlockSplit& commandSplit = M.commandSplit; const BlockSplit& distanceSplit = M.distanceSplit;
+  const uint8_t* lut = GetContextLut(M.contextMode);
+  size_t numLiteralContexts = (size_t)literalSplit.numTypes * 64, numDistanceContexts = (size_t)distanceSplit.numTypes * 4;
+  auto clusteredLit = BuildClusteredHistograms(M.literalHistograms, M.literalContextMap, M.numLiteralClusters, 256);
+  auto clusteredDist = BuildClusteredHistograms(M.distanceHistograms, M.distanceContextMap, M.numDistanceClusters, distAlphabetSize);
 
   StoreCompressedMetaBlockHeader(w, isLast, (uint32_t)length);
   BlockEncoder literalEnc(256, literalSplit), commandEnc(704, commandSplit), distanceEnc(distAlphabetSize, distanceSplit);
@@ -306,28 +322,28 @@ static inline void StoreMetaBlock(BitWriter& w, const Bytes& data, size_t startP
   distanceEnc.buildAndStoreEntropyCodes(w);
   w.writeBits(2, npostfix);
   w.writeBits(4, ndirect >> npostfix);
-  for (uint32_t i = 0; i < literalSplit.numTypes; i++) w.writeBits(2, contextMode);
-  EncodeContextMap(w, literalContextMap.data(), numLiteralContexts, numLiteralClusters);
-  EncodeContextMap(w, distanceContextMap.data(), numDistanceContexts, numDistanceClusters);
-  literalEnc.buildAndStoreHuffmanTrees(w, clusteredLit, numLiteralClusters);
-  commandEnc.buildAndStoreHuffmanTrees(w, commandHistograms, commandSplit.numTypes);
-  distanceEnc.buildAndStoreHuffmanTrees(w, clusteredDist, numDistanceClusters);
+  for (uint32_t i = 0; i < literalSplit.numTypes; i++) w.writeBits(2, M.contextMode);
+  EncodeContextMap(w, M.literalContextMap.data(), numLiteralContexts, M.numLiteralClusters);
+  EncodeContextMap(w, M.distanceContextMap.data(), numDistanceContexts, M.numDistanceClusters);
+  literalEnc.buildAndStoreHuffmanTrees(w, clusteredLit, M.numLiteralClusters);
+  commandEnc.buildAndStoreHuffmanTrees(w, M.commandHistograms, commandSplit.numTypes);
+  distanceEnc.buildAndStoreHuffmanTrees(w, clusteredDist, M.numDistanceClusters);
 
-  pos = startPos; prevByte1 = prev1; prevByte2 = prev2;
+  size_t pos = startPos; uint8_t prevByte1 = prev1, prevByte2 = prev2;
   for (const Command& cmd : commands) {
     commandEnc.storeSymbol(w, cmd.cmdPrefix);
     StoreCommandExtra(w, cmd);
     for (uint32_t j = 0; j < cmd.insertLen; j++) {
       uint8_t literal = input[(pos + j) & mask];
       uint32_t context = GetContext(prevByte1, prevByte2, lut);
-      literalEnc.storeSymbolWithContext(w, literal, context, literalContextMap.data(), 6);
+      literalEnc.storeSymbolWithContext(w, literal, context, M.literalContextMap.data(), 6);
       prevByte2 = prevByte1; prevByte1 = literal;
     }
     pos += cmd.insertLen;
     uint32_t copyLen = CommandCopyLen(cmd);
     if (copyLen && cmd.cmdPrefix >= 128) {
       uint32_t distContext = copyLen > 4 ? 3 : copyLen - 2;
-      distanceEnc.storeSymbolWithContext(w, cmd.distPrefix & 0x3FF, distContext, distanceContextMap.data(), 2);
+      distanceEnc.storeSymbolWithContext(w, cmd.distPrefix & 0x3FF, distContext, M.distanceContextMap.data(), 2);
       w.writeBits(cmd.distPrefix >> 10, cmd.distExtra);
     }
     if (copyLen > 0) {
@@ -338,6 +354,25 @@ static inline void StoreMetaBlock(BitWriter& w, const Bytes& data, size_t startP
     pos += copyLen;
   }
   if (isLast) w.alignToByte();
+}
+
+// metablock.ts:504-761.  prev1/prev2: literal-context bytes before startPos (0,0 in the TS;
+// a stitched shard k>0 passes the true preceding bytes, SURVEY §8e rule 4).
+static inline void StoreMetaBlock(BitWriter& w, const Bytes& data, size_t startPos, size_t length, size_t mask, bool isLast,
+                                  const std::vector<Command>& commands, uint32_t distAlphabetSize, int quality,
+                                  uint32_t npostfix, uint32_t ndirect, uint8_t prev1 = 0, uint8_t prev2 = 0,
+                                  MetaBlockStats* stats = nullptr) {
+  MetaBlockModel M;
+  if (!ComputeMetaBlockModel(data, startPos, length, mask, commands, distAlphabetSize, quality, prev1, prev2, M)) {
+    StoreMetaBlockTrivial(w, data.p, startPos, length, mask, isLast, commands, distAlphabetSize, npostfix, ndirect);
+    return;
+  }
+  if (stats) {
+    stats->trivial = false; stats->litTypes = M.literalSplit.numTypes; stats->cmdTypes = M.commandSplit.numTypes;
+    stats->distTypes = M.distanceSplit.numTypes; stats->litClusters = M.numLiteralClusters; stats->distClusters = M.numDistanceClusters;
+    stats->contextMode = M.contextMode;
+  }
+  EmitMetaBlock(w, data.p, startPos, length, mask, isLast, commands, distAlphabetSize, npostfix, ndirect, prev1, prev2, M);
 }
 
 // metablock.ts:821-855 (mask = all ones: the TS passes input.length-1)

@@ -51,6 +51,11 @@ def lib():
         L.oracle_commands.argtypes = [u8p, C.c_size_t, C.c_int, C.c_int, C.c_int, u8p, C.c_size_t, szp]
         L.oracle_store_trivial.argtypes = [u8p, C.c_size_t, u8p, C.c_size_t, C.c_int, C.c_int, C.c_uint, C.c_uint,
                                            u8p, C.c_size_t, szp, C.POINTER(C.c_uint64), u8p]
+        L.oracle_metablock_model.argtypes = [u8p, C.c_size_t, u8p, C.c_size_t, C.c_int, C.c_int, C.c_int, C.c_int, u8p, u8p, u8p, C.c_size_t, u8p, u8p]
+        L.oracle_context_histograms.argtypes = [u8p, C.c_size_t, u8p, C.c_size_t, C.c_int, C.c_int, C.c_int, u8p, u8p, u8p, C.c_size_t, u8p, u8p, u8p]
+        L.oracle_store_metablock.argtypes = [u8p, C.c_size_t, u8p, C.c_size_t, C.c_int, C.c_int, C.c_uint, C.c_uint, C.c_int, C.c_int,
+                                             u8p, u8p, u8p, C.c_size_t, u8p, u8p, u8p, C.c_size_t, szp, C.POINTER(C.c_uint64)]
+        L.oracle_encode_context_map.argtypes = [u8p, C.c_size_t, C.c_uint32, u8p, C.c_size_t, C.POINTER(C.c_uint64)]
         L.oracle_huffman.argtypes = [u8p, C.c_size_t, C.c_int, u8p, u8p]
         L.oracle_build_store_tree.argtypes = [u8p, C.c_size_t, u8p, u8p, u8p, C.c_size_t, C.POINTER(C.c_uint64)]
         L.oracle_context_lut.restype = C.POINTER(C.c_uint8)
@@ -191,6 +196,91 @@ def store_trivial(data, cmds, is_last=True, font=False, start_nbits=0, start_val
     if rc:
         raise RuntimeError(f"oracle_store_trivial rc={rc}")
     return out[: n.value].tobytes(), nb.value, tab[0]
+
+
+# ---- full-metablock stages (metablock.ts:504-761 cut at the model boundary) ----
+MODEL_CAP_BLOCKS = 1 << 16
+
+
+def _flat_model(model):
+    """dict model -> the flat arrays of oracle/src/encode.cc (FlatToModel)."""
+    hdr = np.zeros(16, dtype=np.uint32)
+    types = np.zeros(3 * MODEL_CAP_BLOCKS, dtype=np.uint8)
+    lengths = np.zeros(3 * MODEL_CAP_BLOCKS, dtype=np.uint32)
+    hdr[0] = model["context_mode"]
+    for k, (nt, t, ln) in enumerate(model["splits"]):
+        hdr[1 + k] = nt; hdr[4 + k] = len(t)
+        types[k * MODEL_CAP_BLOCKS:k * MODEL_CAP_BLOCKS + len(t)] = t
+        lengths[k * MODEL_CAP_BLOCKS:k * MODEL_CAP_BLOCKS + len(ln)] = ln
+    hdr[7] = model.get("literal_clusters", 1); hdr[8] = model.get("distance_clusters", 1)
+    lm = np.ascontiguousarray(model.get("literal_map", np.zeros(int(hdr[1]) * 64)), dtype=np.uint32)
+    dm = np.ascontiguousarray(model.get("distance_map", np.zeros(int(hdr[3]) * 4)), dtype=np.uint32)
+    return hdr, types, lengths, lm, dm
+
+
+def metablock_model(data, cmds, quality=5, font=False, prev=(0, 0)):
+    """splitBlock + chooseContextMode + context-map clustering of one metablock = the whole input.
+    Returns None when the reference stores it trivially, else the model dict (see Context._mb_model)."""
+    a, p = _buf(data)
+    cmds = np.ascontiguousarray(cmds, dtype=CMD_DTYPE)
+    hdr = np.zeros(16, dtype=np.uint32)
+    types = np.zeros(3 * MODEL_CAP_BLOCKS, dtype=np.uint8)
+    lengths = np.zeros(3 * MODEL_CAP_BLOCKS, dtype=np.uint32)
+    lm = np.zeros(256 * 64, dtype=np.uint32)
+    dm = np.zeros(256 * 4, dtype=np.uint32)
+    rc = lib().oracle_metablock_model(p, a.size, cmds.ctypes.data, cmds.size, quality, int(font), prev[0], prev[1], hdr.ctypes.data,
+                                      types.ctypes.data, lengths.ctypes.data, MODEL_CAP_BLOCKS, lm.ctypes.data, dm.ctypes.data)
+    if rc == 1:
+        return None
+    if rc:
+        raise RuntimeError(f"oracle_metablock_model rc={rc}")
+    splits = []
+    for k in range(3):
+        nb = int(hdr[4 + k])
+        splits.append((int(hdr[1 + k]), types[k * MODEL_CAP_BLOCKS:k * MODEL_CAP_BLOCKS + nb].copy(), lengths[k * MODEL_CAP_BLOCKS:k * MODEL_CAP_BLOCKS + nb].copy()))
+    return {"context_mode": int(hdr[0]), "splits": splits, "literal_map": lm[: int(hdr[1]) * 64].copy(), "literal_clusters": int(hdr[7]),
+            "distance_map": dm[: int(hdr[3]) * 4].copy(), "distance_clusters": int(hdr[8])}
+
+
+def context_histograms(data, cmds, model, font=False, prev=(0, 0)):
+    a, p = _buf(data)
+    cmds = np.ascontiguousarray(cmds, dtype=CMD_DTYPE)
+    hdr, types, lengths, _, _ = _flat_model(model)
+    da = 124 if font else 64
+    lh = np.zeros((int(hdr[1]) * 64, 256), dtype=np.uint32)
+    ch = np.zeros((int(hdr[2]), 704), dtype=np.uint32)
+    dh = np.zeros((int(hdr[3]) * 4, da), dtype=np.uint32)
+    rc = lib().oracle_context_histograms(p, a.size, cmds.ctypes.data, cmds.size, int(font), prev[0], prev[1], hdr.ctypes.data, types.ctypes.data,
+                                         lengths.ctypes.data, MODEL_CAP_BLOCKS, lh.ctypes.data, ch.ctypes.data, dh.ctypes.data)
+    if rc:
+        raise RuntimeError(f"oracle_context_histograms rc={rc}")
+    return lh, ch, dh
+
+
+def store_metablock(data, cmds, model, is_last=True, font=False, start_nbits=0, start_value=0, prev=(0, 0)):
+    a, p = _buf(data)
+    cmds = np.ascontiguousarray(cmds, dtype=CMD_DTYPE)
+    hdr, types, lengths, lm, dm = _flat_model(model)
+    cap = a.size * 2 + (1 << 17)
+    out = np.zeros(cap, dtype=np.uint8)
+    n = C.c_size_t(0)
+    nb = C.c_uint64(0)
+    rc = lib().oracle_store_metablock(p, a.size, cmds.ctypes.data, cmds.size, int(is_last), int(font), start_nbits, start_value, prev[0], prev[1],
+                                      hdr.ctypes.data, types.ctypes.data, lengths.ctypes.data, MODEL_CAP_BLOCKS, lm.ctypes.data, dm.ctypes.data,
+                                      out.ctypes.data, cap, C.byref(n), C.byref(nb))
+    if rc:
+        raise RuntimeError(f"oracle_store_metablock rc={rc}")
+    return out[: n.value].tobytes(), nb.value
+
+
+def encode_context_map(cmap, num_clusters):
+    mp = np.ascontiguousarray(cmap, dtype=np.uint32)
+    out = np.zeros(mp.size * 4 + 4096, dtype=np.uint8)
+    nb = C.c_uint64(0)
+    rc = lib().oracle_encode_context_map(mp.ctypes.data, mp.size, int(num_clusters), out.ctypes.data, out.size, C.byref(nb))
+    if rc:
+        raise RuntimeError("oracle_encode_context_map failed")
+    return out[: (nb.value + 7) // 8].tobytes(), nb.value
 
 
 def huffman(hist, tree_limit=15):

@@ -177,3 +177,20 @@ def test_stage_functions_consistent():
     sizes = O.encode_shards_sizes(data, 50000, 4, 22, 0, threads=3)
     assert [int(x) for x in sizes] == [len(O.encode(data[o:o + 50000], 4, 22, 0)) for o in range(0, len(data), 50000)]
     assert int(sizes.sum()) == O.encode_shards_total(data, 50000, 4, 22, 0, threads=2)
+
+
+def test_store_metablock_stage_cut_reproduces_encode():
+    """The stage entry points the GPU parity tests use (oracle_metablock_model -> oracle_store_metablock) are the same
+    storeMetaBlock (metablock.ts:504-761) cut at the model boundary: re-assembled they give the one-shot stream."""
+    for name, q, mode in (("alice29.txt", 5, 0), ("enc-ttf.bin", 9, 2), ("mapsdatazrh", 5, 0), ("alice29.txt", 11, 0)):
+        data = load_input(name)
+        cm = O.commands(data, q, 22, mode)
+        model = O.metablock_model(data, cm, q, mode == 2)
+        assert model is not None
+        s, nbits = O.store_metablock(data, cm, model, True, mode == 2, 4, 0b1011)
+        assert s == O.encode(data, q, 22, mode)
+        lh, ch, dh = O.context_histograms(data, cm, model, mode == 2)
+        assert int(lh.sum()) == int(cm["insertLen"].sum()) and int(ch.sum()) == len(cm)
+        bits, nb = O.encode_context_map(model["literal_map"], model["literal_clusters"])
+        assert 0 < nb <= len(bits) * 8
+    assert O.metablock_model(load_input("quickfox_repeated"), O.commands(load_input("quickfox_repeated"), 5, 22, 0), 5) is None
