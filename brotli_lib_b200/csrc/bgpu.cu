@@ -897,7 +897,7 @@ static int stage_full_front(bgpu_ctx* c, const uint8_t* in, size_t n, const void
     const Cmd& lastc = ((const Cmd*)cmds_in)[ncmd - 1];
     const bool phantom = k == 2 && (lastc.copyLen & 0x1FFFFFF) == 0 && lastc.cmdPrefix >= 128;
     if (sp.num_blocks && sum != counts[k] && !(phantom && sum == (uint64_t)counts[k] + 1)) return BGPU_E_INVALID;
-    if (!sp.num_blocks && sp.num_types != 1) return BGPU_E_INVALID;
+    if (sp.num_types == 1 ? sp.num_blocks > 1 : sp.num_blocks < 2) return BGPU_E_INVALID;   // one type <=> at most one block (no split code)
     max_blocks = std::max(max_blocks, sp.num_blocks); max_types = std::max(max_types, sp.num_types);
   }
   if (model->context_mode > 3) return BGPU_E_INVALID;
@@ -919,7 +919,7 @@ static int stage_full_front(bgpu_ctx* c, const uint8_t* in, size_t n, const void
   CK(cudaMemcpyAsync(c->cmds.as<Cmd>() + (lead >> P.k.sh), cm.data(), slots * sizeof(Cmd), cudaMemcpyHostToDevice, c->stream));
   if ((rc = upload_plan(c, job))) return rc;
   if ((rc = full_setup(c, job, P, F, max_blocks + 1, max_types))) return rc;
-  if ((rc = full_symbols(c, P, d_in, F))) return rc;
+  if ((rc = full_symbols(c, P, d_in, F, model->context_mode))) return rc;
   // the caller's block lists and context mode take the place of full_split (parts B and C)
   const MbModel& M = F.mp.models[0];
   for (int k = 0; k < 3; k++) {
@@ -933,8 +933,7 @@ static int stage_full_front(bgpu_ctx* c, const uint8_t* in, size_t n, const void
     CK(cudaMemcpyAsync(M.sstate[k], st3, sizeof st3, cudaMemcpyHostToDevice, c->stream));
     CK(cudaStreamSynchronize(c->stream));   // the staging vectors die with this iteration
   }
-  const uint32_t zero = 0, cm_mode = (uint32_t)model->context_mode;
-  if (model->context_mode >= 0) CK(cudaMemcpyAsync(M.cnt + 3, &cm_mode, 4, cudaMemcpyHostToDevice, c->stream));
+  const uint32_t zero = 0;
   CK(cudaMemcpyAsync(M.cnt + 4, &zero, 4, cudaMemcpyHostToDevice, c->stream));   // never the trivial writer
   CK(cudaStreamSynchronize(c->stream));
   if ((rc = full_ctx_hist(c, F))) return rc;

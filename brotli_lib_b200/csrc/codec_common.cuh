@@ -279,16 +279,32 @@ HDN inline void tree_store(BitSink& w, const uint8_t* depth, int alphabet, int c
   uint32_t maxBits = 0; uint32_t c = (uint32_t)alphabet - 1;
   while (c) { c >>= 1; maxBits++; }
   if (count <= 4) {  // context-map.ts:266-291 (stable sort by depth)
-    uint16_t s[4];
-    for (int i = 0; i < count; i++) s[i] = s4[i];
-    for (int i = 1; i < count; i++) {
-      uint16_t t = s[i]; int j = i - 1;
-      while (j >= 0 && depth[s[j]] > depth[t]) { s[j + 1] = s[j]; j--; }
-      s[j + 1] = t;
+    // The <= 4 used symbols are the ones with a non-zero depth (count >= 2: every used symbol has a code), in index
+    // order; they are re-collected here into scalars and ranked (smaller depth first, ties by index) without any
+    // indexed local array.  The earlier forms (insertion sort over a copy of s4; ranks over s4) read the caller's
+    // 16-bit local s4[] and came out wrong on the device when inlined into the serial header coders (r4b-r4d:
+    // 2- and 4-symbol codes lost or swapped symbols; correct on the host and in a printf build).
+    (void)s4;
+    uint32_t v0 = 0, v1 = 0, v2 = 0, v3 = 0, d0 = 255, d1 = 255, d2 = 255, d3 = 255; int m = 0;
+    for (int i = 0; i < alphabet; i++) {
+      const uint32_t d = depth[i];
+      if (!d) continue;
+      if (m == 0) { v0 = (uint32_t)i; d0 = d; } else if (m == 1) { v1 = (uint32_t)i; d1 = d; }
+      else if (m == 2) { v2 = (uint32_t)i; d2 = d; } else if (m == 3) { v3 = (uint32_t)i; d3 = d; }
+      m++;
     }
+    // rank = number of symbols sorting before (index order is v0 < v1 < v2 < v3, so ties go to the earlier one); v3 takes the rank left over
+    const uint32_t r0 = (d1 < d0) + (d2 < d0) + (d3 < d0);
+    const uint32_t r1 = (d0 <= d1) + (d2 < d1) + (d3 < d1);
+    const uint32_t r2 = (d0 <= d2) + (d1 <= d2) + (d3 < d2);
     w.put(2, 1); w.put(2, count - 1);
-    for (int i = 0; i < count; i++) w.put(maxBits, s[i]);
-    if (count == 4) w.put(1, depth[s[0]] == 1 ? 1 : 0);
+    uint32_t first_depth = 0;
+    for (uint32_t r = 0; r < (uint32_t)count; r++) {
+      const uint32_t sym = r0 == r ? v0 : r1 == r ? v1 : r2 == r ? v2 : v3;
+      if (r == 0) first_depth = r0 == 0 ? d0 : r1 == 0 ? d1 : r2 == 0 ? d2 : d3;
+      w.put(maxBits, sym);
+    }
+    if (count == 4) w.put(1, first_depth == 1 ? 1 : 0);
     return;
   }
   // context-map.ts:293-347

@@ -16,8 +16,10 @@ __device__ __forceinline__ uint32_t block_len_code(uint32_t len) {   // metabloc
   return code;
 }
 // encodeContextMap alone (bgpu_stage_context_map): the same device function k_mb_header calls.  out must be zeroed.
-__global__ void __launch_bounds__(32) k_stage_context_map(const uint32_t* __restrict__ cmap, uint32_t size, uint32_t ncl, uint32_t* scratch,
-                                                          uint32_t* __restrict__ out, uint32_t* __restrict__ nbits) {
+// (no __restrict__ on out: the BitSink built over it is also written by non-inlined callees — with the qualifier the
+// compiler kept words of `out` in registers across those calls and bits of the symbol list were lost, r4c)
+__global__ void __launch_bounds__(32) k_stage_context_map(const uint32_t* cmap, uint32_t size, uint32_t ncl, uint32_t* scratch,
+                                                          uint32_t* out, uint32_t* nbits) {
   __shared__ SerialHuff S;
   if (threadIdx.x != 0) return;
   BitSink w{out, 0};

@@ -147,7 +147,7 @@ int bgpu_stage_huffman(bgpu_ctx* ctx, const uint32_t* hist, int count, int alpha
  * The float-driven decisions (block splits block-splitter.ts:394-464, context maps metablock.ts:763-797) are INPUTS
  * here, so that the integer stages behind them can be compared bit for bit with the reference's on identical inputs. */
 typedef struct bgpu_block_split {       /* block-splitter.ts BlockSplit */
-  uint32_t num_types, num_blocks;       /* num_blocks == 0: one implicit block of type 0 */
+  uint32_t num_types, num_blocks;       /* num_types == 1: num_blocks is 0 or 1 (one block of type 0, no split code) */
   const uint8_t* types;                 /* [num_blocks] */
   const uint32_t* lengths;              /* [num_blocks], summing to the category's symbol count */
 } bgpu_block_split;

@@ -130,7 +130,9 @@ def test_store_metablock_synthetic_models(gpu_ctx):
                 else:
                     t = int(rng.integers(0, seen))
                     types[b] = t if t != types[b - 1] or seen == 1 else (t + 1) % seen
-            splits.append((max(seen, 1) if nb else 1, types, lengths))
+            if seen == 1:   # one block type never has more than one block (clusterBlocks merges neighbours of equal type)
+                types, lengths = np.zeros(1, np.uint8), np.array([n], np.uint32)
+            splits.append((seen, types, lengths))
         ntl, ntd = splits[0][0], splits[2][0]
         ncl_l = int(min(64, [1, 64, 7, 2, 33, 64][trial])); ncl_d = int(min(ntd * 4, [1, 5, 64, 2, 3, 16][trial]))
         lm = rng.integers(0, ncl_l, ntl * 64).astype(np.uint32); lm[:ncl_l] = np.arange(ncl_l)
@@ -154,6 +156,13 @@ def test_context_map_edge_cases(gpu_ctx):
              (np.concatenate([np.zeros(16000, np.uint32), np.arange(256, dtype=np.uint32)]), 256),
              (rng.integers(0, 64, 16384).astype(np.uint32), 64), (np.concatenate([np.arange(3), np.zeros(700), [2, 1, 0] * 5]).astype(np.uint32), 3),
              (np.arange(256, dtype=np.uint32)[::-1].copy(), 256)]
+    for t in range(120):   # few clusters: simple (2..4 symbol) prefix codes over the context-map alphabet
+        ncl = 2 + t % 5
+        n = int(rng.choice([4, 64, 128, 700]))
+        m = rng.integers(0, ncl, n).astype(np.uint32) if t % 3 else np.repeat(rng.integers(0, ncl, n // 4 + 1), 4)[:n].astype(np.uint32)
+        k = min(ncl, n)
+        m[:k] = np.arange(k)
+        cases.append((m, int(m.max()) + 1))
     for cmap, ncl in cases:
         bits, nb = gpu_ctx.stage_context_map(cmap, ncl)
         obits, onb = O.encode_context_map(cmap, ncl)

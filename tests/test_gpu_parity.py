@@ -91,6 +91,23 @@ def test_huffman_bit_exact(gpu_ctx):
             assert np.array_equal(d[i], od) and np.array_equal(b[i], ob), (alphabet, i)
 
 
+def test_huffman_few_symbols_bit_exact(gpu_ctx):
+    """2..5 used symbols: the simple prefix-code forms (context-map.ts:266-291, stable sort by depth, tree-select bit)."""
+    rng = np.random.default_rng(17)
+    for alphabet in (2, 3, 9, 26, 64, 258, 704):
+        hs = []
+        for t in range(64):
+            h = np.zeros(alphabet, dtype=np.uint32)
+            k = min(alphabet, 2 + t % 4)
+            h[rng.choice(alphabet, k, replace=False)] = rng.integers(1, [4, 40, 4000, 1 << 20][t % 4], k)
+            hs.append(h)
+        d, b, tb, tn = gpu_ctx.stage_huffman(np.stack(hs))
+        for i, h in enumerate(hs):
+            od, ob, obytes, onb = O.build_store_tree(h)
+            assert int(tn[i]) == onb and tb[i].tobytes()[: (onb + 7) // 8] == obytes, (alphabet, i, h[h > 0])
+            assert np.array_equal(d[i], od) and np.array_equal(b[i], ob), (alphabet, i)
+
+
 @pytest.mark.parametrize("name", ["alice29.txt", "enc-ttf.bin", "zeros", "html-content.bin", "random_org_10k.bin", "monkey", "ramp"])
 @pytest.mark.parametrize("quality,mode", [(5, 0), (9, 2), (11, 0)])
 def test_store_trivial_bit_exact_given_oracle_commands(gpu_ctx, name, quality, mode):

@@ -75,6 +75,30 @@ def test_command_coding_matches_oracle_commands():
             assert H.bgpu_hosttest_cmd_extra(int(c["insertLen"]), int(c["copyLen"]), C.byref(val)) <= 48
 
 
+def test_context_map_coder_matches_oracle():
+    """encodeContextMap (context-map.ts:114-170) as k_mb_header runs it (codec_common.cuh encode_context_map), compiled
+    for the host: move-to-front, zero-run RLE with every prefix size, the prefix code over clusters + RLE symbols."""
+    H = _hosttest()
+    H.bgpu_hosttest_context_map.restype = C.c_uint32
+    rng = np.random.default_rng(9)
+    cases = [(np.zeros(64, np.uint32), 1), (np.arange(64, dtype=np.uint32) % 2, 2),
+             (np.concatenate([np.zeros(16000, np.uint32), np.arange(256, dtype=np.uint32)]), 256),
+             (rng.integers(0, 64, 16384).astype(np.uint32), 64),
+             (np.concatenate([np.arange(3), np.zeros(700), [2, 1, 0] * 5]).astype(np.uint32), 3)]
+    for t in range(200):
+        ncl = int(rng.integers(2, 65)) if t % 2 else 2 + t % 5
+        n = int(rng.choice([4, 64, 256, 1024, 4096]))
+        m = rng.integers(0, ncl, n).astype(np.uint32) if t % 3 else np.repeat(rng.integers(0, ncl, n // 8 + 1), 8)[:n].astype(np.uint32)
+        k = min(ncl, n)
+        m[:k] = np.arange(k)
+        cases.append((m, int(m.max()) + 1))
+    for cmap, ncl in cases:
+        w = np.zeros(cmap.size + 1024, np.uint32)
+        nb = H.bgpu_hosttest_context_map(cmap.ctypes.data, cmap.size, ncl, w.ctypes.data)
+        obits, onb = O.encode_context_map(cmap, ncl)
+        assert nb == onb and w.tobytes()[: (nb + 7) // 8] == obits, (cmap.size, ncl)
+
+
 def test_c_abi_library_exports_every_declared_symbol():
     from brotli_lib_b200 import _lib
     header = open(os.path.join(ROOT, "include", "brotligpu.h")).read()
