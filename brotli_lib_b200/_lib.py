@@ -10,7 +10,7 @@ E_OUTPUT_TOO_SMALL = -2
 E_UNSUPPORTED = -3
 
 SYMBOLS = [
-    "bgpu_ctx_create", "bgpu_ctx_destroy", "bgpu_ctx_set_tuning", "bgpu_ctx_set_stream", "bgpu_max_compressed_size", "bgpu_encode",
+    "bgpu_ctx_create", "bgpu_ctx_create_multi", "bgpu_ctx_destroy", "bgpu_ctx_set_tuning", "bgpu_ctx_set_stream", "bgpu_max_compressed_size", "bgpu_encode",
     "bgpu_encode_batch", "bgpu_encode_part", "bgpu_encode_device", "bgpu_stream_create", "bgpu_stream_update", "bgpu_stream_finish",
     "bgpu_stream_destroy", "bgpu_stage_match_candidates", "bgpu_stage_commands", "bgpu_stage_store_trivial",
     "bgpu_stage_huffman", "bgpu_stage_h10_matches", "bgpu_stage_histograms", "bgpu_stage_context_map", "bgpu_stage_store_metablock", "bgpu_stage_timings", "bgpu_last_launch_count", "bgpu_last_counter", "bgpu_strerror", "bgpu_last_cuda_error",
@@ -45,6 +45,7 @@ def load():
     L = C.CDLL(LIB_PATH)
     vp, sz, szp, i = C.c_void_p, C.c_size_t, C.POINTER(C.c_size_t), C.c_int
     L.bgpu_ctx_create.argtypes = [i, C.POINTER(vp)]
+    L.bgpu_ctx_create_multi.argtypes = [C.POINTER(i), i, C.POINTER(vp)]
     L.bgpu_ctx_destroy.argtypes = [vp]
     L.bgpu_ctx_destroy.restype = None
     L.bgpu_ctx_set_tuning.argtypes = [vp, C.POINTER(Tuning)]

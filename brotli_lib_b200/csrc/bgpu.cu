@@ -7,7 +7,11 @@
 #include "zopfli.cuh"
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
+#include <condition_variable>
+#include <mutex>
+#include <thread>
 #include <cstdio>
 #include <cstring>
 #include <string>
@@ -113,6 +117,10 @@ struct bgpu_ctx {
   uint64_t counters[4] = {0, 0, 0, 0};   // [0] H10 match entries of the last q10/q11 call
   bool lut_ready = false;
   std::vector<uint32_t> h_shard_bytes;
+  // multi-device (multi_host.inc): one private context per device of bgpu_ctx_create_multi; parts of one input run on
+  // them from one host thread each and are stitched into the caller's buffer
+  std::vector<bgpu_ctx*> peers; bool is_peer = false;
+  uint8_t* part_out = nullptr; size_t part_out_cap = 0;   // peer only: pinned staging of its compressed part
   // timings
   static const int kMaxStages = 40;
   cudaEvent_t ev[kMaxStages + 1]; const char* names[kMaxStages]; float ms[kMaxStages]; int n_stage = 0; int launches = 0;
@@ -456,6 +464,12 @@ int collect(bgpu_ctx* ctx, const Job& job, uint8_t* const* out, const size_t* ou
 #include "lanes_host.inc"
 
 }  // namespace
+static int encode_part_host(bgpu_ctx* c, const uint8_t* in, size_t n, const uint8_t* prev2, unsigned part_flags, const EncParams& P,
+                            uint8_t* out, size_t out_cap, size_t* out_len);
+namespace {
+#include "multi_host.inc"
+
+}  // namespace
 
 extern "C" {
 
@@ -474,6 +488,22 @@ int bgpu_ctx_create(int device_id, bgpu_ctx** out) {
   return 0;
 }
 
+int bgpu_ctx_create_multi(const int* device_ids, int n_dev, bgpu_ctx** out) {
+  if (!out || !device_ids || n_dev < 1) return BGPU_E_INVALID;
+  bgpu_ctx* c = nullptr;
+  int rc = bgpu_ctx_create(device_ids[0], &c);
+  if (rc) return rc;
+  for (int i = 0; i < n_dev && n_dev > 1; i++) {
+    bgpu_ctx* q = nullptr;
+    if ((rc = bgpu_ctx_create(device_ids[i], &q))) { bgpu_ctx_destroy(c); return rc; }
+    q->is_peer = true;
+    c->peers.push_back(q);
+  }
+  cudaSetDevice(c->device);
+  *out = c;
+  return 0;
+}
+
 void bgpu_ctx_destroy(bgpu_ctx* c) {
   if (!c) return;
   cudaSetDevice(c->device);
@@ -485,6 +515,10 @@ void bgpu_ctx_destroy(bgpu_ctx* c) {
   for (DBuf* b : all) b->release();
   for (bgpu_ctx* l : c->lanes) bgpu_ctx_destroy(l);
   c->lanes.clear();
+  for (bgpu_ctx* q : c->peers) bgpu_ctx_destroy(q);
+  c->peers.clear();
+  cudaSetDevice(c->device);
+  if (c->part_out) cudaFreeHost(c->part_out);
   if (c->lane_ev) cudaEventDestroy(c->lane_ev);
   if (c->fork_ev) cudaEventDestroy(c->fork_ev);
   if (c->h2d_ev) cudaEventDestroy(c->h2d_ev);
@@ -499,6 +533,7 @@ void bgpu_ctx_destroy(bgpu_ctx* c) {
 int bgpu_ctx_set_tuning(bgpu_ctx* c, const bgpu_tuning* t) {
   if (!c || !t) return BGPU_E_INVALID;
   c->tune = *t;
+  for (bgpu_ctx* q : c->peers) q->tune = *t;
   return 0;
 }
 
@@ -528,6 +563,14 @@ int bgpu_encode_batch(bgpu_ctx* c, int count, const uint8_t* const* in, const si
     } else { map.push_back(i); lens.push_back(n[i]); ptrs.push_back(in[i]); }
   }
   if (map.empty()) return result;
+  if (lens.size() == 1 && multi_apply(c, P, lens[0])) {
+    rc = encode_multi(c, ptrs[0], lens[0], P, out[map[0]], out_cap[map[0]], &out_len[map[0]]);
+    return rc ? rc : result;
+  }
+  if (lens.size() > 1 && c->peers.size() > 1) {
+    rc = encode_batch_multi(c, ptrs, lens, P, out, out_cap, out_len, map);
+    return rc ? rc : result;
+  }
   {
     uint32_t L; size_t gb;
     if (lens.size() == 1 && lanes_apply(c, P, lens[0], &L, &gb)) {
@@ -562,10 +605,19 @@ int bgpu_encode(bgpu_ctx* c, const uint8_t* in, size_t n, int quality, int lgwin
 int bgpu_encode_part(bgpu_ctx* c, const uint8_t* in, size_t n, const uint8_t* prev2, unsigned part_flags, int quality, int lgwin, int mode,
                      uint8_t* out, size_t out_cap, size_t* out_len) {
   if (!c || !out_len || (n && !in)) return BGPU_E_INVALID;
-  const bool first = part_flags & BGPU_PART_FIRST, last = part_flags & BGPU_PART_LAST;
+  const bool first = part_flags & BGPU_PART_FIRST;
   if (!first && n && !prev2) return BGPU_E_INVALID;
   EncParams P = make_params(quality, lgwin, mode);
   if (P.quality < 1) return BGPU_E_UNSUPPORTED;   // the host-only uncompressed path has no part form
+  return encode_part_host(c, in, n, prev2, part_flags, P, out, out_cap, out_len);
+}
+
+}  // extern "C"
+
+// The body of bgpu_encode_part (also the per-device worker of multi_host.inc): lanes when the part is large enough.
+static int encode_part_host(bgpu_ctx* c, const uint8_t* in, size_t n, const uint8_t* prev2, unsigned part_flags, const EncParams& P,
+                            uint8_t* out, size_t out_cap, size_t* out_len) {
+  const bool first = part_flags & BGPU_PART_FIRST, last = part_flags & BGPU_PART_LAST;
   int rc;
   if (n == 0) {
     // nothing to code: the header (FIRST) and / or ISLAST + ISEMPTY (LAST), encode.ts:399-405
@@ -579,6 +631,10 @@ int bgpu_encode_part(bgpu_ctx* c, const uint8_t* in, size_t n, const uint8_t* pr
     return 0;
   }
   CK(cudaSetDevice(c->device));
+  {
+    uint32_t L; size_t gb;
+    if (lanes_apply(c, P, n, &L, &gb)) return encode_lanes(c, in, nullptr, n, P, L, gb, out, out_cap, out_len, nullptr, part_flags, prev2);
+  }
   const size_t lead = first ? 0 : 256;
   uint32_t pf[1] = {part_flags}; size_t lens[1] = {n};
   Job job; plan_job(c, P, lens, 1, job, pf, lead);
@@ -600,6 +656,8 @@ int bgpu_encode_part(bgpu_ctx* c, const uint8_t* in, size_t n, const uint8_t* pr
   timing_end(c);
   return rc;
 }
+
+extern "C" {
 
 int bgpu_encode_device(bgpu_ctx* c, const void* d_in, size_t n, int quality, int lgwin, int mode, uint8_t* out, size_t out_cap,
                        size_t* out_len, float* kernel_ms) {

@@ -26,10 +26,16 @@ class EncoderMode(enum.IntEnum):
 class Context:
     """One bgpu_ctx (device, CUDA stream, scratch arenas).  Not thread-safe."""
 
-    def __init__(self, device=-1, shard_bytes=0, segment_bytes=0, metablock_bytes=0):
+    def __init__(self, device=-1, shard_bytes=0, segment_bytes=0, metablock_bytes=0, devices=None):
+        """device: one GPU (-1 = current).  devices=[...]: one context over several GPUs of the box (bgpu_ctx_create_multi):
+        encode() of a large input then runs one part per device and returns one stitched stream."""
         self._L = _lib.load()
         h = C.c_void_p()
-        _lib.check(self._L.bgpu_ctx_create(device, C.byref(h)))
+        if devices is not None:
+            ids = (C.c_int * len(devices))(*[int(d) for d in devices])
+            _lib.check(self._L.bgpu_ctx_create_multi(ids, len(devices), C.byref(h)))
+        else:
+            _lib.check(self._L.bgpu_ctx_create(device, C.byref(h)))
         self._h = h
         if shard_bytes or segment_bytes or metablock_bytes:
             self.set_tuning(shard_bytes, segment_bytes, metablock_bytes)

@@ -52,6 +52,13 @@ typedef struct bgpu_tuning {
 /* Context: owns the CUDA device, stream, scratch arenas.  Not thread-safe; one per thread.
  * device_id < 0 selects the current device. */
 int bgpu_ctx_create(int device_id, bgpu_ctx** out);
+/* One context over several GPUs of one box (stands in for the serial metablock loop of
+ * src/encode/encode.ts:206-278 run by one thread per device).  bgpu_encode on such a context cuts an input of more
+ * than one shard into n_dev contiguous parts of whole shards, encodes part g on device_ids[g] from its own host thread
+ * and returns ONE stream (parts are byte-aligned; the first carries the window header, the last ISLAST);
+ * bgpu_encode_batch deals the items to the devices by bytes.  device_ids may repeat (several contexts on one GPU).
+ * Stage entry points, streaming and bgpu_encode_part / bgpu_encode_device run on device_ids[0]. */
+int bgpu_ctx_create_multi(const int* device_ids, int n_dev, bgpu_ctx** out);
 void bgpu_ctx_destroy(bgpu_ctx* ctx);
 int bgpu_ctx_set_tuning(bgpu_ctx* ctx, const bgpu_tuning* t);
 /* Runs all further work of the context on the caller's CUDA stream (a cudaStream_t passed as void*;
