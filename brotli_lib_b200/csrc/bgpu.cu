@@ -431,8 +431,52 @@ int host_special_case(const uint8_t* in, size_t n, const EncParams& P, std::vect
   return 0;
 }
 
-// Copies every stream's shards, concatenated, to the caller's buffers.
-int collect(bgpu_ctx* ctx, const Job& job, uint8_t* const* out, const size_t* out_cap, size_t* out_len, const int* map, int count) {
+// Raw form of a shard: its bytes as ONE uncompressed metablock (metablock.ts:257-271: ISLAST 0, MNIBBLES, MLEN - 1,
+// ISUNCOMPRESSED 1, byte alignment, the bytes), after the window header when the shard opens the stream and followed
+// by ISLAST + ISEMPTY (0x03, encode.ts:399-405) when it closes it.  The reference has no such fallback above quality 0;
+// here it bounds the output (bgpu_max_compressed_size): a shard whose compressed form exceeds
+// len + len / 32 + 64 bytes is replaced by its raw form — far beyond what the reference's own coding of incompressible
+// bytes costs (<= 52 bytes per KiB-sized input, <= 270 bytes per MiB), so streams stay identical to the reference's.
+struct RawForm { uint8_t hdr[8]; uint32_t hdr_bytes; uint32_t tail; };
+uint32_t raw_shard_form(const ShardD& sh, RawForm& r) {
+  HostBits w;
+  if (sh.flags & 1) w.put(sh.start_nbits, sh.start_value);
+  w.put(1, 0);
+  const int lg = sh.len == 1 ? 1 : (31 - __builtin_clz(sh.len - 1)) + 1;
+  const int mnibbles = (lg < 16 ? 16 : lg + 3) / 4;
+  w.put(2, mnibbles - 4); w.put(mnibbles * 4, sh.len - 1);
+  w.put(1, 1);
+  w.align();
+  r.hdr_bytes = (uint32_t)(w.pos >> 3); r.tail = (sh.flags & 2) ? 1 : 0;
+  memcpy(r.hdr, w.b.data(), r.hdr_bytes);
+  return r.hdr_bytes + sh.len + r.tail;
+}
+inline bool shard_goes_raw(const ShardD& sh, uint32_t compressed_bytes) {
+  return (uint64_t)compressed_bytes > (uint64_t)sh.len + (sh.len >> 5) + 64;
+}
+// Bytes shard `sh` contributes to the stream (compressed, or raw when that is what will be written).
+uint32_t shard_out_bytes(const ShardD& sh, uint32_t compressed_bytes) {
+  if (!shard_goes_raw(sh, compressed_bytes)) return compressed_bytes;
+  RawForm r; return raw_shard_form(sh, r);
+}
+// Queues the copies that put shard `sh` at dst (host): its compressed bytes from the device output region, or its raw
+// form straight from the staged input.  Returns the bytes written.
+int shard_to_host(const ShardD& sh, uint32_t compressed_bytes, const uint8_t* d_out, const uint8_t* d_in, uint8_t* dst, cudaStream_t st, uint32_t* written) {
+  if (!shard_goes_raw(sh, compressed_bytes)) {
+    CK(cudaMemcpyAsync(dst, d_out + sh.out_off, compressed_bytes, cudaMemcpyDeviceToHost, st));
+    *written = compressed_bytes;
+    return 0;
+  }
+  RawForm r; const uint32_t total = raw_shard_form(sh, r);
+  memcpy(dst, r.hdr, r.hdr_bytes);
+  CK(cudaMemcpyAsync(dst + r.hdr_bytes, d_in + sh.in_off, sh.len, cudaMemcpyDeviceToHost, st));
+  if (r.tail) dst[r.hdr_bytes + sh.len] = 0x03;
+  *written = total;
+  return 0;
+}
+
+// Copies every stream's shards, concatenated, to the caller's buffers.  d_in: the staged input the job ran on.
+int collect(bgpu_ctx* ctx, const Job& job, const uint8_t* d_in, uint8_t* const* out, const size_t* out_cap, size_t* out_len, const int* map, int count) {
   cudaStream_t st = ctx->stream;
   ctx->h_shard_bytes.resize(job.shards.size());
   CK(cudaMemcpyAsync(ctx->h_shard_bytes.data(), ctx->shard_bytes.p, job.shards.size() * 4, cudaMemcpyDeviceToHost, st));
@@ -444,7 +488,7 @@ int collect(bgpu_ctx* ctx, const Job& job, uint8_t* const* out, const size_t* ou
     for (uint32_t k = 0; k < sp.n_shard; k++) {
       uint32_t b = ctx->h_shard_bytes[sp.first_shard + k];
       if (b > job.shards[sp.first_shard + k].out_cap) { g_cuda_err = "shard output exceeded its device region"; return BGPU_E_CUDA; }
-      total += b;
+      total += shard_out_bytes(job.shards[sp.first_shard + k], b);
     }
     int dst = map ? map[s] : s;
     out_len[dst] = total;
@@ -452,9 +496,10 @@ int collect(bgpu_ctx* ctx, const Job& job, uint8_t* const* out, const size_t* ou
     size_t o = 0;
     for (uint32_t k = 0; k < sp.n_shard; k++) {
       const ShardD& sh = job.shards[sp.first_shard + k];
-      uint32_t b = ctx->h_shard_bytes[sp.first_shard + k];
-      CK(cudaMemcpyAsync(out[dst] + o, ctx->out.as<uint8_t>() + sh.out_off, b, cudaMemcpyDeviceToHost, st));
-      o += b;
+      uint32_t b = ctx->h_shard_bytes[sp.first_shard + k], wr = 0;
+      int r2 = shard_to_host(sh, b, ctx->out.as<uint8_t>(), d_in, out[dst] + o, st, &wr);
+      if (r2) return r2;
+      o += wr;
     }
   }
   CK(cudaStreamSynchronize(st));
@@ -543,7 +588,12 @@ int bgpu_ctx_set_stream(bgpu_ctx* c, void* cuda_stream) {
   return 0;
 }
 
-size_t bgpu_max_compressed_size(size_t n) { return 2 * n + 8192 + ((n >> 16) + 1) * 2048; }
+// Per shard of len bytes the stream holds at most len + len / 32 + 64 bytes (shard_goes_raw) or the raw form
+// (<= len + 6); shards are >= 1008 bytes for every lgwin at the default tuning (plan_shard_bytes), the last one may be
+// shorter.  Host-only forms (encode.ts:92-138): n + 4 per 16 MiB block + <= 6.  (SURVEY.md section 8b asked for
+// n + 4 ceil(n / 2^24) + 16 shards + 16, which presumes a break-even raw fallback; the threshold here is looser so that
+// the reference's own coding of incompressible shards is never replaced.)
+size_t bgpu_max_compressed_size(size_t n) { return n + (n >> 5) + 70 * (n / 1008 + 1) + 16; }
 
 int bgpu_encode_batch(bgpu_ctx* c, int count, const uint8_t* const* in, const size_t* n, int quality, int lgwin, int mode,
                       uint8_t* const* out, const size_t* out_cap, size_t* out_len) {
@@ -575,6 +625,7 @@ int bgpu_encode_batch(bgpu_ctx* c, int count, const uint8_t* const* in, const si
     uint32_t L; size_t gb;
     if (lens.size() == 1 && lanes_apply(c, P, lens[0], &L, &gb)) {
       rc = encode_lanes(c, ptrs[0], nullptr, lens[0], P, L, gb, out[map[0]], out_cap[map[0]], &out_len[map[0]], nullptr);
+      if (!rc && !out[map[0]]) rc = BGPU_E_OUTPUT_TOO_SMALL;   // a size query, as on the one-job path (collect)
       return rc ? rc : result;
     }
   }
@@ -590,7 +641,7 @@ int bgpu_encode_batch(bgpu_ctx* c, int count, const uint8_t* const* in, const si
   if ((rc = upload_plan(c, job))) return rc;
   if ((rc = run_frontend_any(c, job, P, c->in.as<uint8_t>()))) return rc;
   if ((rc = run_backend_any(c, job, P, c->in.as<uint8_t>()))) return rc;
-  rc = collect(c, job, out, out_cap, out_len, map.data(), (int)map.size());
+  rc = collect(c, job, c->in.as<uint8_t>(), out, out_cap, out_len, map.data(), (int)map.size());
   timing_end(c);
   return rc ? rc : result;
 }
@@ -652,7 +703,7 @@ static int encode_part_host(bgpu_ctx* c, const uint8_t* in, size_t n, const uint
   if ((rc = run_frontend_any(c, job, P, d_in))) return rc;
   if ((rc = run_backend_any(c, job, P, d_in))) return rc;
   uint8_t* outs[1] = {out}; size_t caps[1] = {out_cap};
-  rc = collect(c, job, outs, caps, out_len, nullptr, 1);
+  rc = collect(c, job, d_in, outs, caps, out_len, nullptr, 1);
   timing_end(c);
   return rc;
 }
@@ -677,13 +728,13 @@ int bgpu_encode_device(bgpu_ctx* c, const void* d_in, size_t n, int quality, int
   if ((rc = run_backend_any(c, job, P, (const uint8_t*)d_in))) return rc;
   if (out) {
     uint8_t* outs[1] = {out}; size_t caps[1] = {out_cap};
-    rc = collect(c, job, outs, caps, out_len, nullptr, 1);
+    rc = collect(c, job, (const uint8_t*)d_in, outs, caps, out_len, nullptr, 1);
   } else {
     c->h_shard_bytes.resize(job.shards.size());
     CK(cudaMemcpyAsync(c->h_shard_bytes.data(), c->shard_bytes.p, job.shards.size() * 4, cudaMemcpyDeviceToHost, c->stream));
     CK(cudaStreamSynchronize(c->stream));
     size_t total = 0;
-    for (uint32_t b : c->h_shard_bytes) total += b;
+    for (size_t k = 0; k < job.shards.size(); k++) total += shard_out_bytes(job.shards[k], c->h_shard_bytes[k]);
     *out_len = total;
   }
   timing_end(c);
@@ -738,7 +789,7 @@ static int stream_flush_shard(bgpu_stream* s, size_t n, bool last) {
   size_t cap = sh.out_cap, len = 0, old = s->outbuf.size();
   s->outbuf.resize(old + cap);
   uint8_t* outs[1] = {s->outbuf.data() + old}; size_t caps[1] = {cap};
-  rc = collect(c, job, outs, caps, &len, nullptr, 1);
+  rc = collect(c, job, c->in.as<uint8_t>(), outs, caps, &len, nullptr, 1);
   s->outbuf.resize(old + (rc ? 0 : len));
   timing_end(c);
   s->header_done = true;
@@ -900,7 +951,7 @@ int bgpu_stage_store_trivial(bgpu_ctx* c, const uint8_t* in, size_t n, const voi
   if ((rc = upload_plan(c, job))) return rc;
   if ((rc = run_backend(c, job, P, c->in.as<uint8_t>()))) return rc;
   uint8_t* outs[1] = {out}; size_t caps[1] = {out_cap};
-  rc = collect(c, job, outs, caps, out_len, nullptr, 1);
+  rc = collect(c, job, c->in.as<uint8_t>(), outs, caps, out_len, nullptr, 1);
   timing_end(c);
   if (out_bits) *out_bits = (uint64_t)*out_len * 8;
   if (tables) {
@@ -1041,7 +1092,7 @@ int bgpu_stage_store_metablock(bgpu_ctx* c, const uint8_t* in, size_t n, const v
   CK(cudaStreamSynchronize(c->stream));
   if ((rc = full_emit(c, P, d_in, F))) return rc;
   uint8_t* outs[1] = {out}; size_t caps[1] = {out_cap};
-  rc = collect(c, job, outs, caps, out_len, nullptr, 1);
+  rc = collect(c, job, d_in, outs, caps, out_len, nullptr, 1);
   timing_end(c);
   return rc;
 }

@@ -65,7 +65,12 @@ class Context:
         cap = self._L.bgpu_max_compressed_size(a.size)
         out = np.empty(cap, dtype=np.uint8)
         n = C.c_size_t(0)
-        _lib.check(self._L.bgpu_encode(self._h, _ptr(a), a.size, int(quality), int(lgwin), int(mode), out.ctypes.data, cap, C.byref(n)))
+        rc = self._L.bgpu_encode(self._h, _ptr(a), a.size, int(quality), int(lgwin), int(mode), out.ctypes.data, cap, C.byref(n))
+        if rc == _lib.E_OUTPUT_TOO_SMALL:   # only with a custom shard_bytes below the default: the call reports the size needed
+            cap = n.value
+            out = np.empty(cap, dtype=np.uint8)
+            rc = self._L.bgpu_encode(self._h, _ptr(a), a.size, int(quality), int(lgwin), int(mode), out.ctypes.data, cap, C.byref(n))
+        _lib.check(rc)
         return out[: n.value].tobytes()
 
     def encode_batch(self, items, quality=11, lgwin=22, mode=EncoderMode.GENERIC):

@@ -416,3 +416,35 @@ def test_ring_handover_across_parse_segments(gpu_ctx, quality, mode):
     finally:
         gpu_ctx.set_tuning()
     assert a == b
+
+
+def test_max_compressed_size_holds_on_incompressible_input(gpu_ctx):
+    """bgpu_max_compressed_size is a bound, not a guess: incompressible bytes at every quality and window size, whole and
+    in ragged shards; a shard that would exceed len + len / 32 + 64 is stored raw (one uncompressed metablock)."""
+    import brotli_lib_b200._lib as L
+    lib = L.load()
+    rng = np.random.default_rng(23)
+    for n in (64, 65, 1000, 4096, 70001, (1 << 22) + 4097):
+        data = rng.integers(0, 256, n, dtype=np.uint8).tobytes()
+        for q in (0, 1, 3, 5, 9, 10, 11):
+            for lgwin in ((22, 10) if n <= 70001 else (22,)):
+                s = gpu_ctx.encode(data, q, lgwin, 0)
+                assert len(s) <= lib.bgpu_max_compressed_size(n), (n, q, lgwin, len(s))
+                _rt(s, data)
+    # the reference's own coding of incompressible input is kept (no early raw fallback): byte-identical to the oracle
+    data = rng.integers(0, 256, 1 << 20, dtype=np.uint8).tobytes()
+    gpu_ctx.set_tuning(segment_bytes=EXACT, flags=TRIVIAL)
+    try:
+        assert gpu_ctx.encode(data, 5, 22, 0) == O.encode(data, 5, 22, 0, force_trivial=True)
+    finally:
+        gpu_ctx.set_tuning()
+    # tiny shards, where headers dominate: every shard stays within len + len / 32 + 64 (+ 6 for a raw one), one valid stream
+    data = bytes(rng.integers(0, 256, 20000, dtype=np.uint8))
+    gpu_ctx.set_tuning(shard_bytes=64)
+    try:
+        for q in (1, 5, 11):
+            s = gpu_ctx.encode(data, q, 22, 0)
+            _rt(s, data)
+            assert len(s) <= len(data) + (len(data) // 64 + 1) * (64 // 32 + 64 + 6) + 16
+    finally:
+        gpu_ctx.set_tuning()
