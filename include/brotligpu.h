@@ -2,8 +2,9 @@
  *
  * The reference (countertype/brotli-lib) has no FFI layer; its only boundary is the TypeScript
  * API.  Every entry point below names the reference interface it stands in for (paths relative
- * to the reference tree).  A Node-API addon (node/addon.cc) binds these 1:1; tests bind them
- * with ctypes.  Plain C, no exceptions cross the boundary, every int-returning function yields
+ * to the reference tree).  node/addon.cc (Node-API; compiled only where <node_api.h> exists, which
+ * is not the case in this repository's build image) binds these 1:1; the shipped, tested binding is
+ * ctypes (brotli_lib_b200/_lib.py).  Plain C, no exceptions cross the boundary, every int-returning function yields
  * 0 or a negative BGPU_E_* code.  There is NO CPU fallback: without a usable CUDA device the
  * calls fail with BGPU_E_NO_DEVICE / BGPU_E_CUDA.
  */
@@ -65,7 +66,10 @@ int bgpu_ctx_set_tuning(bgpu_ctx* ctx, const bgpu_tuning* t);
  * NULL restores the context's own stream).  Lets a harness bracket calls with its own CUDA events. */
 int bgpu_ctx_set_stream(bgpu_ctx* ctx, void* cuda_stream);
 
-/* Upper bound of the stream size for n input bytes (any quality/mode). */
+/* Upper bound of the stream size for n input bytes (any quality / lgwin / mode, default tuning):
+ * n + n / 32 + 70 (n / 1008 + 1) + 16.  A shard whose compressed form would exceed len + len / 32 + 64 bytes is stored
+ * as one uncompressed metablock (<= len + 6).  With a bgpu_tuning.shard_bytes below 1008 the calls may need more and
+ * then report it through BGPU_E_OUTPUT_TOO_SMALL / *out_len. */
 size_t bgpu_max_compressed_size(size_t n);
 
 /* brotliEncode(input, {quality, lgwin, mode})            src/encode/encode.ts:50-90

@@ -116,6 +116,24 @@ def test_c_abi_library_exports_every_declared_symbol():
     assert b"quality" in L.bgpu_strerror(-3)
 
 
+def test_node_addon_sources_are_real_and_well_formed():
+    """node/addon.cc binds the C ABI 1:1.  No Node toolchain exists in this image, so the addon compiles
+    to nothing here (guarded by __has_include(<node_api.h>)); against a declaration-only stub of the Node-API subset it
+    uses, the whole file must pass the compiler's syntax and type checks, and it must name only declared C-ABI entries."""
+    import subprocess
+    addon = os.path.join(ROOT, "node", "addon.cc")
+    subprocess.check_call(["g++", "-std=c++17", "-fsyntax-only", "-Wall", "-Werror", "-I", os.path.join(ROOT, "tests", "stubs"), "-I", os.path.join(ROOT, "include"), addon])
+    subprocess.check_call(["g++", "-std=c++17", "-fsyntax-only", addon])   # without node_api.h: an empty translation unit
+    header = open(os.path.join(ROOT, "include", "brotligpu.h")).read()
+    declared = set(re.findall(r"\b(bgpu_[a-z0-9_]+)\s*\(", header))
+    used = set(re.findall(r"\b(bgpu_[a-z0-9_]+)\s*\(", open(addon).read()))
+    assert used and used <= declared, used - declared
+    assert {"bgpu_encode", "bgpu_encode_batch", "bgpu_encode_part", "bgpu_stream_update", "bgpu_stream_finish", "bgpu_ctx_create_multi"} <= used
+    ts = open(os.path.join(ROOT, "node", "encode.ts")).read()
+    for name in ("export function brotliEncode", "export class BrotliEncoder", "export const enum EncoderMode", "export interface BrotliEncodeOptions"):
+        assert name in ts, name
+
+
 def test_product_does_not_reference_the_oracle():
     pkg = os.path.join(ROOT, "brotli_lib_b200")
     for dirpath, _, files in os.walk(pkg):
