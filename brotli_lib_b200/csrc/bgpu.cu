@@ -136,8 +136,10 @@ uint32_t eff(uint32_t v, uint32_t dflt) { return v ? v : dflt; }
 // window header and starts with an unknown distance ring, a part that is not LAST ends with the
 // byte-aligning empty metadata block instead of ISLAST.  `lead` bytes are reserved before the first
 // stream (the two bytes that precede a non-first part live there: literal context, §8e rule 4).
+// `hist` (streaming; one stream of one shard): the first hist bytes of the shard are the already coded window — they
+// take part in match finding, metablocks / segments / tiles start behind them.  hist must be a multiple of 4.
 void plan_job(const bgpu_ctx* ctx, const EncParams& P, const size_t* lens, int count, Job& job,
-              const uint32_t* part_flags = nullptr, size_t lead = 0) {
+              const uint32_t* part_flags = nullptr, size_t lead = 0, size_t hist = 0) {
   uint32_t shard_bytes = std::min<uint32_t>(eff(ctx->tune.shard_bytes, 1u << 22), 1u << 22);
   if (P.lgwin < 22) shard_bytes = std::min<uint32_t>(shard_bytes, ((1u << P.lgwin) - 16) & ~3u);
   shard_bytes = std::max<uint32_t>(shard_bytes & ~3u, 64);
@@ -161,7 +163,8 @@ void plan_job(const bgpu_ctx* ctx, const EncParams& P, const size_t* lens, int c
       job.n_stile += sh.len >= 4 ? (sh.len - 3 + SORT_TILE - 1) / SORT_TILE : 0;
       job.max_shard_len = std::max(job.max_shard_len, sh.len);
       uint32_t shard_idx = (uint32_t)job.shards.size();
-      for (uint32_t mo = 0; mo < sh.len; mo += mb_bytes) {
+      sh.hist = so == 0 ? (uint32_t)std::min<size_t>(hist, sh.len) : 0;
+      for (uint32_t mo = sh.hist; mo < sh.len; mo += mb_bytes) {
         MbD mb; memset(&mb, 0, sizeof mb);
         mb.shard = shard_idx; mb.rel_pos = mo; mb.len = std::min(mb_bytes, sh.len - mo);
         mb.first_seg = (uint32_t)job.segs.size(); mb.first_tile = (uint32_t)job.tile_seg.size();
@@ -442,17 +445,19 @@ uint32_t raw_shard_form(const ShardD& sh, RawForm& r) {
   HostBits w;
   if (sh.flags & 1) w.put(sh.start_nbits, sh.start_value);
   w.put(1, 0);
-  const int lg = sh.len == 1 ? 1 : (31 - __builtin_clz(sh.len - 1)) + 1;
+  const uint32_t len = sh.len - sh.hist;   // the coded bytes (all of the shard except a streaming history prefix)
+  const int lg = len == 1 ? 1 : (31 - __builtin_clz(len - 1)) + 1;
   const int mnibbles = (lg < 16 ? 16 : lg + 3) / 4;
-  w.put(2, mnibbles - 4); w.put(mnibbles * 4, sh.len - 1);
+  w.put(2, mnibbles - 4); w.put(mnibbles * 4, len - 1);
   w.put(1, 1);
   w.align();
   r.hdr_bytes = (uint32_t)(w.pos >> 3); r.tail = (sh.flags & 2) ? 1 : 0;
   memcpy(r.hdr, w.b.data(), r.hdr_bytes);
-  return r.hdr_bytes + sh.len + r.tail;
+  return r.hdr_bytes + len + r.tail;
 }
 inline bool shard_goes_raw(const ShardD& sh, uint32_t compressed_bytes) {
-  return (uint64_t)compressed_bytes > (uint64_t)sh.len + (sh.len >> 5) + 64;
+  const uint32_t len = sh.len - sh.hist;
+  return len > 0 && (uint64_t)compressed_bytes > (uint64_t)len + (len >> 5) + 64;
 }
 // Bytes shard `sh` contributes to the stream (compressed, or raw when that is what will be written).
 uint32_t shard_out_bytes(const ShardD& sh, uint32_t compressed_bytes) {
@@ -469,8 +474,8 @@ int shard_to_host(const ShardD& sh, uint32_t compressed_bytes, const uint8_t* d_
   }
   RawForm r; const uint32_t total = raw_shard_form(sh, r);
   memcpy(dst, r.hdr, r.hdr_bytes);
-  CK(cudaMemcpyAsync(dst + r.hdr_bytes, d_in + sh.in_off, sh.len, cudaMemcpyDeviceToHost, st));
-  if (r.tail) dst[r.hdr_bytes + sh.len] = 0x03;
+  CK(cudaMemcpyAsync(dst + r.hdr_bytes, d_in + sh.in_off + sh.hist, sh.len - sh.hist, cudaMemcpyDeviceToHost, st));
+  if (r.tail) dst[r.hdr_bytes + sh.len - sh.hist] = 0x03;
   *written = total;
   return 0;
 }
@@ -751,6 +756,11 @@ struct bgpu_stream {
   std::vector<uint8_t> outbuf;
   bool header_done = false, finished = false;
   size_t total_in = 0;
+  // Device-resident window (the reference's ring buffer, encode.ts:411-489): win[cur] holds the last hist_len coded
+  // bytes; a flush appends the new bytes behind them, encodes the shard [history | new] with metablocks only over
+  // the new part, and the window slides (into the other buffer) when history + new would exceed the window.
+  DBuf win[2]; int cur = 0; size_t hist_len = 0;
+  uint8_t prev2[2] = {0, 0};   // the last two coded bytes (literal context of the next piece when no history is kept)
 };
 
 extern "C" {
@@ -766,36 +776,84 @@ int bgpu_stream_create(bgpu_ctx* c, int quality, int lgwin, int mode, bgpu_strea
   return 0;
 }
 
-// Encodes `n` pending bytes as one shard of the stream (first: carries the window header; last: ISLAST).
-static int stream_flush_shard(bgpu_stream* s, size_t n, bool last) {
+}  // extern "C"
+
+namespace {
+// enc-constants.ts:129-147 computeLgBlock: the reference's update() emits one metablock per 1 << lgblock input bytes
+uint32_t stream_block_bytes(const EncParams& P) {
+  int lgblock;
+  if (P.quality <= 1) lgblock = P.lgwin;
+  else if (P.quality < 4) lgblock = 14;
+  else { lgblock = 16; if (P.quality >= 9 && P.lgwin > lgblock) lgblock = std::min(18, P.lgwin); }
+  return 1u << lgblock;
+}
+// Window W (= the shard size of the one-shot path), the flush unit (a block, but at most half the window so that at
+// least as much history as new data fits) and the most new bytes one job takes.  Windows below 8 KiB keep no
+// history: every flush is an independent shard, as in the one-shot path.
+struct StreamGeom { uint32_t window, unit, max_new; bool history; };
+StreamGeom stream_geom(const bgpu_ctx* c, const EncParams& P) {
+  StreamGeom g; g.window = plan_shard_bytes(c, P);
+  g.history = g.window >= 8192;
+  if (!g.history) { g.unit = g.max_new = g.window; return g; }
+  const uint32_t half = (g.window / 2) & ~4095u;
+  g.unit = std::min(stream_block_bytes(P), half);
+  g.max_new = (half / g.unit) * g.unit;
+  return g;
+}
+}  // namespace
+
+// Encodes the first `n` pending bytes as the next piece of the stream (first: carries the window header; last: ISLAST;
+// otherwise byte-aligned by an empty metadata block): one job over [history | new bytes] on the device window.
+static int stream_flush(bgpu_stream* s, size_t n, bool last) {
   bgpu_ctx* c = s->ctx;
   EncParams P = make_params(s->quality, s->lgwin, s->mode);
   CK(cudaSetDevice(c->device));
-  Job job; size_t lens[1] = {n}; plan_job(c, P, lens, 1, job);
-  if (job.shards.size() != 1) return BGPU_E_INVALID;
-  ShardD& sh = job.shards[0];
-  sh.flags = (s->header_done ? 0u : 1u) | (last ? 2u : 0u);
-  for (MbD& mb : job.mbs) mb.is_last = 0;
-  if (last) job.mbs.back().is_last = 1;
-  if (s->header_done) for (SegD& sg : job.segs) sg.ring_known = 0;
+  const StreamGeom g = stream_geom(c, P);
   int rc;
-  if ((rc = c->in.reserve(job.in_bytes + IN_PAD))) return rc;
+  size_t H = g.history ? s->hist_len : 0;
+  const size_t lead = (!g.history && s->header_done) ? 256 : 0;   // no history: the two previous bytes sit right before the piece
+  const size_t cap = (size_t)g.window + IN_PAD + 4096 + 256;
+  if ((rc = s->win[0].reserve(cap)) || (rc = s->win[1].reserve(cap))) return rc;
+  if (H + n > g.window) {
+    // slide: the newest (window - n) history bytes, rounded down to the 4-byte granularity of the tile loads
+    const size_t keep = (g.window - n) & ~(size_t)3;
+    CK(cudaMemcpyAsync(s->win[s->cur ^ 1].p, s->win[s->cur].as<uint8_t>() + (H - keep), keep, cudaMemcpyDeviceToDevice, c->stream));
+    s->cur ^= 1; H = keep;
+  }
+  uint8_t* d_in = s->win[s->cur].as<uint8_t>();
+  bgpu_tuning saved = c->tune;
+  if (!c->tune.metablock_bytes && g.history) c->tune.metablock_bytes = g.unit;   // one metablock per block, as encode.ts:366-374
+  Job job; size_t lens[1] = {H + n}; uint32_t pf[1] = {(s->header_done ? 0u : BGPU_PART_FIRST) | (last ? BGPU_PART_LAST : 0u)};
+  plan_job(c, P, lens, 1, job, pf, lead, H);
+  c->tune = saved;
+  if (job.shards.size() != 1) return BGPU_E_INVALID;
   timing_begin(c);
-  CK(cudaMemcpyAsync(c->in.p, s->pending.data(), n, cudaMemcpyHostToDevice, c->stream));
-  CK(cudaMemsetAsync(c->in.as<uint8_t>() + n, 0, job.in_bytes + IN_PAD - n, c->stream));
+  if (lead) {
+    CK(cudaMemsetAsync(d_in, 0, lead, c->stream));
+    CK(cudaMemcpyAsync(d_in + lead - 2, s->prev2, 2, cudaMemcpyHostToDevice, c->stream));
+  }
+  CK(cudaMemcpyAsync(d_in + lead + H, s->pending.data(), n, cudaMemcpyHostToDevice, c->stream));
+  CK(cudaMemsetAsync(d_in + lead + H + n, 0, cap - lead - H - n, c->stream));
   if ((rc = upload_plan(c, job))) return rc;
-  if ((rc = run_frontend_any(c, job, P, c->in.as<uint8_t>()))) return rc;
-  if ((rc = run_backend(c, job, P, c->in.as<uint8_t>()))) return rc;
-  size_t cap = sh.out_cap, len = 0, old = s->outbuf.size();
-  s->outbuf.resize(old + cap);
-  uint8_t* outs[1] = {s->outbuf.data() + old}; size_t caps[1] = {cap};
-  rc = collect(c, job, c->in.as<uint8_t>(), outs, caps, &len, nullptr, 1);
+  if ((rc = run_frontend_any(c, job, P, d_in))) return rc;
+  if ((rc = run_backend_any(c, job, P, d_in))) return rc;
+  const size_t ocap = n + (n >> 5) + 4096, old = s->outbuf.size();
+  size_t len = 0;
+  s->outbuf.resize(old + ocap);
+  uint8_t* outs[1] = {s->outbuf.data() + old}; size_t caps[1] = {ocap};
+  rc = collect(c, job, d_in, outs, caps, &len, nullptr, 1);
   s->outbuf.resize(old + (rc ? 0 : len));
   timing_end(c);
+  if (rc) return rc;
   s->header_done = true;
+  s->hist_len = g.history ? H + n : 0;
+  if (n >= 2) { s->prev2[0] = s->pending[n - 2]; s->prev2[1] = s->pending[n - 1]; }
+  else if (n == 1) { s->prev2[0] = s->prev2[1]; s->prev2[1] = s->pending[0]; }
   s->pending.erase(s->pending.begin(), s->pending.begin() + n);
-  return rc;
+  return 0;
 }
+
+extern "C" {
 
 int bgpu_stream_update(bgpu_stream* s, const uint8_t* chunk, size_t n, const uint8_t** out, size_t* out_len) {
   if (!s || (n && !chunk) || !out || !out_len) return BGPU_E_INVALID;
@@ -804,10 +862,14 @@ int bgpu_stream_update(bgpu_stream* s, const uint8_t* chunk, size_t n, const uin
   s->pending.insert(s->pending.end(), chunk, chunk + n);
   s->total_in += n;
   EncParams P = make_params(s->quality, s->lgwin, s->mode);
-  size_t shard = std::min<size_t>((size_t)1 << 22, P.lgwin < 22 ? ((((size_t)1 << P.lgwin) - 16) & ~(size_t)3) : ((size_t)1 << 22));
-  if (s->ctx->tune.shard_bytes) shard = std::min<size_t>(shard, std::max<uint32_t>(s->ctx->tune.shard_bytes & ~3u, 64));
-  // keep at least one byte pending so that finish() can mark the final metablock ISLAST
-  while (s->pending.size() > shard) { int rc = stream_flush_shard(s, shard, false); if (rc) return rc; }
+  const StreamGeom g = stream_geom(s->ctx, P);
+  // encode.ts:366-374: whole blocks are emitted as soon as they are complete — all the complete blocks of this call in
+  // as few jobs as the window allows; at least one byte stays pending so that finish() can mark the final metablock ISLAST
+  while (s->pending.size() > g.unit) {
+    const size_t whole = ((s->pending.size() - 1) / g.unit) * g.unit;
+    int rc = stream_flush(s, std::min<size_t>(whole, g.max_new), false);
+    if (rc) return rc;
+  }
   *out = s->outbuf.data(); *out_len = s->outbuf.size();
   return 0;
 }
@@ -817,8 +879,13 @@ int bgpu_stream_finish(bgpu_stream* s, const uint8_t** out, size_t* out_len) {
   if (s->finished) return BGPU_E_STATE;
   s->outbuf.clear();
   if (!s->pending.empty()) {
-    int rc = stream_flush_shard(s, s->pending.size(), true);
-    if (rc) return rc;
+    EncParams P = make_params(s->quality, s->lgwin, s->mode);
+    const StreamGeom g = stream_geom(s->ctx, P);
+    while (!s->pending.empty()) {
+      const size_t n = std::min<size_t>(s->pending.size(), g.max_new);
+      int rc = stream_flush(s, n, n == s->pending.size());
+      if (rc) return rc;
+    }
   } else {
     // encode.ts:399-405: ISLAST + ISEMPTY (after the window header if nothing was written yet)
     HostBits w;
@@ -831,7 +898,12 @@ int bgpu_stream_finish(bgpu_stream* s, const uint8_t** out, size_t* out_len) {
   return 0;
 }
 
-void bgpu_stream_destroy(bgpu_stream* s) { delete s; }
+void bgpu_stream_destroy(bgpu_stream* s) {
+  if (!s) return;
+  if (s->ctx) cudaSetDevice(s->ctx->device);
+  s->win[0].release(); s->win[1].release();
+  delete s;
+}
 
 // ------------------------------------------------------------------ stage entry points
 int bgpu_stage_match_candidates(bgpu_ctx* c, const uint8_t* in, size_t n, int quality, int lgwin, uint32_t* len, uint32_t* dist) {

@@ -38,6 +38,7 @@ struct ShardD {
   uint32_t first_mb, n_mb;
   uint32_t start_nbits, start_value;  // stream header bits (encodeWindowBits) for the first shard
   uint32_t first_stile;  // index of the shard's first sort tile (match_h5.cuh)
+  uint32_t hist;         // leading bytes that are HISTORY (streaming, bgpu.cu stream_flush): matched against, not coded
 };
 struct MbD { uint32_t shard, rel_pos, len, first_seg, n_seg, first_tile, n_tile, is_last; };
 struct SegD { uint32_t shard, rel_pos, len, mb, first_tile, ring_known, pad0, pad1; };

@@ -448,3 +448,54 @@ def test_max_compressed_size_holds_on_incompressible_input(gpu_ctx):
             assert len(s) <= len(data) + (len(data) // 64 + 1) * (64 // 32 + 64 + 6) + 16
     finally:
         gpu_ctx.set_tuning()
+
+
+def test_streaming_blocks_and_window_carry_over(gpu_ctx):
+    """encode.ts:354-388: update() emits a metablock per 1 << lgblock input bytes, and later blocks match into earlier
+    ones (the ring buffer of encode.ts:411-489; here a device-resident sliding window).  A 64 KiB pattern repeated ten
+    times and fed in 10 KiB chunks must compress like the one-shot call, and the reference's own streaming encoder
+    (oracle restatement; trivial metablocks) is the size yardstick."""
+    import brotli_lib_b200 as B
+    from brotli_lib_b200 import workloads as W
+    pattern = W.text(65536, 77).tobytes()
+    data = pattern * 10
+    for q in (5, 9, 2, 11):
+        enc = B.BrotliEncoder(quality=q, context=gpu_ctx)
+        parts, early = [], 0
+        for i in range(0, len(data), 10000):
+            parts.append(enc.update(data[i:i + 10000]))
+            if i + 10000 < len(data) and parts[-1]:
+                early += 1
+        parts.append(enc.finish())
+        s = b"".join(parts)
+        _rt(s, data)
+        lgblock = 14 if q < 4 else (18 if q >= 9 else 16)
+        assert early >= (len(data) >> lgblock) - 2, (q, early)          # blocks leave as they complete, not at finish()
+        one = gpu_ctx.encode(data, q, 22, 0)
+        ref = O.StreamEncoder(q, 22, 0)
+        rs = b"".join([ref.update(data[i:i + 10000]) for i in range(0, len(data), 10000)] + [ref.finish()])
+        assert O.decode(rs, len(data)) == data
+        # repeats of the pattern cost next to nothing once the first copy is in the window
+        assert len(s) <= len(one) * 1.02 + 256, (q, len(s), len(one))
+        # (pure repetition is the worst case of the segment-parallel parse: every 8 KiB segment re-finds the running copy)
+        assert len(s) <= len(rs) * 1.05 + 64 * (len(data) >> lgblock), (q, len(s), len(rs))
+    # long stream: the window slides (history + new > 4 MiB), ragged chunk sizes, every quality class
+    g = Xorshift32(0x12345678)
+    big = (W.mixed_segment(1, 0, 3 << 20).tobytes() + W.mixed_segment(4, 0, 2 << 20).tobytes() + W.mixed_segment(6, 0, 3 << 20).tobytes() + bytes(300001))
+    for q in (1, 5, 10):
+        enc = B.BrotliEncoder(quality=q, context=gpu_ctx)
+        parts, pos = [], 0
+        while pos < len(big):
+            k = 1 + (g.next() % 700001)
+            parts.append(enc.update(big[pos:pos + k]))
+            pos += k
+        parts.append(enc.finish())
+        s = b"".join(parts)
+        _rt(s, big)
+        assert len(s) <= len(gpu_ctx.encode(big, q, 22, 0)) * 1.01 + 1024
+    # small windows keep working (no history below 8 KiB windows; half-window units above)
+    small = load_input("alice29.txt")[:60000]
+    for lgwin in (10, 13, 16):
+        enc = B.BrotliEncoder(quality=5, lgwin=lgwin, context=gpu_ctx)
+        parts = [enc.update(small[i:i + 7001]) for i in range(0, len(small), 7001)] + [enc.finish()]
+        _rt(b"".join(parts), small)
