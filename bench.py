@@ -1,14 +1,22 @@
 #!/usr/bin/env python
 """bench.py — input GB/s of the Brotli encoder hot path (BASELINE.json metric).
 
-A step = one pass of the whole encoder (match finding -> parse -> histograms -> Huffman -> bit
-writer) over one batch of synthetic input.  Default workload: BASELINE config 2 — q5, GENERIC,
-lgwin 22 over 1 GiB of synthetic mixed text/binary, 256 independent 4 MiB shards, on one B200.
-With --gpus N each rank encodes its own 1 GiB (weak scaling, no collective on the data path).
+A step = one pass of the whole encoder (match finding -> parse -> block split / clustering -> histograms -> Huffman ->
+bit writer) over one batch of synthetic input.  Default workload: BASELINE config 2 — q5, GENERIC, lgwin 22 over
+1 GiB of synthetic mixed text/binary, 256 independent 4 MiB shards, on one B200.  With --gpus N (torchrun) each rank
+encodes its own 1 GiB (weak scaling, no collective on the data path).
 
-  value  : device-resident throughput (input already in HBM), whole job
-  e2e    : the same through bgpu_encode with pinned HOST buffers (H2D + kernels + D2H + stitch)
-  --impl reference : the reference's CPU encoder (oracle/ C++ restatement; Node is not available)
+  value         device-resident throughput (input already in HBM), whole job
+  e2e           the same through bgpu_encode with pinned HOST buffers (H2D + kernels + D2H + stitch in the timed region)
+  e2e_pageable  the same call on ordinary (pageable) host memory, as a Node Uint8Array is
+  q11           BASELINE config 3 (q11 TEXT lgwin 24, 256 MiB), measured the same way in the same run
+  cpu_baseline / cpu_lines   the reference's CPU encoder (oracle/ C++ restatement; no JS runtime on the box):
+                single thread and all host threads (4 shards per thread); Google's C encoder as a context line
+  size_delta    compressed size vs the restatement, per 4 MiB shard type
+  extra         config 1 (enc-ttf, q11, one call: latency), config 5 (FONT q11 batch of WOFF2-glyf-like blobs through
+                bgpu_encode_batch), config 4 (q9 lgwin 24: ONE input over all N GPUs through one bgpu_encode call of a
+                bgpu_ctx_create_multi context, one stitched stream, decoded and compared)
+  --impl reference   the reference arm: the restatement on all host threads, bounded sample per step
 """
 import argparse
 import ctypes as C
@@ -110,24 +118,66 @@ def host_threads():
         return os.cpu_count() or 1
 
 
-def cpu_sample(wl, threads):
-    """Bounded CPU sample of the same workload (4 MiB shards)."""
+def sample_shards(wl, count, shard_bytes):
+    """`count` independent shards of the workload's generator, shard i of segment type i mod 8 for the mixed workloads
+    (so any multiple of 8 shards has the workload's type mix), each the first shard_bytes of its 4 MiB segment."""
     import numpy as np
     from brotli_lib_b200 import workloads as W
-    if wl["gen"] == "mixed":
-        # one shard of each of the 8 segment types; the slow qualities take fewer copies of the cycle
-        return np.concatenate([W.mixed_segment(i, 0) for i in range(8)]), "32 MiB = one 4 MiB shard of each of the 8 segment types"
-    k = max(1, min(threads, 16))
-    return np.concatenate([_text_segment(i, 0, W.SEG) for i in range(k)]), f"{4 * k} MiB = {k} text shards of 4 MiB (one per host thread)"
+    fn = W.mixed_segment if wl["gen"] == "mixed" else _text_segment
+    return np.concatenate([fn(i, 0, shard_bytes) for i in range(count)])
 
 
-def time_oracle(sample, quality, lgwin, mode, threads):
+def time_oracle(sample, quality, lgwin, mode, threads, shard_bytes=1 << 22):
+    """The oracle (C++ restatement of brotli-lib's encoder) over `sample` cut into independent shards, `threads` host
+    threads pulling shards from one queue.  Returns (GB/s, per-shard compressed sizes, seconds)."""
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import _oracle as O
     t = time.perf_counter()
-    sizes = O.encode_shards_sizes(sample, 1 << 22, quality, lgwin, mode, threads)
+    sizes = O.encode_shards_sizes(sample, shard_bytes, quality, lgwin, mode, threads)
     dt = time.perf_counter() - t
     return sample.size / dt / 1e9, sizes, dt
+
+
+def cpu_lines(wl, threads):
+    """line A (the restatement) single-thread and on every host thread with 4 shards per thread,
+    line B (the real brotliEncode under Node) when a `node` binary exists, line C (Google's C encoder, context only)."""
+    import shutil
+    q, lgwin, mode = wl["quality"], wl["lgwin"], wl["mode"]
+    shard = (1 << 20) if q < 10 else (1 << 18)
+    one = sample_shards(wl, 8 if wl["gen"] == "mixed" else 2, shard)
+    g1, _, t1 = time_oracle(one, q, lgwin, mode, 1, shard)
+    n_many = 4 * threads
+    many = sample_shards(wl, n_many, shard)
+    gN, _, tN = time_oracle(many, q, lgwin, mode, threads, shard)
+    lines = {
+        "A_single_thread": {"value": g1, "unit": UNIT, "threads": 1, "kind": "port",
+                            "sample": f"{one.size >> 20} MiB = {one.size // shard} shards of {shard >> 10} KiB" + (" (one of each of the 8 segment types)" if wl["gen"] == "mixed" else ""), "seconds": round(t1, 1)},
+        "A_all_threads": {"value": gN, "unit": UNIT, "threads": min(threads, n_many), "kind": "port",
+                          "sample": f"{many.size >> 20} MiB = {n_many} shards of {shard >> 10} KiB (4 per host thread, one work queue)", "seconds": round(tN, 1)},
+    }
+    node = shutil.which("node")
+    lines["B_node"] = {"node": node, "note": "the reference's own TypeScript needs a resolver hook and --experimental-transform-types (SURVEY.md section 8b); not wired"} if node \
+        else "node: unavailable on this box (command -v node fails; deno / bun / qjs absent too: profiles/r4a_gpu_box_js_runtime_probe.txt)"
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import _oracle as O
+        t = time.perf_counter()
+        csz = sum(len(O.ref_encode(one[o:o + shard], q, lgwin, 0)) for o in range(0, one.size, shard))
+        dt = time.perf_counter() - t
+        lines["C_google_c_encoder"] = {"value": one.size / dt / 1e9, "unit": UNIT, "threads": 1, "library": "system libbrotlienc (1.1.0)", "sample": lines["A_single_thread"]["sample"],
+                                       "compressed_ratio": round(csz / one.size, 4), "note": "context only: a different encoder (lazy matching, static dictionary), never a parity target"}
+    except Exception as e:   # pragma: no cover
+        lines["C_google_c_encoder"] = f"unavailable: {e}"
+    return lines
+
+
+def size_sample(wl):
+    """The shards of the ratio accounting: real 4 MiB shards, one of each segment type."""
+    import numpy as np
+    from brotli_lib_b200 import workloads as W
+    if wl["gen"] == "mixed":
+        return np.concatenate([W.mixed_segment(i, 0) for i in range(8)]), "one 4 MiB shard of each of the 8 segment types"
+    return np.concatenate([_text_segment(i, 0, W.SEG) for i in range(8)]), "8 text shards of 4 MiB"
 
 
 def size_delta(sample, ref_sizes, quality, lgwin, mode, device, tune=None):
@@ -169,10 +219,16 @@ ALGO_BYTES = {
     "zopfli": lambda n, M, S: 2 * (9.0 * n + 8.0 * S),       # K6, two passes: N + 8N + 8 * matches (+16C) each
     "histograms": lambda n, M, S: 1.0 * n,                   # K7: L (+16C + 4AH), L <= N
     "block_split": lambda n, M, S: 1.0 * n,                  # K8: the symbol streams once
-    "clustering": lambda n, M, S: 0.0,                       # K9: 4A(H_in + H_out): small tables
-    "huffman": lambda n, M, S: 0.0,                          # K10: 7AH bytes: negligible
+    "clustering": lambda n, M, S: 0.0,                       # K9: 4A(H_in + H_out): from the device counters (BGPU_F_MODEL_STATS), see measure()
+    "huffman": lambda n, M, S: 0.0,                          # K10: 7AH: from the device counters
     "bit_writer": lambda n, M, S: n + M,                     # K11: L + M (+16C + 3AH)
 }
+
+
+def stage_of(name, quality):
+    if name == "k_stitch" and quality >= 10:
+        return "zopfli"      # at q10/11 the stitch joins Zopfli segments; there is no greedy parse stage
+    return STAGE_OF.get(name)
 
 
 def peaks():
@@ -198,25 +254,37 @@ def ncu_traffic(stage, n):
 
 
 def run_reference(args, wl, rank, world):
+    """The reference's CPU implementation of the path (the oracle restatement: no JS runtime exists on the box) with all
+    the host threads, 4 shards per thread from one work queue.  A step is a bounded sample of the arm's workload — the
+    same generators, quality, window and mode, shard size chosen from a calibration pass so that the K + W steps take
+    about 100 s — because the full workload would take about a minute per step on these cores."""
     if rank != 0:
         return
     threads = host_threads()
-    sample, what = cpu_sample(wl, threads)
     q, lgwin, mode = wl["quality"], wl["lgwin"], wl["mode"]
-    for _ in range(min(args.warmup, 1)):
-        time_oracle(sample[: 1 << 20], q, lgwin, mode, 1)
+    n_shards = 4 * threads
+    probe = sample_shards(wl, n_shards, 1 << 16)
+    rate, _, _ = time_oracle(probe, q, lgwin, mode, threads, 1 << 16)
+    budget = max(1.0, min(20.0, 100.0 / max(1, args.steps + args.warmup)))
+    shard = 1 << 16
+    while shard < (1 << 22) and 2 * shard * n_shards / (rate * 1e9) <= budget:
+        shard *= 2
+    sample = sample_shards(wl, n_shards, shard)
+    what = f"{sample.size >> 20} MiB per step = {n_shards} independent shards of {shard >> 10} KiB (4 per host thread, types cycling as in the workload)"
+    for _ in range(args.warmup):
+        time_oracle(sample, q, lgwin, mode, threads, shard)
     t0 = time.perf_counter()
     for _ in range(args.steps):
-        time_oracle(sample, q, lgwin, mode, threads)
+        time_oracle(sample, q, lgwin, mode, threads, shard)
     wall = time.perf_counter() - t0
     value = sample.size * args.steps / wall / 1e9
     line = {
         "impl": "reference", "metric": wl["metric"], "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": wall / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "u8",
         "data": "synthetic",
-        "config": {"workload": wl["label"].format(mb=wl["size_mb"], shards=wl["size_mb"] // 4), "sample": what + " per step"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port",
-                         "sample": "oracle/ C++ restatement of brotli-lib (Node unavailable on this box); " + what + " per step"},
+        "config": {"workload": wl["label"].format(mb=wl["size_mb"], shards=wl["size_mb"] // 4)},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": min(threads, n_shards), "kind": "port",
+                         "sample": "oracle/ C++ restatement of brotli-lib (no JS runtime on this box), " + what},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -283,10 +351,31 @@ def measure(args, wl, ctx, torch, dist, dev, rank, world, local_rank, steps, war
     ev1.record(stream)
     barrier()
     t_e2e = ev0.elapsed_time(ev1) * 1e-3
+    # ---- the same call on pageable host memory (what a Node Uint8Array is): the driver stages the copies
+    import numpy as np
+    pg_out = np.empty(cap, dtype=np.uint8)
+
+    def step_e2e_pageable():
+        ln = C.c_size_t(0)
+        rc = L.bgpu_encode(ctx._h, host.ctypes.data, n, q, lgwin, mode, pg_out.ctypes.data, cap, C.byref(ln))
+        if rc:
+            raise RuntimeError(f"bgpu_encode rc={rc}: {L.bgpu_last_cuda_error().decode()}")
+        return ln.value
+
+    step_e2e_pageable()
+    pg_steps = max(1, min(steps, 3))
+    barrier()
+    ev0.record(stream)
+    for _ in range(pg_steps):
+        step_e2e_pageable()
+    ev1.record(stream)
+    barrier()
+    t_pg = ev0.elapsed_time(ev1) * 1e-3 / pg_steps
+    del pg_out
     # ---- per-kernel durations: in the timed regions above the groups of shards run on several CUDA
     # streams (lanes) and kernels of different groups overlap, so a kernel's own duration is taken from
     # one-lane (in-order) passes of the same work, CUDA events around every launch family
-    ctx.set_tuning(**dict(tune, lanes=1))
+    ctx.set_tuning(**dict(tune, lanes=1, flags=(tune.get("flags") or 0) | 8))   # 8 = BGPU_F_MODEL_STATS: table bytes of the modelling stages
     step_device()
     stage_ms = {}
     stage_steps = max(1, min(steps, 2))
@@ -296,14 +385,15 @@ def measure(args, wl, ctx, torch, dist, dev, rank, world, local_rank, steps, war
         step_device()
         for name, ms in ctx.timings():
             stage_ms[name] = stage_ms.get(name, 0.0) + ms
+        model_bytes = [ctx.counter(1) + ctx.counter(2), ctx.counter(3)]
     ev1.record(stream)
     barrier()
     t_one_lane = ev0.elapsed_time(ev1) * 1e-3 / stage_steps
     ctx.set_tuning(**tune)
-    times = torch.tensor([t_dev, t_e2e], dtype=torch.float64, device=dev)
+    times = torch.tensor([t_dev, t_e2e, t_pg], dtype=torch.float64, device=dev)
     if dist is not None:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
-    t_dev, t_e2e = times.tolist()
+    t_dev, t_e2e, t_pg = times.tolist()
     # ---- verification outside the timed region (rank 0): the stream decodes to the input
     verified = None
     if rank == 0 and verify:
@@ -319,12 +409,16 @@ def measure(args, wl, ctx, torch, dist, dev, rank, world, local_rank, steps, war
     for name, ms in stage_ms.items():
         avg = ms / stage_steps
         per_kernel[name] = round(per_kernel.get(name, 0.0) + avg, 3)
-        st = STAGE_OF.get(name)
+        st = stage_of(name, q)
         if st:
             per_stage[st] = per_stage.get(st, 0.0) + avg
     stages = {}
     for st, avg in per_stage.items():
         ab = ALGO_BYTES[st](float(n), float(M), float(n_matches))
+        if st == "clustering":
+            ab = float(model_bytes[0])
+        elif st == "huffman":
+            ab = float(model_bytes[1])
         stages[st] = {"ms": round(avg, 3), "algo_bytes": int(ab), "algo_GBps": round(ab / (avg * 1e-3) / 1e9, 1) if avg > 0 else None,
                       "frac": round(ab / (avg * 1e-3) / 1e9 / peak, 4) if avg > 0 else None}
     top = max(stages, key=lambda k: stages[k]["ms"])
@@ -340,13 +434,114 @@ def measure(args, wl, ctx, torch, dist, dev, rank, world, local_rank, steps, war
                    "l2": f"input ({wl['size_mb']} MiB) and every intermediate array exceed the 126 MB L2; no flush needed",
                    "compressed_ratio": round(M / n, 4), "verified_roundtrip": verified, "datagen_s": round(t_gen, 1),
                    "h10_matches_per_position": round(n_matches / n, 3) if n_matches else None},
-        "e2e": {"value": n * world * steps / t_e2e / 1e9, "unit": UNIT, "h2d_bytes_per_step": n, "d2h_bytes_per_step": int(e2e_size)},
+        "e2e": {"value": n * world * steps / t_e2e / 1e9, "unit": UNIT, "h2d_bytes_per_step": n, "d2h_bytes_per_step": int(e2e_size), "host_memory": "pinned"},
+        "e2e_pageable": {"value": n * world / t_pg / 1e9, "unit": UNIT, "steps": pg_steps, "host_memory": "pageable (numpy arrays, as a Node Uint8Array)",
+                         "h2d_bytes_per_step": n, "d2h_bytes_per_step": int(e2e_size)},
         "gpu_launches": launches,
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": top, "kernels": STAGE_KERNELS.get(top, top), "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": round(achieved / peak, 4),
                      "traffic": ncu_traffic(top, n), "peak_source": which, "whole_step_frac": round((n + M) * steps / t_dev / 1e9 / peak, 4),
                      "stages": stages, "launch_ms": per_kernel},
     }
+
+
+def cpu_block(wl, threads, device, tune):
+    """cpu_baseline (all host threads), the three BASELINE.md lines, and the per-shard size accounting."""
+    lines = cpu_lines(wl, threads)
+    a = lines["A_all_threads"]
+    base = {"value": a["value"], "unit": UNIT, "cores": a["threads"], "kind": "port",
+            "sample": f"oracle/ C++ restatement of brotli-lib (no JS runtime on this box), {a['sample']}, {a['seconds']} s; single thread: {lines['A_single_thread']['value']:.5f} GB/s"}
+    sample, what = size_sample(wl)
+    _, sizes, _ = time_oracle(sample, wl["quality"], wl["lgwin"], wl["mode"], threads)
+    sd = size_delta(sample, sizes, wl["quality"], wl["lgwin"], wl["mode"], device, tune)
+    sd["sample"] = what
+    return base, lines, sd
+
+
+def extra_config1(ctx, torch):
+    """BASELINE config 1: brotliEncode q11 lgwin22 GENERIC on bench/fixtures/enc-ttf.bin (312 668 bytes): ONE shard, so the
+    figure is the latency of one call (host buffers in and out), not a throughput the GPU is sized for."""
+    path = os.path.join(ROOT, "tests", "golden", "data", "enc-ttf.bin")
+    data = open(path, "rb").read()
+    for _ in range(2):
+        out = ctx.encode(data, 11, 22, 0)
+    ts = []
+    for _ in range(5):
+        torch.cuda.synchronize()
+        t = time.perf_counter()
+        out = ctx.encode(data, 11, 22, 0)
+        ts.append(time.perf_counter() - t)
+    ts.sort()
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import _oracle as O
+    ok = O.decode(out, len(data)) == data
+    t = time.perf_counter()
+    ref = O.encode(data, 11, 22, 0)
+    t_cpu = time.perf_counter() - t
+    return {"workload": "brotliEncode q11 lgwin22 GENERIC on bench/fixtures/enc-ttf.bin (312668 bytes), one call = one shard", "ms_per_call_median": round(ts[2] * 1e3, 2),
+            "ms_per_call_min": round(ts[0] * 1e3, 2), "input_GBps": len(data) / ts[2] / 1e9, "compressed_bytes": len(out), "oracle_bytes": len(ref),
+            "size_delta": round((len(out) - len(ref)) / len(ref), 5), "verified_roundtrip": ok, "launches": ctx.launch_count(),
+            "stages_ms": {k: round(v, 2) for k, v in ctx.timings() if v >= 0.05},
+            "cpu_restatement_ms_single_thread": round(t_cpu * 1e3, 1)}
+
+
+def extra_config5(ctx, torch, n_blobs):
+    """BASELINE config 5: FONT mode q11 batch of WOFF2-transformed glyf-like blobs (4-300 KB each) through ONE
+    bgpu_encode_batch call; every blob is its own stream."""
+    from brotli_lib_b200 import workloads as W
+    blobs = [b.tobytes() for b in W.font_blobs(n_blobs)]
+    total = sum(len(b) for b in blobs)
+    ctx.encode_batch(blobs[: max(8, n_blobs // 20)], 11, 22, 2)
+    torch.cuda.synchronize()
+    t = time.perf_counter()
+    outs = ctx.encode_batch(blobs, 11, 22, 2)
+    dt = time.perf_counter() - t
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import _oracle as O
+    check = list(range(0, n_blobs, max(1, n_blobs // 50)))
+    ok = all(O.decode(outs[i], len(blobs[i])) == blobs[i] for i in check)
+    return {"workload": f"FONT q11 lgwin22 batch of {n_blobs} WOFF2-glyf-like blobs, log-uniform 4-300 KiB (BASELINE config 5 is 10000 blobs; --config5-blobs sets the count), one bgpu_encode_batch call, host buffers",
+            "blobs": n_blobs, "input_bytes": total, "seconds": round(dt, 3), "input_GBps": total / dt / 1e9, "blobs_per_s": round(n_blobs / dt, 1),
+            "compressed_ratio": round(sum(len(o) for o in outs) / total, 4), "verified_roundtrip": ok, "verified_blobs": len(check), "launches": ctx.launch_count()}
+
+
+def extra_config4(torch, devices, mb_per_gpu, steps):
+    """BASELINE config 4 as north_star describes it: ONE input, cut into one part per GPU, each part compressed on its
+    own GPU, stitched on the host into a single valid stream — one bgpu_encode call on a bgpu_ctx_create_multi context
+    (one host thread per device), host buffers in and out.  Wall-clock of the call (it returns when the stream is complete)."""
+    import numpy as np
+    import brotli_lib_b200 as B
+    wl = WORKLOADS["config4"]
+    n = (mb_per_gpu << 20) * len(devices)
+    host = gen_data(wl["gen"], n, 0)
+    ctx = B.Context(devices=devices)
+    L = ctx._L
+    cap = int(L.bgpu_max_compressed_size(n))
+    out = np.empty(cap, dtype=np.uint8)
+    ln = C.c_size_t(0)
+
+    def call():
+        rc = L.bgpu_encode(ctx._h, host.ctypes.data, n, wl["quality"], wl["lgwin"], wl["mode"], out.ctypes.data, cap, C.byref(ln))
+        if rc:
+            raise RuntimeError(f"bgpu_encode (multi) rc={rc}: {L.bgpu_last_cuda_error().decode()}")
+    call()
+    ts = []
+    for _ in range(max(1, steps)):
+        t = time.perf_counter()
+        call()
+        ts.append(time.perf_counter() - t)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import _oracle as O
+    t = time.perf_counter()
+    ok = O.decode(out[: ln.value].tobytes(), n) == host.tobytes()
+    t_dec = time.perf_counter() - t
+    launches = ctx.launch_count()
+    ctx.close()
+    best = min(ts)
+    return {"workload": f"q9 GENERIC lgwin24, ONE {n >> 20} MiB input ({mb_per_gpu} MiB per GPU; BASELINE config 4 is 8 GiB over 8 GPUs: --config4-mb-per-gpu 1024) over {len(devices)} GPU(s), one stitched stream",
+            "n_gpus": len(devices), "input_bytes": n, "e2e_GBps": n / best / 1e9, "seconds_best": round(best, 3), "seconds_all": [round(x, 3) for x in ts],
+            "host_memory": "pageable", "compressed_ratio": round(ln.value / n, 4), "verified_roundtrip": ok, "decode_seconds_cpu": round(t_dec, 1), "launches": launches,
+            "limiter": "see DESIGN.md section 5: per-device H2D from one pageable buffer + the final parallel memcpy of the parts"}
 
 
 def run_gpu(args, wl, rank, world, local_rank):
@@ -366,33 +561,38 @@ def run_gpu(args, wl, rank, world, local_rank):
     ctx.close()
     torch.cuda.empty_cache()
     q11 = None
+    tune11 = {"lanes": args.q11_lanes, "group_shards": args.q11_group_shards}
     if args.workload == "config2" and not args.no_q11:
         # the metric names q5 AND q11: BASELINE config 3 measured in the same run, reported beside the headline
         ctx = B.Context(local_rank)
         w3 = dict(WORKLOADS["config3"])
         if args.q11_size_mb:
             w3["size_mb"] = args.q11_size_mb
-        tune11 = {"lanes": args.q11_lanes, "group_shards": args.q11_group_shards}
         ctx.set_tuning(**tune11)
         q11 = measure(args, w3, ctx, torch, dist, dev, rank, world, local_rank, min(args.steps, 3), 3, not args.no_verify, tune11)
         ctx.close()
+        torch.cuda.empty_cache()
     if rank == 0:
         if q11 is not None:
-            line["q11"] = {k: q11[k] for k in ("metric", "value", "unit", "steps", "warmup", "ms_per_step", "config", "e2e", "gpu_launches", "roofline")}
+            line["q11"] = {k: q11[k] for k in ("metric", "value", "unit", "steps", "warmup", "ms_per_step", "config", "e2e", "e2e_pageable", "gpu_launches", "roofline")}
         if world == 1 and not args.no_cpu:
             threads = host_threads()
-            sample, what = cpu_sample(wl, threads)
-            gbps, sizes, dt = time_oracle(sample, wl["quality"], wl["lgwin"], wl["mode"], threads)
-            line["cpu_baseline"] = {"value": gbps, "unit": UNIT, "cores": threads, "kind": "port",
-                                    "sample": f"oracle/ C++ restatement of brotli-lib, {what}, {dt:.1f} s"}
-            line["size_delta"] = size_delta(sample, sizes, wl["quality"], wl["lgwin"], wl["mode"], local_rank, tune)
+            line["cpu_baseline"], line["cpu_lines"], line["size_delta"] = cpu_block(wl, threads, local_rank, tune)
             if q11 is not None:
-                w3 = WORKLOADS["config3"]
-                sample, what = cpu_sample(w3, threads)
-                gbps, sizes, dt = time_oracle(sample, w3["quality"], w3["lgwin"], w3["mode"], threads)
-                line["q11"]["cpu_baseline"] = {"value": gbps, "unit": UNIT, "cores": threads, "kind": "port",
-                                               "sample": f"oracle/ C++ restatement of brotli-lib, {what}, {dt:.1f} s"}
-                line["q11"]["size_delta"] = size_delta(sample, sizes, w3["quality"], w3["lgwin"], w3["mode"], local_rank, tune11)
+                line["q11"]["cpu_baseline"], line["q11"]["cpu_lines"], line["q11"]["size_delta"] = cpu_block(WORKLOADS["config3"], threads, local_rank, tune11)
+        if not args.no_extra and args.workload == "config2":
+            extra = {}
+            try:
+                if world == 1:
+                    ectx = B.Context(local_rank)
+                    extra["config1"] = extra_config1(ectx, torch)
+                    extra["config5"] = extra_config5(ectx, torch, args.config5_blobs)
+                    ectx.close()
+                n_dev = min(world, torch.cuda.device_count())
+                extra["config4"] = extra_config4(torch, list(range(n_dev)), args.config4_mb_per_gpu, 2)
+            except Exception as e:   # an extra leg never takes the headline line down
+                extra["error"] = f"{type(e).__name__}: {e}"
+            line["extra"] = extra
         print(json.dumps(line))
     if dist is not None:
         dist.barrier()
@@ -419,6 +619,9 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     ap.add_argument("--no-q11", action="store_true", help="skip the config-3 (q11) measurement that accompanies the default run")
     ap.add_argument("--q11-size-mb", type=int, default=0)
+    ap.add_argument("--no-extra", action="store_true", help="skip the config 1 / 4 / 5 legs")
+    ap.add_argument("--config5-blobs", type=int, default=2000, help="blobs of the config-5 batch leg (BASELINE: 10000)")
+    ap.add_argument("--config4-mb-per-gpu", type=int, default=256, help="input MiB per GPU of the stitched multi-GPU leg (BASELINE: 1024)")
     args = ap.parse_args()
     wl = dict(WORKLOADS[args.workload])
     if args.size_mb:

@@ -112,7 +112,7 @@ struct bgpu_ctx {
   DBuf in, sa_pos, sa_v, sb_pos, sb_v, sort_hist, role, ins, cmds, out, shards, mbs, segs, tile_seg, seg_ncmd, seg_trail, seg_ring, hist, codes, tree_bits, tree_nbits,
       tile_bits, tile_off, tile_model, warp_base, thr_off, shard_bytes, huff_meta, model_arena, misc_arena, d_models, d_splits, d_cb, d_cx, d_bh_ptrs, d_bh_strides, d_cx_outs,
       h10_bstart, h10_bend, h10_short, h10_forest, h10_m, h10_off, h10_cnt, h10_cursor, h10_full, h10_hot,
-      zop_bytehist, zop_model, zop_lc, zop_nodes, zop_ring;
+      zop_bytehist, zop_model, zop_lc, zop_nodes, zop_ring, stats;
   uint32_t h10_cap = 0;
   uint64_t counters[4] = {0, 0, 0, 0};   // [0] H10 match entries of the last q10/q11 call
   bool lut_ready = false;
@@ -382,7 +382,7 @@ int run_frontend_any(bgpu_ctx* ctx, const Job& job, const EncParams& P, const ui
 
 void timing_begin(bgpu_ctx* ctx) {
   pin_rewind(ctx);
-  ctx->n_stage = 0; ctx->launches = 0; ctx->counters[0] = 0;
+  ctx->n_stage = 0; ctx->launches = 0; for (int i = 0; i < 4; i++) ctx->counters[i] = 0;
   if (ctx->ev_ok) cudaEventRecord(ctx->ev[0], ctx->stream);
 }
 void timing_end(bgpu_ctx* ctx) {
@@ -561,7 +561,7 @@ void bgpu_ctx_destroy(bgpu_ctx* c) {
                  &c->seg_trail, &c->seg_ring, &c->hist, &c->codes, &c->tree_bits, &c->tree_nbits, &c->tile_bits, &c->tile_off, &c->tile_model, &c->warp_base, &c->thr_off, &c->shard_bytes, &c->huff_meta,
                  &c->model_arena, &c->misc_arena, &c->d_models, &c->d_splits, &c->d_cb, &c->d_cx, &c->d_bh_ptrs, &c->d_bh_strides, &c->d_cx_outs,
                  &c->h10_bstart, &c->h10_bend, &c->h10_short, &c->h10_forest, &c->h10_m, &c->h10_off, &c->h10_cnt, &c->h10_cursor, &c->h10_full, &c->h10_hot,
-                 &c->zop_bytehist, &c->zop_model, &c->zop_lc, &c->zop_nodes, &c->zop_ring};
+                 &c->zop_bytehist, &c->zop_model, &c->zop_lc, &c->zop_nodes, &c->zop_ring, &c->stats};
   for (DBuf* b : all) b->release();
   for (bgpu_ctx* l : c->lanes) bgpu_ctx_destroy(l);
   c->lanes.clear();

@@ -186,6 +186,28 @@ __global__ void __launch_bounds__(256) k_cluster_sum(const ClusterProb* __restri
   }
 }
 
+// SURVEY.md section 8d table bytes of the modelling stages, summed over the metablocks (BGPU_F_MODEL_STATS).
+// out[0] += 4 A H_in, out[1] += 4 A H_out of the clustering problems (clusterBlocks per category, then the two context
+// maps), out[2] += 7 A H of the prefix codes actually built.  One thread per metablock.
+__global__ void k_model_stats(const MbModel* __restrict__ models, uint32_t n_mb, uint32_t dist_alphabet, unsigned long long* __restrict__ out) {
+  const uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;
+  if (m >= n_mb) return;
+  const MbModel& M = models[m];
+  const uint32_t A[3] = {ALPHA_LIT, ALPHA_CMD, dist_alphabet};
+  unsigned long long in_b = 0, out_b = 0, huff = 0;
+  const bool trivial = M.cnt[4] != 0;
+  for (int c = 0; c < 3; c++) {
+    const uint32_t nb = M.sstate[c][1], nt = M.sstate[c][2];
+    if (nb > 1) { in_b += 4ull * A[c] * nb; out_b += 4ull * A[c] * nt; }
+  }
+  if (!trivial) {
+    in_b += 4ull * 256 * M.sstate[LIT][2] * 64 + 4ull * dist_alphabet * M.sstate[DIST][2] * 4;
+    out_b += 4ull * 256 * M.cstate[LIT][2] + 4ull * dist_alphabet * M.cstate[DIST][2];
+  }
+  huff = 7ull * (256ull * M.cstate[LIT][2] + (unsigned long long)ALPHA_CMD * M.sstate[CMD][2] + (unsigned long long)dist_alphabet * M.cstate[DIST][2]);
+  atomicAdd(&out[0], in_b); atomicAdd(&out[1], out_b); atomicAdd(&out[2], huff);
+}
+
 // Prefix codes of a metablock.  grid (HDR_TREE_SLOTS, metablocks), 128 threads.
 // slot < 64: literal cluster; 64..319: command block type; 320..383: distance cluster.
 __global__ void __launch_bounds__(128) k_huff_mb(const MbModel* __restrict__ models, int dist_alphabet) {

@@ -48,6 +48,7 @@ typedef struct bgpu_tuning {
 } bgpu_tuning;
 #define BGPU_F_KEEP_DEVICE_OUTPUT 1u /* bench: skip the device->host gather (device-resident timing) */
 #define BGPU_F_RING_HANDOVER 4u      /* greedy parse: segments guess the last distance at their start and k_ring_handover re-codes their first copies against the decoder's ring */
+#define BGPU_F_MODEL_STATS 8u        /* bench: after the call bgpu_last_counter(1..3) hold the table bytes of the clustering / Huffman stages (one extra tiny kernel + a blocking read-back) */
 #define BGPU_F_TRIVIAL_METABLOCKS 2u /* storeMetaBlockTrivial for every metablock (metablock.ts:290-389): no block split, no context map */
 
 /* Context: owns the CUDA device, stream, scratch arenas.  Not thread-safe; one per thread.
@@ -207,7 +208,10 @@ int bgpu_stage_h10_matches(bgpu_ctx* ctx, const uint8_t* in, size_t n, int lgwin
 int bgpu_stage_timings(bgpu_ctx* ctx, const char** names, float* ms, int cap);
 /* Number of kernel launches issued by the last encode call. */
 int bgpu_last_launch_count(bgpu_ctx* ctx);
-/* Work counters of the last encode call: which = 0 -> H10 match entries found (sum over all positions). */
+/* Work counters of the last encode call: which = 0 -> H10 match entries found (sum over all positions); with
+ * BGPU_F_MODEL_STATS also 1 -> bytes of histogram rows entering the clustering problems (4 A H_in; clusterBlocks + context
+ * maps), 2 -> bytes of rows leaving them (4 A H_out), 3 -> bytes of the prefix-code stage (7 A H: u32 count in, u8 depth +
+ * u16 code out), SURVEY.md section 8d's per-stage algorithmic traffic. */
 uint64_t bgpu_last_counter(bgpu_ctx* ctx, int which);
 
 const char* bgpu_strerror(int code);
