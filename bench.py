@@ -389,6 +389,20 @@ def measure(args, wl, ctx, torch, dist, dev, rank, world, local_rank, steps, war
     ev1.record(stream)
     barrier()
     t_one_lane = ev0.elapsed_time(ev1) * 1e-3 / stage_steps
+    # ---- on-device verification of the device-resident result at full size (BGPU_F_VERIFY: every shard decoded by the
+    # library's own device decoder and compared with the input in HBM; no device->host copy, no CPU decode)
+    device_verified, t_verify = None, None
+    if verify:
+        ctx.set_tuning(**dict(tune, flags=(tune.get("flags") or 0) | 16))
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        try:
+            step_device()
+            device_verified = ctx.counter(4) == 0
+        except Exception as e:
+            device_verified = f"FAILED: {e}"
+        torch.cuda.synchronize()
+        t_verify = time.perf_counter() - t0
     ctx.set_tuning(**tune)
     times = torch.tensor([t_dev, t_e2e, t_pg], dtype=torch.float64, device=dev)
     if dist is not None:
@@ -432,7 +446,8 @@ def measure(args, wl, ctx, torch, dist, dev, rank, world, local_rank, steps, war
                    "lanes": tune.get("lanes") or "library default (4 lanes, groups of shards/4 clamped to 16..64, for q5-9; 1 lane for q10/11)",
                    "stage_timing": f"roofline.stages / launch_ms: one-lane in-order passes after the timed region ({round(t_one_lane * 1e3, 1)} ms per step)",
                    "l2": f"input ({wl['size_mb']} MiB) and every intermediate array exceed the 126 MB L2; no flush needed",
-                   "compressed_ratio": round(M / n, 4), "verified_roundtrip": verified, "datagen_s": round(t_gen, 1),
+                   "compressed_ratio": round(M / n, 4), "verified_roundtrip": verified, "verified_on_device": device_verified,
+                   "verify_on_device_s": round(t_verify, 2) if t_verify else None, "datagen_s": round(t_gen, 1),
                    "h10_matches_per_position": round(n_matches / n, 3) if n_matches else None},
         "e2e": {"value": n * world * steps / t_e2e / 1e9, "unit": UNIT, "h2d_bytes_per_step": n, "d2h_bytes_per_step": int(e2e_size), "host_memory": "pinned"},
         "e2e_pageable": {"value": n * world / t_pg / 1e9, "unit": UNIT, "steps": pg_steps, "host_memory": "pageable (numpy arrays, as a Node Uint8Array)",

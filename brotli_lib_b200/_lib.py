@@ -11,7 +11,7 @@ E_UNSUPPORTED = -3
 
 SYMBOLS = [
     "bgpu_ctx_create", "bgpu_ctx_create_multi", "bgpu_ctx_destroy", "bgpu_ctx_set_tuning", "bgpu_ctx_set_stream", "bgpu_max_compressed_size", "bgpu_encode",
-    "bgpu_encode_batch", "bgpu_encode_part", "bgpu_encode_device", "bgpu_stream_create", "bgpu_stream_update", "bgpu_stream_finish",
+    "bgpu_encode_batch", "bgpu_encode_part", "bgpu_encode_device", "bgpu_decode", "bgpu_stream_create", "bgpu_stream_update", "bgpu_stream_finish",
     "bgpu_stream_destroy", "bgpu_stage_match_candidates", "bgpu_stage_commands", "bgpu_stage_store_trivial",
     "bgpu_stage_huffman", "bgpu_stage_h10_matches", "bgpu_stage_histograms", "bgpu_stage_context_map", "bgpu_stage_store_metablock", "bgpu_stage_timings", "bgpu_last_launch_count", "bgpu_last_counter", "bgpu_strerror", "bgpu_last_cuda_error",
     "bgpu_version",
@@ -56,6 +56,7 @@ def load():
     L.bgpu_encode_batch.argtypes = [vp, i, C.POINTER(vp), szp, i, i, i, C.POINTER(vp), szp, szp]
     L.bgpu_encode_part.argtypes = [vp, vp, sz, vp, C.c_uint, i, i, i, vp, sz, szp]
     L.bgpu_encode_device.argtypes = [vp, vp, sz, i, i, i, vp, sz, szp, C.POINTER(C.c_float)]
+    L.bgpu_decode.argtypes = [vp, vp, sz, vp, sz, szp]
     L.bgpu_stream_create.argtypes = [vp, i, i, i, C.POINTER(vp)]
     L.bgpu_stream_update.argtypes = [vp, vp, sz, C.POINTER(vp), szp]
     L.bgpu_stream_finish.argtypes = [vp, C.POINTER(vp), szp]
@@ -87,7 +88,7 @@ class BgpuError(RuntimeError):
         self.code = code
         msg = L.bgpu_strerror(code).decode()
         detail = L.bgpu_last_cuda_error().decode()
-        super().__init__(f"brotligpu: {msg} ({code})" + (f": {detail}" if detail and code in (-4, -5, -6) else ""))
+        super().__init__(f"brotligpu: {msg} ({code})" + (f": {detail}" if detail and code in (-4, -5, -6, -8, -9) else ""))
 
 
 def check(rc):

@@ -5,6 +5,7 @@
 #include "metablock_write.cuh"
 #include "h10.cuh"
 #include "zopfli.cuh"
+#include "decode.cuh"
 
 #include <algorithm>
 #include <atomic>
@@ -112,9 +113,9 @@ struct bgpu_ctx {
   DBuf in, sa_pos, sa_v, sb_pos, sb_v, sort_hist, role, ins, cmds, out, shards, mbs, segs, tile_seg, seg_ncmd, seg_trail, seg_ring, hist, codes, tree_bits, tree_nbits,
       tile_bits, tile_off, tile_model, warp_base, thr_off, shard_bytes, huff_meta, model_arena, misc_arena, d_models, d_splits, d_cb, d_cx, d_bh_ptrs, d_bh_strides, d_cx_outs,
       h10_bstart, h10_bend, h10_short, h10_forest, h10_m, h10_off, h10_cnt, h10_cursor, h10_full, h10_hot,
-      zop_bytehist, zop_model, zop_lc, zop_nodes, zop_ring, stats;
+      zop_bytehist, zop_model, zop_lc, zop_nodes, zop_ring, stats, dec_arena, dec_results, dec_jobs;
   uint32_t h10_cap = 0;
-  uint64_t counters[4] = {0, 0, 0, 0};   // [0] H10 match entries of the last q10/q11 call
+  uint64_t counters[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // [0] H10 match entries; [1..3] model table bytes (BGPU_F_MODEL_STATS); [4] shards that failed BGPU_F_VERIFY
   bool lut_ready = false;
   std::vector<uint32_t> h_shard_bytes;
   // multi-device (multi_host.inc): one private context per device of bgpu_ctx_create_multi; parts of one input run on
@@ -283,11 +284,36 @@ int upload_plan(bgpu_ctx* ctx, const Job& job) {
 
 #include "model_host.inc"
 
+// BGPU_F_VERIFY: every shard of the job decoded on the device (decode.cuh) and compared with the staged input.
+int run_verify(bgpu_ctx* ctx, const Job& job, const uint8_t* d_in) {
+  cudaStream_t st = ctx->stream;
+  const uint32_t n_shard = (uint32_t)job.shards.size();
+  int rc;
+  if ((rc = ensure_lut(ctx))) return rc;
+  if ((rc = ctx->dec_arena.reserve((size_t)n_shard * sizeof(DecArena)))) return rc;
+  if ((rc = ctx->dec_results.reserve((size_t)n_shard * sizeof(DecResult)))) return rc;
+  k_verify_shards<<<n_shard, 32, 0, st>>>(ctx->out.as<uint8_t>(), ctx->shards.as<ShardD>(), ctx->shard_bytes.as<uint32_t>(), n_shard, d_in,
+                                         ctx->dec_arena.as<DecArena>(), ctx->dec_results.as<DecResult>());
+  ctx->launches++; stage_mark(ctx, "k_verify");
+  std::vector<DecResult> res(n_shard);
+  CK(cudaMemcpyAsync(res.data(), ctx->dec_results.p, (size_t)n_shard * sizeof(DecResult), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  uint64_t bad = 0;
+  for (uint32_t k = 0; k < n_shard; k++)
+    if (res[k].status != BGPU_DEC_OK) {
+      if (!bad) { char b[160]; snprintf(b, sizeof b, "verify: shard %u decode status %u at input offset %llu", k, res[k].status, (unsigned long long)res[k].where); g_cuda_err = b; }
+      bad++;
+    }
+  ctx->counters[4] += bad;
+  return bad ? BGPU_E_VERIFY : 0;
+}
+
 // storeMetaBlock (full modelling) unless the caller asked for storeMetaBlockTrivial everywhere.
 int run_backend_any(bgpu_ctx* ctx, const Job& job, const EncParams& P, const uint8_t* d_in) {
   // metablock.ts:517-524: quality < 5 always stores trivial metablocks (as does encodeFast, encode.ts:169)
-  if ((ctx->tune.flags & BGPU_F_TRIVIAL_METABLOCKS) || P.quality < 5) return run_backend(ctx, job, P, d_in);
-  return run_backend_full(ctx, job, P, d_in);
+  int rc = ((ctx->tune.flags & BGPU_F_TRIVIAL_METABLOCKS) || P.quality < 5) ? run_backend(ctx, job, P, d_in) : run_backend_full(ctx, job, P, d_in);
+  if (!rc && (ctx->tune.flags & BGPU_F_VERIFY)) rc = run_verify(ctx, job, d_in);
+  return rc;
 }
 
 int reserve_front(bgpu_ctx* ctx, const Job& job, const EncParams& P) {
@@ -382,7 +408,7 @@ int run_frontend_any(bgpu_ctx* ctx, const Job& job, const EncParams& P, const ui
 
 void timing_begin(bgpu_ctx* ctx) {
   pin_rewind(ctx);
-  ctx->n_stage = 0; ctx->launches = 0; for (int i = 0; i < 4; i++) ctx->counters[i] = 0;
+  ctx->n_stage = 0; ctx->launches = 0; for (int i = 0; i < 8; i++) ctx->counters[i] = 0;
   if (ctx->ev_ok) cudaEventRecord(ctx->ev[0], ctx->stream);
 }
 void timing_end(bgpu_ctx* ctx) {
@@ -561,7 +587,7 @@ void bgpu_ctx_destroy(bgpu_ctx* c) {
                  &c->seg_trail, &c->seg_ring, &c->hist, &c->codes, &c->tree_bits, &c->tree_nbits, &c->tile_bits, &c->tile_off, &c->tile_model, &c->warp_base, &c->thr_off, &c->shard_bytes, &c->huff_meta,
                  &c->model_arena, &c->misc_arena, &c->d_models, &c->d_splits, &c->d_cb, &c->d_cx, &c->d_bh_ptrs, &c->d_bh_strides, &c->d_cx_outs,
                  &c->h10_bstart, &c->h10_bend, &c->h10_short, &c->h10_forest, &c->h10_m, &c->h10_off, &c->h10_cnt, &c->h10_cursor, &c->h10_full, &c->h10_hot,
-                 &c->zop_bytehist, &c->zop_model, &c->zop_lc, &c->zop_nodes, &c->zop_ring, &c->stats};
+                 &c->zop_bytehist, &c->zop_model, &c->zop_lc, &c->zop_nodes, &c->zop_ring, &c->stats, &c->dec_arena, &c->dec_results, &c->dec_jobs};
   for (DBuf* b : all) b->release();
   for (bgpu_ctx* l : c->lanes) bgpu_ctx_destroy(l);
   c->lanes.clear();
@@ -1276,7 +1302,34 @@ int bgpu_stage_timings(bgpu_ctx* c, const char** names, float* ms, int cap) {
   return c->n_stage;
 }
 int bgpu_last_launch_count(bgpu_ctx* c) { return c ? c->launches : 0; }
-uint64_t bgpu_last_counter(bgpu_ctx* c, int which) { return (c && which >= 0 && which < 4) ? c->counters[which] : 0; }
+uint64_t bgpu_last_counter(bgpu_ctx* c, int which) { return (c && which >= 0 && which < 8) ? c->counters[which] : 0; }
+
+int bgpu_decode(bgpu_ctx* c, const uint8_t* stream, size_t n, uint8_t* out, size_t out_cap, size_t* out_len) {
+  if (!c || !stream || !out_len || n == 0 || (out_cap && !out)) return BGPU_E_INVALID;
+  CK(cudaSetDevice(c->device));
+  int rc;
+  if ((rc = ensure_lut(c))) return rc;
+  DBuf ds, dout;
+  auto done = [&](int r) { ds.release(); dout.release(); return r; };
+  if ((rc = ds.reserve(n + 16)) || (rc = dout.reserve(out_cap + 16)) || (rc = c->dec_arena.reserve(sizeof(DecArena))) ||
+      (rc = c->dec_results.reserve(sizeof(DecResult))) || (rc = c->dec_jobs.reserve(sizeof(DecJob))))
+    return done(rc);
+  DecJob J; J.stream_off = 0; J.stream_len = n; J.out_off = 0; J.out_len = 0; J.flags = 3; J.pad = 0;
+  DecResult R; memset(&R, 0, sizeof R);
+  cudaError_t e = cudaMemcpyAsync(ds.p, stream, n, cudaMemcpyHostToDevice, c->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(c->dec_jobs.p, &J, sizeof J, cudaMemcpyHostToDevice, c->stream);
+  if (e == cudaSuccess) {
+    k_decode_shards<<<1, 32, 0, c->stream>>>(ds.as<uint8_t>(), c->dec_jobs.as<DecJob>(), 1, dout.as<uint8_t>(), nullptr, out_cap, c->dec_arena.as<DecArena>(), c->dec_results.as<DecResult>());
+    e = cudaMemcpyAsync(&R, c->dec_results.p, sizeof R, cudaMemcpyDeviceToHost, c->stream);
+  }
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+  if (e != cudaSuccess) { g_cuda_err = cudaGetErrorString(e); return done(BGPU_E_CUDA); }
+  *out_len = R.produced;
+  if (R.status == BGPU_DEC_OUTPUT) return done(BGPU_E_OUTPUT_TOO_SMALL);
+  if (R.status != BGPU_DEC_OK) { char b[128]; snprintf(b, sizeof b, "decode status %u at output offset %llu", R.status, (unsigned long long)R.where); g_cuda_err = b; return done(BGPU_E_DECODE); }
+  if (R.produced) { e = cudaMemcpy(out, dout.p, R.produced, cudaMemcpyDeviceToHost); if (e != cudaSuccess) { g_cuda_err = cudaGetErrorString(e); return done(BGPU_E_CUDA); } }
+  return done(0);
+}
 
 const char* bgpu_strerror(int code) {
   switch (code) {
@@ -1288,6 +1341,8 @@ const char* bgpu_strerror(int code) {
     case BGPU_E_CUDA: return "CUDA error";
     case BGPU_E_NOMEM: return "out of device memory";
     case BGPU_E_STATE: return "stream already finished";
+    case BGPU_E_VERIFY: return "on-device verification failed: a shard does not decode back to its input";
+    case BGPU_E_DECODE: return "corrupt or unsupported Brotli stream";
     default: return "unknown error";
   }
 }

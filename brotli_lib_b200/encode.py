@@ -115,6 +115,14 @@ class Context:
         _lib.check(self._L.bgpu_encode_device(self._h, d_ptr, n, int(quality), int(lgwin), int(mode), optr, cap, C.byref(ln), C.byref(ms)))
         return ln.value, ms.value, (out[: ln.value].tobytes() if fetch else None)
 
+    def decode(self, stream, max_out):
+        """On-device Brotli decoder (bgpu_decode: one device thread, no static dictionary) — self-verification and tests."""
+        a = _as_u8(stream)
+        out = np.empty(max_out + 16, dtype=np.uint8)
+        n = C.c_size_t(0)
+        _lib.check(self._L.bgpu_decode(self._h, _ptr(a), a.size, out.ctypes.data, max_out, C.byref(n)))
+        return out[: n.value].tobytes()
+
     def timings(self):
         names = (C.c_char_p * 64)()
         ms = (C.c_float * 64)()

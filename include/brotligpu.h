@@ -25,6 +25,8 @@ extern "C" {
 #define BGPU_E_CUDA (-5)             /* bgpu_last_cuda_error() has the text */
 #define BGPU_E_NOMEM (-6)
 #define BGPU_E_STATE (-7)            /* stream used after finish */
+#define BGPU_E_VERIFY (-8)           /* BGPU_F_VERIFY: a shard did not decode back to its input (bgpu_last_counter(ctx, 4) = how many) */
+#define BGPU_E_DECODE (-9)           /* bgpu_decode: corrupt / truncated stream, or a static-dictionary reference (not supported) */
 
 /* src/encode/enc-constants.ts:56-60  const enum EncoderMode */
 #define BGPU_MODE_GENERIC 0
@@ -49,6 +51,8 @@ typedef struct bgpu_tuning {
 #define BGPU_F_KEEP_DEVICE_OUTPUT 1u /* bench: skip the device->host gather (device-resident timing) */
 #define BGPU_F_RING_HANDOVER 4u      /* greedy parse: segments guess the last distance at their start and k_ring_handover re-codes their first copies against the decoder's ring */
 #define BGPU_F_MODEL_STATS 8u        /* bench: after the call bgpu_last_counter(1..3) hold the table bytes of the clustering / Huffman stages (one extra tiny kernel + a blocking read-back) */
+#define BGPU_F_VERIFY 16u            /* after encoding, every shard is decoded ON THE DEVICE (csrc/decode.cuh, one thread per shard) and compared with the
+                                        staged input: no device->host copy, no CPU decode; a mismatch fails the call with BGPU_E_VERIFY */
 #define BGPU_F_TRIVIAL_METABLOCKS 2u /* storeMetaBlockTrivial for every metablock (metablock.ts:290-389): no block split, no context map */
 
 /* Context: owns the CUDA device, stream, scratch arenas.  Not thread-safe; one per thread.
@@ -112,6 +116,12 @@ int bgpu_encode_part(bgpu_ctx* ctx, const uint8_t* in, size_t n, const uint8_t* 
  * the kernels is returned in *kernel_ms when non-NULL. */
 int bgpu_encode_device(bgpu_ctx* ctx, const void* d_in, size_t n, int quality, int lgwin, int mode,
                        uint8_t* out, size_t out_cap, size_t* out_len, float* kernel_ms);
+
+/* On-device Brotli decoder (format: RFC 7932, the reference's decoder is src/decode/engine.ts:1012-1518).
+ * Decodes one whole stream with ONE device thread — meant for self-verification and tests, not for throughput; streams made
+ * by this library are verified shard-parallel with BGPU_F_VERIFY instead.  No static dictionary: a stream that uses it
+ * fails with BGPU_E_DECODE.  out_cap bytes are available at out; *out_len receives the decoded size. */
+int bgpu_decode(bgpu_ctx* ctx, const uint8_t* stream, size_t n, uint8_t* out, size_t out_cap, size_t* out_len);
 
 /* new BrotliEncoder(opts) / update(chunk) / finish()     src/encode/encode.ts:290-409
  * update copies the chunk (encode.ts:360-363) and returns the bytes completed so far (possibly
