@@ -6,6 +6,7 @@
 #include "h10.cuh"
 #include "zopfli.cuh"
 #include "decode.cuh"
+#include "woff2.cuh"
 
 #include <algorithm>
 #include <atomic>
@@ -1330,6 +1331,10 @@ int bgpu_decode(bgpu_ctx* c, const uint8_t* stream, size_t n, uint8_t* out, size
   if (R.produced) { e = cudaMemcpy(out, dout.p, R.produced, cudaMemcpyDeviceToHost); if (e != cudaSuccess) { g_cuda_err = cudaGetErrorString(e); return done(BGPU_E_CUDA); } }
   return done(0);
 }
+
+}  // extern "C"
+#include "woff2_host.inc"
+extern "C" {
 
 const char* bgpu_strerror(int code) {
   switch (code) {

@@ -123,6 +123,21 @@ int bgpu_encode_device(bgpu_ctx* ctx, const void* d_in, size_t n, int quality, i
  * fails with BGPU_E_DECODE.  out_cap bytes are available at out; *out_len receives the decoded size. */
 int bgpu_decode(bgpu_ctx* ctx, const uint8_t* stream, size_t n, uint8_t* out, size_t out_cap, size_t* out_len);
 
+/* WOFF2 glyf/loca transform front end: the step upstream of BASELINE config 5.  Not in the
+ * reference (README.md:63 only points at WOFF2); format: W3C WOFF 2.0 section 5.1 "Transformed glyf table format" (36-byte
+ * header, nContour / nPoints / flag / glyph / composite / bbox / instruction sub-streams, optional overlapSimpleBitmap);
+ * the transformed loca table is empty (section 5.3).  One thread per glyph of every table of the batch; out[i] receives
+ * table i's transformed glyf (out_len[i] bytes; BGPU_E_OUTPUT_TOO_SMALL sets every out_len to the size needed). */
+typedef struct bgpu_glyf_table {
+  const uint8_t* glyf; size_t glyf_len;   /* the font's glyf table */
+  const uint8_t* loca; size_t loca_len;   /* its loca table */
+  uint32_t num_glyphs;                    /* maxp.numGlyphs */
+  int index_format;                       /* head.indexToLocFormat: 0 = u16 offsets / 2, 1 = u32 offsets */
+} bgpu_glyf_table;
+size_t bgpu_woff2_glyf_bound(size_t glyf_len, uint32_t num_glyphs);   /* enough for ordinary fonts; not a proven bound */
+int bgpu_woff2_transform_glyf(bgpu_ctx* ctx, int count, const bgpu_glyf_table* tables, uint8_t* const* out, const size_t* out_cap,
+                              size_t* out_len);
+
 /* new BrotliEncoder(opts) / update(chunk) / finish()     src/encode/encode.ts:290-409
  * update copies the chunk (encode.ts:360-363) and returns the bytes completed so far (possibly
  * none); *out stays valid until the next call on the same stream.  Every quality 0..11 (the streaming
