@@ -431,6 +431,9 @@ int oracle_build_store_tree(const uint32_t* hist, size_t n, uint8_t* depths, uin
   return 0;
 }
 
+// test_h10_repairs_are_needed: 0 = repaired (default), bit 0 / bit 1 = the TS behaviours (zopfli.h g_h10_compat)
+void oracle_set_h10_compat(int bits) { g_h10_compat = bits; }
+
 const uint8_t* oracle_context_lut(void) { return ContextLookupTable(); }
 const double* oracle_log2_table(void) { return kLog2Table(); }
 

@@ -17,13 +17,22 @@ struct BackwardMatch { uint32_t distance, length; };
 // (:100-107) reports match lengths that were never compared -> corrupt streams (observed on
 // bench/fixtures/enc-ttf.bin at q10/q11).  The restatement initialises buckets to invalidPos,
 // as reset() and the C encoder do.
+// Reproducer switches (tests/test_oracle.py::test_h10_repairs_are_needed): bit 0 = leave the buckets zero-initialised as the
+// TS constructor does (hash-binary-tree.ts:30-45: only reset() fills them with the invalid marker, and nothing calls it);
+// bit 1 = let the walk simply end when the 64-level budget runs out (:86), without closing the two dangling links.
+// Default 0 = both repairs on.  Why they are needed: the length of a tree match is only COMPARED from
+// curLen = min(bestLenLeft, bestLenRight) on (:103-109); the first curLen bytes are taken on trust from the search-tree
+// order.  A stale link (bit 1) or a node reached through position 0's links, which belong to another bucket's tree and are
+// then re-rooted into this one (bit 0), breaks that order, so lengths come out longer than the true common prefix and the
+// Zopfli pass emits copies the decoder resolves to different bytes.
+static int g_h10_compat = 0;
 class BinaryTreeHasher {
  public:
   static const int kBucketBits = 17;
   static const uint32_t kMaxTreeCompLength = 128, kMaxTreeSearchDepth = 64;
   std::vector<uint32_t> buckets, forest; uint32_t windowMask, invalidPos;
   BinaryTreeHasher(int lgwin, size_t inputSize)
-      : buckets((size_t)1 << kBucketBits, 0u - ((1u << lgwin) - 1)), windowMask((1u << lgwin) - 1), invalidPos(0u - ((1u << lgwin) - 1)) {
+      : buckets((size_t)1 << kBucketBits, (g_h10_compat & 1) ? 0u : 0u - ((1u << lgwin) - 1)), windowMask((1u << lgwin) - 1), invalidPos(0u - ((1u << lgwin) - 1)) {
     size_t numNodes = std::min<size_t>(inputSize, (size_t)1 << lgwin);
     forest.assign(2 * numNodes, invalidPos);
   }
@@ -50,7 +59,7 @@ class BinaryTreeHasher {
     // the common-prefix shortcut relies on and yields unverified match lengths (corrupt streams on
     // bench/fixtures/enc-*.bin at q10/q11).  As in the C encoder, both dangling links are closed.
     for (uint32_t depthRemaining = kMaxTreeSearchDepth;; depthRemaining--) {
-      if (depthRemaining == 0) { if (reroot) { fset(nodeLeft, invalidPos); fset(nodeRight, invalidPos); } break; }
+      if (depthRemaining == 0) { if (reroot && !(g_h10_compat & 2)) { fset(nodeLeft, invalidPos); fset(nodeRight, invalidPos); } break; }
       if (prevIx == invalidPos) { if (reroot) { fset(nodeLeft, invalidPos); fset(nodeRight, invalidPos); } break; }
       int64_t backward = (int64_t)curIx - (int64_t)prevIx;
       size_t prevMasked = prevIx & mask;

@@ -283,6 +283,11 @@ def encode_context_map(cmap, num_clusters):
     return out[: (nb.value + 7) // 8].tobytes(), nb.value
 
 
+def set_h10_compat(bits):
+    """0: H10 repairs on (default); bit 0: zero-initialised buckets, bit 1: dangling links at depth exhaustion (the TS as written)."""
+    lib().oracle_set_h10_compat(int(bits))
+
+
 def huffman(hist, tree_limit=15):
     h = np.ascontiguousarray(hist, dtype=np.uint32)
     d = np.zeros(h.size, dtype=np.uint8)

@@ -194,3 +194,53 @@ def test_store_metablock_stage_cut_reproduces_encode():
         bits, nb = O.encode_context_map(model["literal_map"], model["literal_clusters"])
         assert 0 < nb <= len(bits) * 8
     assert O.metablock_model(load_input("quickfox_repeated"), O.commands(load_input("quickfox_repeated"), 5, 22, 0), 5) is None
+
+
+def test_h10_repairs_are_needed():
+    """Reproducer for the two deliberate H10 deviations from hash-binary-tree.ts.
+
+    (1) Dangling links: the TS walk just ends when its 64-level budget runs out (hash-binary-tree.ts:86) and leaves
+    forest[nodeLeft] / forest[nodeRight] pointing at stale subtrees.  Tree match lengths are only compared from
+    min(bestLenLeft, bestLenRight) on (:103-109) — the bytes before that are taken on trust from the search-tree order —
+    so a stale link yields lengths longer than the true common prefix and the q10/q11 stream no longer decodes to the
+    input.  With the links closed (what Google's C encoder does) it does.  Failing-then-passing, on the reference's own
+    bench fixture.
+    (2) Zero-initialised buckets (:30-45: position 0 is a phantom root of every bucket): valid streams, but position 0's
+    links splice the trees of different buckets together in insertion order, which makes the per-bucket trees — the unit of
+    parallelism of the CUDA H10 (csrc/h10.cuh) — depend on each other.  Buckets therefore start at the invalid marker, as
+    reset() would leave them.  Measured here: the match lists of < 0.2 % of the positions change and the compressed total
+    does not move."""
+    data = load_input("enc-ttf.bin")
+    try:
+        O.set_h10_compat(2)
+        for q in (10, 11):
+            s = O.encode(data, q, 22, 0)
+            try:
+                ok = O.decode(s, len(data)) == data
+            except ValueError:
+                ok = False
+            assert not ok, "the unrepaired walk was expected to corrupt this stream"
+        O.set_h10_compat(0)
+        for q in (10, 11):
+            assert O.decode(O.encode(data, q, 22, 0), len(data)) == data
+        # (2): zero-initialised buckets alone
+        tot = [0, 0]
+        for name in ("alice29.txt", "enc-ttf.bin", "mapsdatazrh", "compressed_repeated"):
+            d = load_input(name)
+            lists = []
+            for bits in (0, 1):
+                O.set_h10_compat(bits)
+                s = O.encode(d, 11, 22, 0)
+                assert O.decode(s, len(d)) == d
+                tot[bits] += len(s)
+                lists.append(O.h10_all_matches(d, 22))
+            (oa, da, la), (ob, db, lb) = lists
+            same = (np.diff(oa.astype(np.int64)) == np.diff(ob.astype(np.int64)))
+            changed = int((~same).sum())
+            if len(da) == len(db):
+                neq = (da != db) | (la != lb)
+                changed = len(set(np.searchsorted(oa, np.nonzero(neq)[0], side="right") - 1) | set(np.nonzero(~same)[0]))
+            assert changed <= 0.002 * len(d), (name, changed)
+        assert abs(tot[1] - tot[0]) <= 1e-4 * tot[0], tot
+    finally:
+        O.set_h10_compat(0)
