@@ -145,7 +145,17 @@ void plan_job(const bgpu_ctx* ctx, const EncParams& P, const size_t* lens, int c
   uint32_t shard_bytes = std::min<uint32_t>(eff(ctx->tune.shard_bytes, 1u << 22), 1u << 22);
   if (P.lgwin < 22) shard_bytes = std::min<uint32_t>(shard_bytes, ((1u << P.lgwin) - 16) & ~3u);
   shard_bytes = std::max<uint32_t>(shard_bytes & ~3u, 64);
-  uint32_t seg_bytes = eff(ctx->tune.segment_bytes, P.quality >= 10 ? 1u << 15 : 1u << 13);   // q5-9: 8 KiB measured best (parse 15.5 ms per GiB vs 17.4 at 16 KiB, ratio +0.0001; gpurun r2l)
+  // q5-9: 8 KiB measured best (parse 15.5 ms per GiB vs 17.4 at 16 KiB, ratio +0.0001; gpurun r2l).  q10/11: a Zopfli segment
+  // is one warp's serial DP, so its size is the latency of a small job and irrelevant once ~8 K segments fill the machine:
+  // 32 KiB for large jobs, down to 2 KiB for small ones (enc-ttf, 312 KB, one call: 340 -> 75 ms, 138152 -> 137701 bytes; r4l)
+  uint32_t seg_dflt = 1u << 13;
+  if (P.quality >= 10) {
+    size_t total = 0;
+    for (int s = 0; s < count; s++) total += lens[s];
+    seg_dflt = 1u << 15;
+    while (seg_dflt > 2048 && total / seg_dflt < 8192) seg_dflt >>= 1;
+  }
+  uint32_t seg_bytes = eff(ctx->tune.segment_bytes, seg_dflt);
   seg_bytes = seg_bytes >= shard_bytes ? shard_bytes : std::max<uint32_t>(seg_bytes & ~(TILE - 1), TILE);
   uint32_t mb_bytes = eff(ctx->tune.metablock_bytes, shard_bytes);
   mb_bytes = mb_bytes >= shard_bytes ? shard_bytes : std::max<uint32_t>((mb_bytes / seg_bytes) * seg_bytes, seg_bytes);
