@@ -114,7 +114,7 @@ struct bgpu_ctx {
   DBuf in, sa_pos, sa_v, sb_pos, sb_v, sort_hist, role, ins, cmds, out, shards, mbs, segs, tile_seg, seg_ncmd, seg_trail, seg_ring, hist, codes, tree_bits, tree_nbits,
       tile_bits, tile_off, tile_model, warp_base, thr_off, shard_bytes, huff_meta, model_arena, misc_arena, d_models, d_splits, d_cb, d_cx, d_bh_ptrs, d_bh_strides, d_cx_outs,
       h10_bstart, h10_bend, h10_short, h10_forest, h10_m, h10_off, h10_cnt, h10_cursor, h10_full, h10_hot,
-      zop_bytehist, zop_model, zop_lc, zop_nodes, zop_ring, stats, dec_arena, dec_results, dec_jobs;
+      zop_bytehist, zop_model, zop_lc, zop_nodes, zop_ring, stats, dec_arena, dec_results, dec_jobs, seg_aux;
   uint32_t h10_cap = 0;
   uint64_t counters[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // [0] H10 match entries; [1..3] model table bytes (BGPU_F_MODEL_STATS); [4] shards that failed BGPU_F_VERIFY
   bool lut_ready = false;
@@ -147,13 +147,14 @@ void plan_job(const bgpu_ctx* ctx, const EncParams& P, const size_t* lens, int c
   shard_bytes = std::max<uint32_t>(shard_bytes & ~3u, 64);
   // q5-9: 8 KiB measured best (parse 15.5 ms per GiB vs 17.4 at 16 KiB, ratio +0.0001; gpurun r2l).  q10/11: a Zopfli segment
   // is one warp's serial DP, so its size is the latency of a small job and irrelevant once ~8 K segments fill the machine:
-  // 32 KiB for large jobs, down to 2 KiB for small ones (enc-ttf, 312 KB, one call: 340 -> 75 ms, 138152 -> 137701 bytes; r4l)
+  // 32 KiB for large jobs, down to 4 KiB for small ones (enc-ttf, 312 KB, one call: 340 ms / 138152 bytes at 32 KiB, 100 ms / 137689 at
+  // 4 KiB, 75 ms / 137701 at 2 KiB; 2 KiB costs ~0.2 % on 5-20 KB font blobs, r4l/r4m)
   uint32_t seg_dflt = 1u << 13;
   if (P.quality >= 10) {
     size_t total = 0;
     for (int s = 0; s < count; s++) total += lens[s];
     seg_dflt = 1u << 15;
-    while (seg_dflt > 2048 && total / seg_dflt < 8192) seg_dflt >>= 1;
+    while (seg_dflt > 4096 && total / seg_dflt < 8192) seg_dflt >>= 1;
   }
   uint32_t seg_bytes = eff(ctx->tune.segment_bytes, seg_dflt);
   seg_bytes = seg_bytes >= shard_bytes ? shard_bytes : std::max<uint32_t>(seg_bytes & ~(TILE - 1), TILE);
@@ -393,17 +394,35 @@ int run_frontend(bgpu_ctx* ctx, const Job& job, const EncParams& P, const uint8_
   } else {
     CK(cudaMemsetAsync(best, 0, N * 4, st));
   }
-  Params Pk = P.k; Pk.hint = (ctx->tune.flags & BGPU_F_RING_HANDOVER) ? 1 : 0;
+  Params Pk = P.k; Pk.hint = 0;
   CK(cudaMemsetAsync(ctx->role.p, 0, N, st));
-  k_parse<PARSE_G><<<(n_seg * PARSE_G + 127) / 128, 128, 0, st>>>(d_in, d_sh, d_sg, n_seg, best, ctx->role.as<uint8_t>(), ctx->ins.as<uint32_t>(),
-                                           ctx->cmds.as<Cmd>(), ctx->seg_ncmd.as<uint32_t>(), ctx->seg_trail.as<uint32_t>(), ctx->seg_ring.as<int4>(), Pk);
-  ctx->launches++; stage_mark(ctx, "k_parse");
+  // seg_aux: [0] seg_info (final), [1] seg_info of the first pass, then int4 x n_seg: first-pass end rings, assumed start rings
+  if ((rc = ctx->seg_aux.reserve((size_t)n_seg * (8 + 32) + 64))) return rc;
+  uint32_t* seg_info = ctx->seg_aux.as<uint32_t>(); uint32_t* seg_info0 = seg_info + n_seg;
+  int4* seg_ring0 = reinterpret_cast<int4*>(ctx->seg_aux.as<uint8_t>() + (((size_t)n_seg * 8 + 15) & ~(size_t)15));
+  int4* seg_assumed = seg_ring0 + n_seg;
+  CK(cudaMemsetAsync(seg_assumed, 0, (size_t)n_seg * 16, st));
+  const unsigned pgrid = (n_seg * PARSE_G + 127) / 128;
+  k_parse<PARSE_G, false><<<pgrid, 128, 0, st>>>(d_in, d_sh, d_sg, n_seg, best, ctx->role.as<uint8_t>(), ctx->ins.as<uint32_t>(),
+                                           ctx->cmds.as<Cmd>(), ctx->seg_ncmd.as<uint32_t>(), ctx->seg_trail.as<uint32_t>(), ctx->seg_ring.as<int4>(),
+                                           seg_info, nullptr, nullptr, seg_assumed, Pk);
+  ctx->launches++;
+  if (n_seg > 1 && !(ctx->tune.flags & BGPU_F_NO_REFINE)) {
+    // second pass over the segments that start inside a running copy, from the ring the first pass ended the previous segment with
+    CK(cudaMemcpyAsync(seg_info0, seg_info, (size_t)n_seg * 4, cudaMemcpyDeviceToDevice, st));
+    CK(cudaMemcpyAsync(seg_ring0, ctx->seg_ring.p, (size_t)n_seg * 16, cudaMemcpyDeviceToDevice, st));
+    k_parse<PARSE_G, true><<<pgrid, 128, 0, st>>>(d_in, d_sh, d_sg, n_seg, best, ctx->role.as<uint8_t>(), ctx->ins.as<uint32_t>(),
+                                            ctx->cmds.as<Cmd>(), ctx->seg_ncmd.as<uint32_t>(), ctx->seg_trail.as<uint32_t>(), ctx->seg_ring.as<int4>(),
+                                            seg_info, seg_ring0, seg_info0, seg_assumed, Pk);
+    ctx->launches++;
+  }
+  stage_mark(ctx, "k_parse");
   k_stitch<<<(n_mb + 63) / 64, 64, 0, st>>>(d_sh, d_mb, d_sg, n_mb, ctx->role.as<uint8_t>(), ctx->ins.as<uint32_t>(), ctx->cmds.as<Cmd>(),
                                             ctx->seg_ncmd.as<uint32_t>(), ctx->seg_trail.as<uint32_t>(), Pk);
   ctx->launches++;
-  if (Pk.hint) {
-    k_ring_handover<<<(n_seg + 127) / 128, 128, 0, st>>>(d_sh, d_sg, n_seg, ctx->ins.as<uint32_t>(), ctx->cmds.as<Cmd>(), ctx->seg_ncmd.as<uint32_t>(),
-                                                       ctx->seg_ring.as<int4>(), Pk);
+  if (n_seg > 1) {
+    k_ring_fixup<<<(n_seg + 127) / 128, 128, 0, st>>>(d_sh, d_sg, n_seg, ctx->ins.as<uint32_t>(), ctx->cmds.as<Cmd>(), ctx->seg_ncmd.as<uint32_t>(),
+                                                    ctx->seg_ring.as<int4>(), seg_info, seg_assumed, Pk);
     ctx->launches++;
   }
   stage_mark(ctx, "k_stitch");
@@ -598,7 +617,7 @@ void bgpu_ctx_destroy(bgpu_ctx* c) {
                  &c->seg_trail, &c->seg_ring, &c->hist, &c->codes, &c->tree_bits, &c->tree_nbits, &c->tile_bits, &c->tile_off, &c->tile_model, &c->warp_base, &c->thr_off, &c->shard_bytes, &c->huff_meta,
                  &c->model_arena, &c->misc_arena, &c->d_models, &c->d_splits, &c->d_cb, &c->d_cx, &c->d_bh_ptrs, &c->d_bh_strides, &c->d_cx_outs,
                  &c->h10_bstart, &c->h10_bend, &c->h10_short, &c->h10_forest, &c->h10_m, &c->h10_off, &c->h10_cnt, &c->h10_cursor, &c->h10_full, &c->h10_hot,
-                 &c->zop_bytehist, &c->zop_model, &c->zop_lc, &c->zop_nodes, &c->zop_ring, &c->stats, &c->dec_arena, &c->dec_results, &c->dec_jobs};
+                 &c->zop_bytehist, &c->zop_model, &c->zop_lc, &c->zop_nodes, &c->zop_ring, &c->stats, &c->dec_arena, &c->dec_results, &c->dec_jobs, &c->seg_aux};
   for (DBuf* b : all) b->release();
   for (bgpu_ctx* l : c->lanes) bgpu_ctx_destroy(l);
   c->lanes.clear();

@@ -47,7 +47,7 @@ struct Params {
   int bucket_bits, depth, num_last;
   uint32_t npostfix, ndirect, dist_alphabet;
   int sh;  // command slot shift
-  int hint;  // BGPU_F_RING_HANDOVER: parse segments guess the last distance at their start (k_parse) and k_ring_handover re-codes
+  int hint;  // unused (the former BGPU_F_RING_HANDOVER guess; superseded by the REFINE pass of k_parse)
 };
 
 // ---------------------------------------------------------------------------------------
@@ -95,12 +95,24 @@ __device__ __forceinline__ uint32_t distance_to_code(uint32_t distance, const in
 // a segment is latency bound (a dependent chain of L2 reads per accepted match), so throughput
 // comes from the number of segments in flight: G = 8 keeps one 32-byte sector of `best` and of the
 // input per group read while quadrupling the segments per warp.
-template <int G>
+// Per-segment bookkeeping of the parse: seg_info bits 0..2 = min(ring updates made inside the segment, 7) — with >= 4 the
+// segment's end view of the ring IS the decoder's ring there, whatever it started from; bit 8 = the segment's last copy
+// was cut by the segment end and its source keeps matching for >= PARSE_TAIL_MIN bytes beyond it, i.e. the next segment
+// starts inside a running copy (rare on text, where copies are short; the rule on copy-heavy data).  REFINE pass (second launch): only segments behind such a tail, whose predecessor's end view is
+// complete, are parsed again, now starting from that ring — the last-distance probe then continues the running copy the
+// way the reference's serial parse does (backward-references.ts:36-134), instead of re-finding it through the hash chain
+// (DESIGN.md section 4 "Distance ring across parse segments": that re-finding cost ~20 bytes per 8 KiB boundary on copy-heavy
+// data).  seg_assumed[seg] records the ring a segment was parsed from; k_ring_fixup reconciles it with the ring the decoder
+// really has there.
+constexpr uint32_t PARSE_TAIL_MIN = 8;
+template <int G, bool REFINE>
 __global__ void __launch_bounds__(128) k_parse(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
                                                const SegD* __restrict__ segs, uint32_t n_seg,
                                                const uint32_t* __restrict__ best, uint8_t* __restrict__ role,
                                                uint32_t* __restrict__ ins_at, Cmd* __restrict__ cmds,
-                                               uint32_t* __restrict__ seg_ncmd, uint32_t* __restrict__ seg_trail, int4* __restrict__ seg_ring, Params P) {
+                                               uint32_t* __restrict__ seg_ncmd, uint32_t* __restrict__ seg_trail, int4* __restrict__ seg_ring,
+                                               uint32_t* __restrict__ seg_info, const int4* __restrict__ seg_ring0, const uint32_t* __restrict__ seg_info0,
+                                               int4* __restrict__ seg_assumed, Params P) {
   const uint32_t seg = (blockIdx.x * 128 + threadIdx.x) / G;
   if (seg >= n_seg) return;
   const uint32_t wl = threadIdx.x & 31;
@@ -116,13 +128,20 @@ __global__ void __launch_bounds__(128) k_parse(const uint8_t* __restrict__ in, c
   int ring[4];
   if (sg.ring_known) { ring[0] = 4; ring[1] = 11; ring[2] = 15; ring[3] = 16; }
   else { ring[0] = ring[1] = ring[2] = ring[3] = 0; }
-  uint32_t pos = sg.rel_pos, ins_start = sg.rel_pos, ncmd = 0;
-  // A segment that does not open the stream cannot know the decoder's ring, but the copy that is probably running
-  // across its start has the distance of the table candidate one byte earlier: until the first command, that
-  // distance is probed like distanceCache[0] (bonus score, so a long copy continues instead of switching to a nearer
-  // source) and emitted with an explicit code; k_ring_handover turns it into code 0 when the guess was right.
-  int hint = 0;
-  if (P.hint && !sg.ring_known && sg.rel_pos > 0) { const uint32_t hb = sbest[sg.rel_pos - 1]; if ((hb >> 24) >= 4) hint = (int)(hb & 0xFFFFFFu); }
+  if (REFINE) {
+    // (uniform over the G lanes of the segment: every value below is per segment)
+    if (seg == 0 || sg.ring_known || segs[seg - 1].shard != sg.shard || segs[seg - 1].rel_pos + segs[seg - 1].len != sg.rel_pos) return;
+    const uint32_t pi = seg_info0[seg - 1];
+    if (!(pi & 0x100u) || (pi & 7u) < 4u) return;
+    const int4 a = seg_ring0[seg - 1];
+    ring[0] = a.x; ring[1] = a.y; ring[2] = a.z; ring[3] = a.w;
+    if (lane == 0) seg_assumed[seg] = a;
+    // the first pass marked this segment's positions: start from a clean slate (roles index everything else)
+    for (uint32_t q = sg.rel_pos + lane * 4; q + 4 <= seg_end; q += G * 4) *reinterpret_cast<uint32_t*>(srole + q) = 0u;   // rel_pos is a multiple of 4
+    if (lane == 0) for (uint32_t q = sg.rel_pos + ((seg_end - sg.rel_pos) & ~3u); q < seg_end; q++) srole[q] = 0;            // ragged shard end
+    __syncwarp(gmask);
+  }
+  uint32_t pos = sg.rel_pos, ins_start = sg.rel_pos, ncmd = 0, npush = 0, last_dist = 0;
   while (pos < seg_end) {
     const uint32_t q = pos + lane;
     uint32_t blen = 0, bdist = 0; int bscore = 0;
@@ -143,11 +162,6 @@ __global__ void __launch_bounds__(128) k_parse(const uint8_t* __restrict__ in, c
         uint32_t len = 4 + match_len(sin, q + 4, q - d + 4, maxLen - 4);
         int score = 135 * (int)len + 975;
         if (score > bscore) { bscore = score; blen = len; bdist = (uint32_t)d; }
-      }
-      if (hint > 0 && ring[0] == 0 && (uint32_t)hint <= maxBackward && ld32u(sin, q - hint) == v) {
-        const uint32_t len = 4 + match_len(sin, q + 4, q - hint + 4, maxLen - 4);
-        const int score = 135 * (int)len + 975;
-        if (score > bscore) { bscore = score; blen = len; bdist = (uint32_t)hint; }
       }
       // chain best from K3 (truncated at the segment end)
       uint32_t clen = min(b >> 24, maxLen), cdist = b & 0xFFFFFFu;
@@ -170,10 +184,16 @@ __global__ void __launch_bounds__(128) k_parse(const uint8_t* __restrict__ in, c
       ins_at[(sh.in_off + ins_start) >> P.sh] = qf - ins_start;
       *reinterpret_cast<uint4*>(&cmds[(sh.in_off + qf) >> P.sh]) = *reinterpret_cast<uint4*>(&c);
     }
-    if (code > 0) { ring[3] = ring[2]; ring[2] = ring[1]; ring[1] = ring[0]; ring[0] = (int)mdist; }
-    pos = qf + mlen; ins_start = pos; ncmd++;
+    if (code > 0) { ring[3] = ring[2]; ring[2] = ring[1]; ring[1] = ring[0]; ring[0] = (int)mdist; npush++; }
+    pos = qf + mlen; ins_start = pos; ncmd++; last_dist = mdist;
   }
-  if (lane == 0) { seg_ncmd[seg] = ncmd; seg_trail[seg] = ins_start; seg_ring[seg] = make_int4(ring[0], ring[1], ring[2], ring[3]); }
+  if (lane == 0) {
+    seg_ncmd[seg] = ncmd; seg_trail[seg] = ins_start; seg_ring[seg] = make_int4(ring[0], ring[1], ring[2], ring[3]);
+    uint32_t tail = 0;
+    if (ncmd && ins_start == seg_end && seg_end + PARSE_TAIL_MIN <= sh.len)
+      tail = match_len(sin, seg_end, seg_end - last_dist, PARSE_TAIL_MIN) >= PARSE_TAIL_MIN ? 0x100u : 0u;
+    seg_info[seg] = min(npush, 7u) | tail;
+  }
 }
 
 // Joins the segments of a metablock: literals left over at the end of a segment become part of the
@@ -213,42 +233,47 @@ __global__ void k_stitch(const ShardD* __restrict__ shards, const MbD* __restric
 }
 
 
-// Distance-ring hand-over (BGPU_F_RING_HANDOVER, greedy parse only; runs after k_stitch).  A segment that does not open
-// the stream was parsed with an unknown ring, so its first copies carry explicit distance codes even where the
-// decoder's ring holds the distance.  When the previous segment of the shard made >= 4 ring updates, its end view of
-// the ring (seg_ring, written by k_parse) IS the decoder's ring R at this segment's start, whatever came before.  The
-// segment's first commands, up to the point where its own view V is complete (4 updates, after which V == R), are
-// re-coded against R.  Only the first command of a segment can lose its update (explicit -> code 0), which leaves every
-// later short code pointing at the same value, so the commands that are not visited stay valid as they are, and so
-// does the end view the next segment relies on.  One thread per segment.
-__global__ void k_ring_handover(const ShardD* __restrict__ shards, const SegD* __restrict__ segs, uint32_t n_seg,
-                                const uint32_t* __restrict__ ins_at, Cmd* __restrict__ cmds,
-                                const uint32_t* __restrict__ seg_ncmd, const int4* __restrict__ seg_ring, Params P) {
+// Ring reconciliation (runs after k_stitch).  Segment s was parsed from the ring A0 = seg_assumed[s] (zeros = "unknown":
+// nothing referenced until learned; or the first pass's end view of segment s - 1 when s was re-parsed by the REFINE pass).
+// The ring the decoder really has at the start of s is R0 = the FINAL end view of segment s - 1 when that segment made
+// >= 4 ring updates of its own (then its end view does not depend on where it started); otherwise R0 is taken as unknown.
+// Walking the segment's commands, each distance is decoded under the A view and re-coded under the R view; both views
+// are advanced by their own push rule (a command whose code is 0 = "last distance" pushes nothing), and the walk stops
+// as soon as they agree — from there on the remaining commands mean the same thing to both.  With A0 = zeros and R0 known
+// this turns explicit distances into short codes (the former BGPU_F_RING_HANDOVER); with A0 != R0 after a re-parse it keeps
+// the stream valid.  One thread per segment.
+__global__ void k_ring_fixup(const ShardD* __restrict__ shards, const SegD* __restrict__ segs, uint32_t n_seg,
+                             const uint32_t* __restrict__ ins_at, Cmd* __restrict__ cmds,
+                             const uint32_t* __restrict__ seg_ncmd, const int4* __restrict__ seg_ring, const uint32_t* __restrict__ seg_info,
+                             const int4* __restrict__ seg_assumed, Params P) {
   const uint32_t s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= n_seg || s == 0) return;
   const SegD sg = segs[s];
   const uint32_t nc = seg_ncmd[s];
-  if (sg.ring_known || nc == 0 || segs[s - 1].shard != sg.shard) return;
-  const int4 e = seg_ring[s - 1];
-  if (e.w == 0) return;
+  if (sg.ring_known || nc == 0) return;
+  const int4 a0 = seg_assumed[s];
+  int A[4] = {a0.x, a0.y, a0.z, a0.w};
+  int R[4] = {0, 0, 0, 0};
+  const bool prev_ok = segs[s - 1].shard == sg.shard && segs[s - 1].rel_pos + segs[s - 1].len == sg.rel_pos && (seg_info[s - 1] & 7u) >= 4u;
+  if (prev_ok) { const int4 e = seg_ring[s - 1]; R[0] = e.x; R[1] = e.y; R[2] = e.z; R[3] = e.w; }
+  if (A[0] == R[0] && A[1] == R[1] && A[2] == R[2] && A[3] == R[3]) return;
   const ShardD sh = shards[sg.shard];
-  int R[4] = {e.x, e.y, e.z, e.w};
   const int8_t off[16] = {0, 0, 0, 0, -1, 1, -2, 2, -3, 3, -1, 1, -2, 2, -3, 3};
-  int V[4] = {0, 0, 0, 0};
   uint32_t p = sg.rel_pos;
-  for (uint32_t k = 0; k < nc && V[3] == 0; k++) {
+  for (uint32_t k = 0; k < nc; k++) {
     const uint32_t il = ins_at[(sh.in_off + p) >> P.sh];
     Cmd* c = &cmds[(sh.in_off + p + il) >> P.sh];
     const uint32_t dp = c->distPrefix, oc = dp & 0x3FF;
-    const uint32_t dist = oc < 16 ? (uint32_t)((oc < 4 ? V[oc] : (oc < 10 ? V[0] : V[1])) + off[oc]) : distance_of_explicit(dp, c->distExtra, P.ndirect, P.npostfix);
-    const uint32_t nc_code = distance_to_code(dist, R);
-    if (nc_code != (oc < 16 ? oc : dist + 15)) {
-      uint32_t extra; const uint32_t ndp = dist_prefix(nc_code, P.ndirect, P.npostfix, &extra);
+    const uint32_t dist = oc < 16 ? (uint32_t)((oc < 4 ? A[oc] : (oc < 10 ? A[0] : A[1])) + off[oc]) : distance_of_explicit(dp, c->distExtra, P.ndirect, P.npostfix);
+    const uint32_t ncode = distance_to_code(dist, R);
+    if (ncode != (oc < 16 ? oc : dist + 15)) {
+      uint32_t extra; const uint32_t ndp = dist_prefix(ncode, P.ndirect, P.npostfix, &extra);
       c->distPrefix = (uint16_t)ndp; c->distExtra = extra;
       c->cmdPrefix = (uint16_t)combine_codes(ins_code(c->insertLen), copy_code(c->copyLen & 0x1FFFFFF), (ndp & 0x3FF) == 0);
     }
-    if (nc_code > 0) { R[3] = R[2]; R[2] = R[1]; R[1] = R[0]; R[0] = (int)dist; }
-    if (oc > 0) { V[3] = V[2]; V[2] = V[1]; V[1] = V[0]; V[0] = (int)dist; }
+    if (ncode > 0) { R[3] = R[2]; R[2] = R[1]; R[1] = R[0]; R[0] = (int)dist; }
+    if (oc > 0) { A[3] = A[2]; A[2] = A[1]; A[1] = A[0]; A[0] = (int)dist; }
+    if (A[0] == R[0] && A[1] == R[1] && A[2] == R[2] && A[3] == R[3]) break;
     p += il + (c->copyLen & 0x1FFFFFF);
   }
 }

@@ -49,7 +49,8 @@ typedef struct bgpu_tuning {
   uint32_t group_shards;    /* shards per group (default: shards / lanes, clamped to 16..64)       */
 } bgpu_tuning;
 #define BGPU_F_KEEP_DEVICE_OUTPUT 1u /* bench: skip the device->host gather (device-resident timing) */
-#define BGPU_F_RING_HANDOVER 4u      /* greedy parse: segments guess the last distance at their start and k_ring_handover re-codes their first copies against the decoder's ring */
+#define BGPU_F_RING_HANDOVER 4u      /* accepted and ignored (round-1 experiment; the second parse pass + ring reconciliation replaced it) */
+#define BGPU_F_NO_REFINE 32u         /* greedy parse: skip the second pass over segments that start inside a running copy (A/B runs) */
 #define BGPU_F_MODEL_STATS 8u        /* bench: after the call bgpu_last_counter(1..3) hold the table bytes of the clustering / Huffman stages (one extra tiny kernel + a blocking read-back) */
 #define BGPU_F_VERIFY 16u            /* after encoding, every shard is decoded ON THE DEVICE (csrc/decode.cuh, one thread per shard) and compared with the
                                         staged input: no device->host copy, no CPU decode; a mismatch fails the call with BGPU_E_VERIFY */

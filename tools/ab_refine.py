@@ -1,0 +1,15 @@
+"""A/B of the second parse pass (BGPU_F_NO_REFINE = 32): per-shard size vs the oracle on the 8 config-2 shard types."""
+import sys, time; sys.path.insert(0, '.'); sys.path.insert(0, 'tests')
+import numpy as np, brotli_lib_b200 as B, _oracle as O
+from brotli_lib_b200 import workloads as W
+ctx = B.Context()
+sample = np.concatenate([W.mixed_segment(i, 0) for i in range(8)])
+items = [sample[o:o + (1 << 22)] for o in range(0, sample.size, 1 << 22)]
+for q in (5, 9, 3):
+    ref = [int(x) for x in O.encode_shards_sizes(sample, 1 << 22, q, 22, 0, 16)]
+    for flags in (32, 0, 4):
+        ctx.set_tuning(flags=flags)
+        t = time.perf_counter(); outs = ctx.encode_batch(items, q, 22, 0); dt = time.perf_counter() - t
+        g = [len(s) for s in outs]
+        ok = all(O.decode(s, 1 << 22) == it.tobytes() for s, it in zip(outs[4:7], items[4:7]))
+        print(f"q{q} flags={flags}: total {100*(sum(g)-sum(ref))/sum(ref):+.3f}% per-shard " + " ".join(f"{100*(a-b)/b:+.2f}" for a, b in zip(g, ref)) + f"  parse {dict(ctx.timings()).get('k_parse'):.2f} ms ok={ok}")
