@@ -11,7 +11,7 @@ E_UNSUPPORTED = -3
 
 SYMBOLS = [
     "bgpu_ctx_create", "bgpu_ctx_create_multi", "bgpu_ctx_destroy", "bgpu_ctx_set_tuning", "bgpu_ctx_set_stream", "bgpu_max_compressed_size", "bgpu_encode",
-    "bgpu_encode_batch", "bgpu_encode_part", "bgpu_encode_device", "bgpu_decode", "bgpu_woff2_glyf_bound", "bgpu_woff2_transform_glyf", "bgpu_stream_create", "bgpu_stream_update", "bgpu_stream_finish",
+    "bgpu_encode_batch", "bgpu_encode_part", "bgpu_encode_device", "bgpu_decode", "bgpu_decode_noalloc", "bgpu_noalloc_scratch_bytes", "bgpu_woff2_glyf_bound", "bgpu_woff2_transform_glyf", "bgpu_stream_create", "bgpu_stream_update", "bgpu_stream_finish",
     "bgpu_stream_destroy", "bgpu_stage_match_candidates", "bgpu_stage_commands", "bgpu_stage_store_trivial",
     "bgpu_stage_huffman", "bgpu_stage_h10_matches", "bgpu_stage_histograms", "bgpu_stage_context_map", "bgpu_stage_store_metablock", "bgpu_stage_timings", "bgpu_last_launch_count", "bgpu_last_counter", "bgpu_strerror", "bgpu_last_cuda_error",
     "bgpu_version",
@@ -62,6 +62,9 @@ def load():
     L.bgpu_encode_part.argtypes = [vp, vp, sz, vp, C.c_uint, i, i, i, vp, sz, szp]
     L.bgpu_encode_device.argtypes = [vp, vp, sz, i, i, i, vp, sz, szp, C.POINTER(C.c_float)]
     L.bgpu_decode.argtypes = [vp, vp, sz, vp, sz, szp]
+    L.bgpu_decode_noalloc.argtypes = [i, vp, szp, vp, szp, szp, C.POINTER(C.c_int), vp]
+    L.bgpu_noalloc_scratch_bytes.argtypes = []
+    L.bgpu_noalloc_scratch_bytes.restype = sz
     L.bgpu_woff2_glyf_bound.argtypes = [sz, C.c_uint32]
     L.bgpu_woff2_glyf_bound.restype = sz
     L.bgpu_woff2_transform_glyf.argtypes = [vp, i, C.POINTER(GlyfTable), C.POINTER(vp), szp, szp]

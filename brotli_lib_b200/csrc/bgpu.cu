@@ -1385,3 +1385,109 @@ const char* bgpu_last_cuda_error(void) { return g_cuda_err.c_str(); }
 int bgpu_version(void) { return 0x000100; }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------
+// bgpu_decode_noalloc: the on-device decoder for callers that may not allocate (include/brotligpu.h).  No
+// counterpart in the reference.  The decoder's scratch memory (its
+// per-stream table arena, the job descriptors and the results) lives in ONE file-scope device array instead of the
+// context's cudaMalloc'ed buffers.  Every GPU that loads the library holds the array until the process exits.
+//
+// g_noalloc_scratch as written in HOST code is only a host-side stand-in for the symbol: its device address is taken
+// with cudaGetSymbolAddress, once per device with that device current (noalloc_setup), and that address is what the
+// kernel receives.  All calls on a device share the array and it keeps the previous call's contents: the job / result
+// header is cleared at the start of every call (the arenas need no clearing: dec_read_code / dec_context_map write
+// every table entry before dec_piece reads it), and two calls that overlap on the GPU race on it.
+namespace {
+
+constexpr size_t kNoallocArenaStride = (sizeof(DecArena) + 255) & ~(size_t)255;
+constexpr size_t kNoallocHeader = 1024;   // NoallocJob[8] at 0, DecResult[8] at 512
+constexpr size_t kNoallocScratchBytes = kNoallocHeader + (size_t)BGPU_NOALLOC_MAX_STREAMS * kNoallocArenaStride;
+static_assert(kNoallocScratchBytes <= (size_t)BGPU_NOALLOC_SCRATCH_BYTES, "BGPU_NOALLOC_SCRATCH_BYTES in brotligpu.h is the stated limit");
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[BGPU_NOALLOC_SCRATCH_BYTES];
+
+struct NoallocJob { const uint8_t* stream; uint64_t stream_len; uint8_t* out; uint64_t out_cap; };
+static_assert(sizeof(NoallocJob) * BGPU_NOALLOC_MAX_STREAMS <= 512 && sizeof(DecResult) * BGPU_NOALLOC_MAX_STREAMS <= 512, "header layout");
+
+// grid = streams; lane 0 of each CTA decodes one whole stream (window header .. ISLAST) into its own output.
+__global__ void __launch_bounds__(32) k_decode_noalloc(unsigned char* scratch, uint32_t n_streams) {
+  const uint32_t j = blockIdx.x;
+  if (j >= n_streams || threadIdx.x != 0) return;
+  const NoallocJob N = reinterpret_cast<const NoallocJob*>(scratch)[j];
+  DecResult* results = reinterpret_cast<DecResult*>(scratch + 512);
+  DecArena* arena = reinterpret_cast<DecArena*>(scratch + kNoallocHeader + (size_t)j * kNoallocArenaStride);
+  DecJob J; J.stream_off = 0; J.stream_len = N.stream_len; J.out_off = 0; J.out_len = 0; J.flags = 3; J.pad = 0;
+  dec_piece(N.stream, J, N.out, nullptr, N.out_cap, *arena, results[j]);
+}
+
+constexpr int kNoallocMaxDevices = 64;
+std::mutex g_noalloc_mu;
+unsigned char* g_noalloc_ptr[kNoallocMaxDevices];   // device address of g_noalloc_scratch, per device (nullptr: not set up)
+
+// Once per device, with that device current: the array's device address and the context-lookup constants.
+int noalloc_setup(int device, unsigned char** ptr) {
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_ptr[device]) {
+    unsigned char* p = nullptr;
+    CK(cudaGetSymbolAddress((void**)&p, g_noalloc_scratch));
+    uint8_t lut[2048]; build_context_lut(lut);
+    CK(cudaMemcpyToSymbol(c_ctx_lut, lut, sizeof lut));
+    g_noalloc_ptr[device] = p;
+  }
+  *ptr = g_noalloc_ptr[device];
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+size_t bgpu_noalloc_scratch_bytes(void) { return sizeof g_noalloc_scratch; }
+
+int bgpu_decode_noalloc(int n_streams, const void* const* d_stream, const size_t* stream_len, void* const* d_out, const size_t* out_cap,
+                        size_t* out_len, int* status, void* cuda_stream) {
+  if (n_streams < 0 || (n_streams && (!d_stream || !stream_len || !d_out || !out_cap || !out_len))) {
+    g_cuda_err = "bgpu_decode_noalloc: null argument"; return BGPU_E_INVALID;
+  }
+  if (n_streams > BGPU_NOALLOC_MAX_STREAMS) {
+    char b[160]; snprintf(b, sizeof b, "bgpu_decode_noalloc: %d streams in one call exceed BGPU_NOALLOC_MAX_STREAMS = %d (fixed scratch of %zu bytes)",
+                          n_streams, BGPU_NOALLOC_MAX_STREAMS, sizeof g_noalloc_scratch);
+    g_cuda_err = b; return BGPU_E_INVALID;
+  }
+  if (n_streams == 0) return 0;
+  NoallocJob jobs[BGPU_NOALLOC_MAX_STREAMS]; DecResult res[BGPU_NOALLOC_MAX_STREAMS];
+  for (int k = 0; k < n_streams; k++) {
+    if (!d_stream[k] || stream_len[k] == 0 || (out_cap[k] && !d_out[k])) { g_cuda_err = "bgpu_decode_noalloc: empty stream or null buffer"; return BGPU_E_INVALID; }
+    jobs[k].stream = (const uint8_t*)d_stream[k]; jobs[k].stream_len = stream_len[k]; jobs[k].out = (uint8_t*)d_out[k]; jobs[k].out_cap = out_cap[k];
+    out_len[k] = 0; if (status) status[k] = 0;
+  }
+  int device = 0;
+  CK(cudaGetDevice(&device));
+  if (device < 0 || device >= kNoallocMaxDevices) { g_cuda_err = "bgpu_decode_noalloc: device ordinal out of range"; return BGPU_E_INVALID; }
+  unsigned char* scratch = nullptr;
+  int rc = noalloc_setup(device, &scratch);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)cuda_stream;
+  CK(cudaMemsetAsync(scratch, 0, kNoallocHeader, st));
+  CK(cudaMemcpyAsync(scratch, jobs, sizeof(NoallocJob) * n_streams, cudaMemcpyHostToDevice, st));
+  k_decode_noalloc<<<n_streams, 32, 0, st>>>(scratch, (uint32_t)n_streams);
+  CK(cudaGetLastError());
+  CK(cudaMemcpyAsync(res, scratch + 512, sizeof(DecResult) * n_streams, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  int result = 0;
+  for (int k = 0; k < n_streams; k++) {
+    out_len[k] = res[k].produced;
+    int r = 0;
+    if (res[k].status == BGPU_DEC_OUTPUT) r = BGPU_E_OUTPUT_TOO_SMALL;
+    else if (res[k].status != BGPU_DEC_OK) r = BGPU_E_DECODE;
+    if (status) status[k] = r;
+    if (r && !result) {
+      result = r;
+      char b[160]; snprintf(b, sizeof b, "bgpu_decode_noalloc: stream %d: decode status %u at output offset %llu", k, res[k].status, (unsigned long long)res[k].where);
+      g_cuda_err = b;
+    }
+  }
+  return result;
+}
+
+}  // extern "C"

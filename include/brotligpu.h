@@ -124,6 +124,28 @@ int bgpu_encode_device(bgpu_ctx* ctx, const void* d_in, size_t n, int quality, i
  * fails with BGPU_E_DECODE.  out_cap bytes are available at out; *out_len receives the decoded size. */
 int bgpu_decode(bgpu_ctx* ctx, const uint8_t* stream, size_t n, uint8_t* out, size_t out_cap, size_t* out_len);
 
+/* Decoder entry point that allocates nothing.  It has NO counterpart in the reference and was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  Same decoder as bgpu_decode (same device code, one device thread per stream), but its scratch memory — job
+ * descriptors, results and one table arena per stream — is a file-scope `static __device__` array of
+ * BGPU_NOALLOC_SCRATCH_BYTES (10 MiB) that every GPU which loads the library holds until the process exits.  The call makes
+ * no cudaMalloc / cudaFree / cudaMallocHost and uses no context: the caller passes inputs and outputs.
+ *   d_stream[k], stream_len[k]  DEVICE pointer to whole Brotli stream k and its size in bytes (k < n_streams);
+ *   d_out[k], out_cap[k]        DEVICE pointer that receives its bytes, and the room there;
+ *   out_len[k]                  (host) decoded size of stream k;   status[k] (host, may be NULL) 0 or a BGPU_E_* code per stream;
+ *   cuda_stream                 a cudaStream_t of the CURRENT device (NULL: the default stream); the call returns after the
+ *                               work on it has finished.
+ * The device used is the calling thread's current device (cudaGetDevice).  The arrays d_stream .. status are host arrays.
+ * Limit: n_streams <= BGPU_NOALLOC_MAX_STREAMS; more is refused with BGPU_E_INVALID (bgpu_last_cuda_error() names the limit)
+ * — split the batch over several calls.  Returns 0, or the first failing stream's code (BGPU_E_DECODE, BGPU_E_OUTPUT_TOO_SMALL).
+ * All calls on one device share the array, which keeps the previous call's contents (the call clears what it needs zeroed):
+ * calls that overlap on the same GPU — two host threads, or two streams — race on it and must be serialised by the caller. */
+#define BGPU_NOALLOC_MAX_STREAMS 8
+#define BGPU_NOALLOC_SCRATCH_BYTES (10u << 20)
+int bgpu_decode_noalloc(int n_streams, const void* const* d_stream, const size_t* stream_len, void* const* d_out,
+                        const size_t* out_cap, size_t* out_len, int* status, void* cuda_stream);
+size_t bgpu_noalloc_scratch_bytes(void);   /* = BGPU_NOALLOC_SCRATCH_BYTES: the per-GPU footprint of the array */
+
 /* WOFF2 glyf/loca transform front end: the step upstream of BASELINE config 5.  Not in the
  * reference (README.md:63 only points at WOFF2); format: W3C WOFF 2.0 section 5.1 "Transformed glyf table format" (36-byte
  * header, nContour / nPoints / flag / glyph / composite / bbox / instruction sub-streams, optional overlapSimpleBitmap);
