@@ -110,6 +110,7 @@ struct bgpu_ctx {
   std::vector<bgpu_ctx*> lanes; bool is_lane = false;
   cudaEvent_t lane_ev = nullptr, fork_ev = nullptr, h2d_ev = nullptr;
   cudaStream_t copy_stream = nullptr;   // parent only: the groups' host->device copies, in group order
+  cudaStream_t hi_stream = nullptr; cudaEvent_t hi_ev = nullptr;   // lanes: high-priority side stream of the modelling phase (model_host.inc side_begin)
   uint32_t* h_sizes = nullptr; size_t h_sizes_cap = 0;   // pinned: shard sizes of the lane's current group
   uint8_t* pin = nullptr; size_t pin_cap = 0, pin_used = 0, pin_want = 0;   // pinned staging of descriptor uploads
   DBuf in, sa_pos, sa_v, sb_pos, sb_v, sort_hist, role, ins, cmds, out, shards, mbs, segs, tile_seg, seg_ncmd, seg_trail, seg_ring, hist, codes, tree_bits, tree_nbits,
@@ -365,15 +366,15 @@ int run_frontend(bgpu_ctx* ctx, const Job& job, const EncParams& P, const uint8_
     const int bb = P.k.bucket_bits;
     k_sort_hist<2><<<gs, 256, 0, st>>>(d_in, nullptr, d_sh, sh_hist, bb, 0, 6);
     k_sort_scan<<<n_shard, 1024, 0, st>>>(d_sh, sh_hist, 1 << 6);
-    k_sort_scatter<2><<<gs, 256, 0, st>>>(d_in, nullptr, nullptr, d_sh, sh_hist, sa_pos, sa_v, bb, 0, 6);
+    k_sort_scatter<2><<<gs, 256, SORT_SCATTER_SMEM, st>>>(d_in, nullptr, nullptr, d_sh, sh_hist, sa_pos, sa_v, bb, 0, 6);
     ctx->launches += 3; stage_mark(ctx, "k_sort_pass0");
     k_sort_hist<3><<<gs, 256, 0, st>>>(d_in, sa_v, d_sh, sh_hist, bb, 6, 6);
     k_sort_scan<<<n_shard, 1024, 0, st>>>(d_sh, sh_hist, 1 << 6);
-    k_sort_scatter<3><<<gs, 256, 0, st>>>(d_in, sa_pos, sa_v, d_sh, sh_hist, sb_pos, sb_v, bb, 6, 6);
+    k_sort_scatter<3><<<gs, 256, SORT_SCATTER_SMEM, st>>>(d_in, sa_pos, sa_v, d_sh, sh_hist, sb_pos, sb_v, bb, 6, 6);
     ctx->launches += 3; stage_mark(ctx, "k_sort_pass1");
     k_sort_hist<3><<<gs, 256, 0, st>>>(d_in, sb_v, d_sh, sh_hist, bb, 12, bb - 12);
     k_sort_scan<<<n_shard, 1024, 0, st>>>(d_sh, sh_hist, 1 << (bb - 12));
-    k_sort_scatter<3><<<gs, 256, 0, st>>>(d_in, sb_pos, sb_v, d_sh, sh_hist, sa_pos, sa_v, bb, 12, bb - 12);
+    k_sort_scatter<3><<<gs, 256, SORT_SCATTER_SMEM, st>>>(d_in, sb_pos, sb_v, d_sh, sh_hist, sa_pos, sa_v, bb, 12, bb - 12);
     ctx->launches += 3; stage_mark(ctx, "k_sort_pass2");
     k_probe_simple<<<gp, 256, 0, st>>>(d_in, d_sh, sa_pos, sa_v, best);
     ctx->launches++; stage_mark(ctx, "k_probe");
@@ -383,14 +384,20 @@ int run_frontend(bgpu_ctx* ctx, const Job& job, const EncParams& P, const uint8_
     const int bb = P.k.bucket_bits, nb0 = 1 << SORT_LOW_BITS, nb1 = 1 << (bb - SORT_LOW_BITS);
     k_sort_hist<0><<<gs, 256, 0, st>>>(d_in, nullptr, d_sh, sh_hist, bb, 0, SORT_LOW_BITS);
     k_sort_scan<<<n_shard, 1024, 0, st>>>(d_sh, sh_hist, nb0);
-    k_sort_scatter<0><<<gs, 256, 0, st>>>(d_in, nullptr, nullptr, d_sh, sh_hist, sa_pos, sa_v, bb, 0, SORT_LOW_BITS);
+    k_sort_scatter<0><<<gs, 256, SORT_SCATTER_SMEM, st>>>(d_in, nullptr, nullptr, d_sh, sh_hist, sa_pos, sa_v, bb, 0, SORT_LOW_BITS);
     ctx->launches += 3; stage_mark(ctx, "k_sort_pass0");
     k_sort_hist<1><<<gs, 256, 0, st>>>(d_in, sa_v, d_sh, sh_hist, bb, SORT_LOW_BITS, bb - SORT_LOW_BITS);
     k_sort_scan<<<n_shard, 1024, 0, st>>>(d_sh, sh_hist, nb1);
-    k_sort_scatter<1><<<gs, 256, 0, st>>>(d_in, sa_pos, sa_v, d_sh, sh_hist, sb_pos, sb_v, bb, SORT_LOW_BITS, bb - SORT_LOW_BITS);
+    k_sort_scatter<1><<<gs, 256, SORT_SCATTER_SMEM, st>>>(d_in, sa_pos, sa_v, d_sh, sh_hist, sb_pos, sb_v, bb, SORT_LOW_BITS, bb - SORT_LOW_BITS);
     ctx->launches += 3; stage_mark(ctx, "k_sort_pass1");
-    CK(cudaFuncSetAttribute(k_probe_sorted, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PROBE_SMEM));
-    k_probe_sorted<<<gp, 256, PROBE_SMEM, st>>>(d_in, d_sh, sb_pos, sb_v, best, P.k.depth, bb);
+    if (!(ctx->tune.flags & BGPU_F_PROBE_WINDOW)) {
+      const size_t sm = (size_t)(PROBE_TILE + P.k.depth) * 24;
+      CK(cudaFuncSetAttribute(k_probe_diag, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+      k_probe_diag<<<gp, 256, sm, st>>>(d_in, d_sh, sb_pos, sb_v, best, P.k.depth, bb);
+    } else {
+      CK(cudaFuncSetAttribute(k_probe_sorted, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PROBE_SMEM));
+      k_probe_sorted<<<gp, 256, PROBE_SMEM, st>>>(d_in, d_sh, sb_pos, sb_v, best, P.k.depth, bb);
+    }
     ctx->launches++; stage_mark(ctx, "k_probe");
   } else {
     CK(cudaMemsetAsync(best, 0, N * 4, st));
@@ -633,6 +640,8 @@ void bgpu_ctx_destroy(bgpu_ctx* c) {
   if (c->h_sizes) cudaFreeHost(c->h_sizes);
   if (c->pin) cudaFreeHost(c->pin);
   if (c->ev_ok) for (int i = 0; i <= bgpu_ctx::kMaxStages; i++) cudaEventDestroy(c->ev[i]);
+  if (c->hi_stream) cudaStreamDestroy(c->hi_stream);
+  if (c->hi_ev) cudaEventDestroy(c->hi_ev);
   if (c->own_stream) cudaStreamDestroy(c->own_stream);
   delete c;
 }

@@ -116,42 +116,49 @@ __global__ void __launch_bounds__(1024) k_sort_scan(const ShardD* __restrict__ s
 }
 
 // Stable scatter of one tile.  PASS 0: entry e is position e (v read from the input); PASS 1:
-// entries come from (src_pos, src_v).  256 threads = 8 warps; warp w ranks the contiguous slice
-// [w * 512, (w + 1) * 512) of the tile in 16 rounds of 32 consecutive entries, which keeps equal
-// digits in entry order.
-template <int PASS>
-__global__ void __launch_bounds__(256) k_sort_scatter(const uint8_t* __restrict__ in, const uint32_t* __restrict__ src_pos,
+// entries come from (src_pos, src_v).  WARPS warps; warp w ranks the contiguous slice
+// [w * SORT_TILE / WARPS, ...) of the tile in rounds of 32 consecutive entries, which keeps equal
+// digits in entry order.  The rounds of a warp are a dependent chain through its counter row (read counter,
+// match.any, leader adds the group size), so the kernel is latency-bound on that chain (r5d: 37 % of the stall
+// samples on the leader's store, short scoreboard 12 per issue, warps active 49 %): more, shorter chains per tile
+// (WARPS = 16: 8 rounds each) finish a tile sooner than 8 chains of 16 rounds.
+constexpr uint32_t SORT_SCATTER_SMEM = SORT_TILE * 8;
+template <int PASS, int WARPS = 8>
+__global__ void __launch_bounds__(32 * WARPS, 2048 / (32 * WARPS) > 5 ? 5 : 2048 / (32 * WARPS)) k_sort_scatter(const uint8_t* __restrict__ in, const uint32_t* __restrict__ src_pos,
                                                       const uint32_t* __restrict__ src_v, const ShardD* __restrict__ shards,
                                                       const uint32_t* __restrict__ hist, uint32_t* __restrict__ dst_pos,
                                                       uint32_t* __restrict__ dst_v, int bucket_bits, int shift, int nbits) {
-  constexpr int ROUNDS = SORT_TILE / 256;  // 16
-  __shared__ uint32_t s_cnt[8][SORT_BINS];
+  constexpr int THREADS = 32 * WARPS;
+  constexpr int ROUNDS = SORT_TILE / THREADS;
+  constexpr uint32_t SLICE = SORT_TILE / WARPS;
+  __shared__ uint16_t s_cnt[WARPS][SORT_BINS];
   __shared__ uint32_t s_base[SORT_BINS];   // tile-local exclusive offset of each digit
-  __shared__ uint32_t s_goff[SORT_BINS];   // shard-level destination of the digit's first entry of this tile
-  __shared__ uint32_t s_pos[SORT_TILE], s_v[SORT_TILE];
+  __shared__ uint32_t s_goff[SORT_BINS];   // shard-level destination of the digit's first entry of this tile, minus s_base
+  extern __shared__ __align__(16) uint32_t s_dyn[];   // SORT_SCATTER_SMEM bytes: the reorder buffers
+  uint32_t* s_pos = s_dyn; uint32_t* s_v = s_dyn + SORT_TILE;
   __shared__ uint32_t s_ws[8];
   const ShardD sh = shards[blockIdx.y];
   const uint32_t npos = shard_npos(sh), n_stile = shard_nstile(sh), tile = blockIdx.x;
   if (tile >= n_stile) return;
   const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
   const uint32_t nb = 1u << nbits;
-  for (uint32_t i = tid; i < 8 * SORT_BINS; i += 256) (&s_cnt[0][0])[i] = 0;
-  if (tid < nb) s_goff[tid] = hist[(size_t)sh.first_stile * SORT_BINS + (size_t)tid * n_stile + tile];
+  for (uint32_t i = tid; i < WARPS * SORT_BINS / 2; i += THREADS) reinterpret_cast<uint32_t*>(&s_cnt[0][0])[i] = 0;
+  uint32_t goff = 0;
+  if (tid < SORT_BINS) goff = tid < nb ? hist[(size_t)sh.first_stile * SORT_BINS + (size_t)tid * n_stile + tile] : 0;
   __syncthreads();
   const uint32_t base = tile * SORT_TILE;
   const uint8_t* sin = in + sh.in_off;
   uint32_t v[ROUNDS]; uint16_t rk[ROUNDS];
-  // all 16 loads of the thread first: the ranking rounds below are separated by __syncwarp, which keeps the
-  // compiler from hoisting a round's load above the previous round (r2i: long-scoreboard 15.5 per issue,
-  // issue active 26 %, one exposed global round trip per round)
+  // all loads of the thread first: the ranking rounds below are separated by __syncwarp, which keeps the
+  // compiler from hoisting a round's load above the previous round
 #pragma unroll
   for (int r = 0; r < ROUNDS; r++) {
-    const uint32_t e = base + w * (SORT_TILE / 8) + r * 32 + lane;
+    const uint32_t e = base + w * SLICE + r * 32 + lane;
     v[r] = e < npos ? sort_load<PASS>(sin, src_v + sh.in_off, e, sh.len, bucket_bits) : 0;
   }
 #pragma unroll
   for (int r = 0; r < ROUNDS; r++) {
-    const uint32_t e = base + w * (SORT_TILE / 8) + r * 32 + lane;
+    const uint32_t e = base + w * SLICE + r * 32 + lane;
     const bool valid = e < npos;
     const uint32_t d = valid ? sort_digit_of<PASS>(v[r], bucket_bits, shift, nbits) : (0x10000u | lane);
     const uint32_t peers = __match_any_sync(0xffffffffu, d);
@@ -159,28 +166,34 @@ __global__ void __launch_bounds__(256) k_sort_scatter(const uint8_t* __restrict_
     uint32_t b = 0;
     if (valid) b = s_cnt[w][d];
     __syncwarp();
-    if (valid && (peers >> lane) == 1u) s_cnt[w][d] = b + __popc(peers);
+    if (valid && (peers >> lane) == 1u) s_cnt[w][d] = (uint16_t)(b + __popc(peers));
     __syncwarp();
     rk[r] = (uint16_t)(b + before);
   }
   __syncthreads();
-  // per-digit exclusive prefix over the 8 warps, then exclusive scan over digits
+  // per-digit exclusive prefix over the warps, then exclusive scan over digits (threads 0 .. 255 hold one digit each)
   uint32_t tot = 0;
   if (tid < nb) {
 #pragma unroll
-    for (int ww = 0; ww < 8; ww++) { uint32_t c = s_cnt[ww][tid]; s_cnt[ww][tid] = tot; tot += c; }
+    for (int ww = 0; ww < WARPS; ww++) { uint32_t c = s_cnt[ww][tid]; s_cnt[ww][tid] = (uint16_t)tot; tot += c; }
   }
-  uint32_t incl = tot;
-  for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= (uint32_t)o) incl += y; }
-  if (lane == 31) s_ws[w] = incl;
+  if (tid < SORT_BINS) {
+    uint32_t incl = tot;
+    for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= (uint32_t)o) incl += y; }
+    if (lane == 31) s_ws[w] = incl;
+    tot = incl - tot;   // exclusive inside the warp
+  }
   __syncthreads();
-  uint32_t wb = 0;
-  for (uint32_t i = 0; i < w; i++) wb += s_ws[i];
-  s_base[tid] = wb + incl - tot;
+  if (tid < SORT_BINS) {
+    uint32_t wb = 0;
+    for (uint32_t i = 0; i < w; i++) wb += s_ws[i];
+    s_base[tid] = wb + tot;
+    s_goff[tid] = goff - (wb + tot);
+  }
   __syncthreads();
 #pragma unroll
   for (int r = 0; r < ROUNDS; r++) {
-    const uint32_t idx = w * (SORT_TILE / 8) + r * 32 + lane;
+    const uint32_t idx = w * SLICE + r * 32 + lane;
     const uint32_t e = base + idx;
     if (e < npos) {
       const uint32_t d = sort_digit_of<PASS>(v[r], bucket_bits, shift, nbits);
@@ -193,10 +206,10 @@ __global__ void __launch_bounds__(256) k_sort_scatter(const uint8_t* __restrict_
   const uint32_t nvalid = min(SORT_TILE, npos - base);
   uint32_t* dp = dst_pos + sh.in_off; uint32_t* dv = dst_v + sh.in_off;
 #pragma unroll 4
-  for (uint32_t j = tid; j < nvalid; j += 256) {
+  for (uint32_t j = tid; j < nvalid; j += THREADS) {
     const uint32_t vv = s_v[j];
     const uint32_t d = sort_digit_of<PASS>(vv, bucket_bits, shift, nbits);
-    const uint32_t dest = s_goff[d] + (j - s_base[d]);
+    const uint32_t dest = s_goff[d] + j;
     dp[dest] = s_pos[j]; dv[dest] = vv;
   }
 }
@@ -419,6 +432,117 @@ __global__ void __launch_bounds__(256, PROBE_MIN_BLOCKS) k_probe_sorted(const ui
   for (int k = 0; k < 4; k++) {
     const uint32_t e = e0 + k;
     if (g0 + e < npos) sbest[s_p[halo + e]] = (bLen[k] << 24) | bDist[k];
+  }
+}
+
+// Lane-per-entry form of the same probe ("diagonal": at chain step j every lane of a warp looks at the entry j places
+// before its own).  Consecutive lanes own consecutive sorted entries, so each step is one conflict-free row of shared
+// memory per warp: the 4 key bytes of entries e - j (one wavefront), and for the lanes whose candidate is confirmed its
+// position and 16 data bytes (contiguous 16-byte words, four wavefronts) — where k_probe_sorted gathers 16-byte words
+// at random offsets (r3g: 3.8 G bank-conflict wavefronts per GiB on top of ~1.3 G useful ones; here 0.1 G, r5e).
+// Same candidates, same order, same scores: bit-identical best[] (tools/probe_bench.cu, tools/ab_probe.py).
+//   * no per-step chain-limit state: the walk's only early end (backward > MAX_BACKWARD, hash-chains.ts:124) equals
+//     skipping every such candidate, because candidates come in order of growing distance; steps that would reach
+//     before the shard's first entry exist only in the first tile of a shard (EDGE);
+//   * candidates come in order of growing distance, so only a LONGER one can score higher (score = 135 len + 960 -
+//     30 log2 distance): the score is computed only then;
+//   * matches of >= 20 bytes are deferred to the input as in k_probe_sorted.
+// Issue-bound (r5e: issue active 84 %, 28 warp instructions per position at depth 16).
+// Shared memory: (PROBE_TILE + depth) * 24 bytes.
+__device__ __forceinline__ void probe_deferred(const uint8_t* sin, const uint32_t* s_p, uint32_t i0, uint32_t jc, uint32_t p, uint32_t mlen, uint32_t lm,
+                                               uint32_t& bLen, uint32_t& bDist, int& bScore) {
+  while (lm) {   // newest first
+    const uint32_t jj = __ffs((int)lm) - 1; lm &= lm - 1;
+    const uint32_t c = s_p[i0 - jc - jj - 1];
+    const uint32_t backward = p - c;
+    const int dcost = 960 - 30 * log2_floor(backward);
+    // Skip when even the full length cannot win.  Against an equal score the nearer candidate
+    // wins, so ">=" when the current best is nearer, ">" when it is farther.
+    const int ub = 135 * (int)mlen + dcost;
+    if (ub < bScore || (ub == bScore && bDist <= backward)) continue;
+    const uint32_t len = 20 + match_len16(sin, p + 20, c + 20, mlen - 20);
+    const int score = 135 * (int)len + dcost;
+    if (score > bScore || (score == bScore && backward < bDist)) { bScore = score; bLen = len; bDist = backward; }
+  }
+}
+template <bool EDGE>
+__device__ __forceinline__ void probe_entry(const uint8_t* sin, const uint4* s_x, const uint32_t* s_p, const uint32_t* s_v, uint32_t i0, uint32_t g,
+                                            uint32_t shard_len, int depth, uint32_t* sbest) {
+  const uint32_t v = s_v[i0], p = s_p[i0];
+  const uint4 x = s_x[i0];
+  const uint32_t mlen = min(shard_len - p, 128u);
+  uint32_t bLen = 0, bDist = 0; int bScore = 0;
+  const uint32_t jlim = EDGE ? min((uint32_t)depth, g) : (uint32_t)depth;
+  for (uint32_t jc = 0; jc < jlim; jc += 16) {
+    uint32_t lm = 0;
+#pragma unroll
+    for (uint32_t jj = 0; jj < 16; jj++) {
+      const uint32_t ci = i0 - jc - jj - 1;
+      if ((!EDGE || jc + jj < jlim) && s_v[ci] == v) {
+        const uint32_t cp = s_p[ci];
+        const uint4 cx = s_x[ci];
+        const uint32_t backward = p - cp;
+        const bool near = backward <= MAX_BACKWARD;
+        uint32_t len = 4 + prefix16(x, cx);
+        if (len == 20 && mlen > 20) { if (near) lm |= 1u << jj; }
+        else {
+          len = min(len, mlen);
+          if (len > bLen) {
+            const int score = 135 * (int)len + 960 - 30 * log2_floor(backward);
+            if (score > bScore && near) { bScore = score; bLen = len; bDist = backward; }
+          }
+        }
+      }
+    }
+    probe_deferred(sin, s_p, i0, jc, p, mlen, lm, bLen, bDist, bScore);
+  }
+  sbest[p] = (bLen << 24) | bDist;
+}
+__global__ void __launch_bounds__(256, 6) k_probe_diag(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
+                                                      const uint32_t* __restrict__ srt_pos, const uint32_t* __restrict__ srt_v,
+                                                      uint32_t* __restrict__ best, int depth, int bucket_bits) {
+  extern __shared__ __align__(16) uint8_t smem[];
+  const uint32_t halo = (uint32_t)depth;  // multiple of 16, <= PROBE_HALO
+  const uint32_t n_ent = PROBE_TILE + halo;
+  uint4* s_x = reinterpret_cast<uint4*>(smem);
+  uint32_t* s_p = reinterpret_cast<uint32_t*>(s_x + n_ent);
+  uint32_t* s_v = s_p + n_ent;
+  const ShardD sh = shards[blockIdx.y];
+  const uint32_t npos = shard_npos(sh);
+  const uint32_t g0 = blockIdx.x * PROBE_TILE;
+  const uint32_t tid = threadIdx.x;
+  uint32_t* sbest = best + sh.in_off;
+  // the <= 3 tail positions of the shard have no 4-byte key: no candidate
+  if (blockIdx.x == 0 && tid < sh.len - npos) sbest[npos + tid] = 0;
+  if (g0 >= npos) return;
+  const uint32_t* sp = srt_pos + sh.in_off; const uint32_t* sv = srt_v + sh.in_off;
+  const uint8_t* sin = in + sh.in_off;
+  {
+    // staging in three sweeps so that the loads of all (up to 5) entries of a thread are in flight together:
+    // positions and key bytes, then the dependent 16 data bytes behind each position, then the stores
+    constexpr int NST = (PROBE_TILE + PROBE_HALO + 255) / 256;
+    uint32_t pp[NST], vv[NST]; uint4 xx[NST]; bool ok[NST];
+#pragma unroll
+    for (int t = 0; t < NST; t++) {
+      const uint32_t i = tid + 256 * t;
+      const int64_t g = (int64_t)g0 - halo + i;
+      ok[t] = i < n_ent && g >= 0 && g < (int64_t)npos;
+      pp[t] = ok[t] ? __ldg(sp + g) : 0;
+      vv[t] = ok[t] ? __ldg(sv + g) : 0;
+    }
+#pragma unroll
+    for (int t = 0; t < NST; t++) xx[t] = ok[t] ? ld128v(sin + pp[t] + 4) : make_uint4(0, 0, 0, 0);   // reads <= 36 bytes past p: inside the padded input
+#pragma unroll
+    for (int t = 0; t < NST; t++) {
+      const uint32_t i = tid + 256 * t;
+      if (i < n_ent) { s_p[i] = pp[t]; s_v[i] = vv[t]; s_x[i] = xx[t]; }
+    }
+  }
+  __syncthreads();
+  if (g0 < halo) {
+    for (uint32_t r = 0; r < PROBE_TILE / 256; r++) { const uint32_t e = r * 256 + tid; if (g0 + e < npos) probe_entry<true>(sin, s_x, s_p, s_v, halo + e, g0 + e, sh.len, depth, sbest); }
+  } else {
+    for (uint32_t r = 0; r < PROBE_TILE / 256; r++) { const uint32_t e = r * 256 + tid; if (g0 + e < npos) probe_entry<false>(sin, s_x, s_p, s_v, halo + e, g0 + e, sh.len, depth, sbest); }
   }
 }
 
