@@ -274,7 +274,8 @@ HDN inline int tree_rle(const uint8_t* depth, int length, uint8_t* rle_sym, uint
 // context-map.ts:215-347 buildAndStoreHuffmanTree, serialisation half.  `depth`/`bits` already hold
 // the code for `alphabet` symbols with `count` (>= 2) non-zero histogram entries; s4 the first four.
 // For count <= 1 use tree_store_single.  rle_* are scratch (alphabet + 8 bytes each).
-HDN inline void tree_store(BitSink& w, const uint8_t* depth, int alphabet, int count, const uint16_t* s4,
+template <class Sink>
+HDN inline void tree_store(Sink& w, const uint8_t* depth, int alphabet, int count, const uint16_t* s4,
                            uint8_t* rle_sym, uint8_t* rle_extra) {
   uint32_t maxBits = 0; uint32_t c = (uint32_t)alphabet - 1;
   while (c) { c >>= 1; maxBits++; }
@@ -336,7 +337,8 @@ HDN inline void tree_store(BitSink& w, const uint8_t* depth, int alphabet, int c
   }
 }
 // context-map.ts:236-243: zero or one used symbol
-HD void tree_store_single(BitSink& w, int alphabet, uint32_t symbol) {
+template <class Sink>
+HD void tree_store_single(Sink& w, int alphabet, uint32_t symbol) {
   uint32_t maxBits = 0; uint32_t c = (uint32_t)alphabet - 1;
   while (c) { c >>= 1; maxBits++; }
   w.put(4, 1); w.put(maxBits, symbol);
@@ -345,7 +347,8 @@ HD void tree_store_single(BitSink& w, int alphabet, uint32_t symbol) {
 // ------------------------------------------------------------------------------------------
 // Serial coders of the metablock header (one thread per metablock in k_mb_header): small prefix codes
 // (block types, block lengths, context-map symbols) and encodeContextMap.
-HD void put_varlen8(BitSink& w, uint32_t n) {  // context-map.ts:524-533
+template <class Sink>
+HD void put_varlen8(Sink& w, uint32_t n) {  // context-map.ts:524-533
   if (n == 0) { w.put(1, 0); return; }
   const uint32_t nbits = log2_floor(n);
   w.put(1, 1); w.put(3, nbits); w.put(nbits, n - (1u << nbits));
@@ -358,7 +361,8 @@ struct SerialHuff {
   uint32_t hist[SH_MAX]; uint8_t depth[SH_MAX]; uint16_t bits[SH_MAX];
 };
 // buildAndStoreHuffmanTree (context-map.ts:215-264) of S.hist, one thread.
-HDN inline void huff_serial_store(BitSink& w, SerialHuff& S, int alphabet) {
+template <class Sink>
+HDN inline void huff_serial_store(Sink& w, SerialHuff& S, int alphabet) {
   uint16_t s4[4] = {0, 0, 0, 0}; int n = 0;
   for (int i = 0; i < alphabet; i++) { S.depth[i] = 0; S.bits[i] = 0; if (S.hist[i]) { if (n < 4) s4[n] = (uint16_t)i; n++; } }
   if (n <= 1) { tree_store_single(w, alphabet, s4[0]); return; }
