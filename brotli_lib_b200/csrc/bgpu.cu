@@ -116,7 +116,7 @@ struct bgpu_ctx {
   DBuf in, sa_pos, sa_v, sb_pos, sb_v, sort_hist, role, ins, cmds, out, shards, mbs, segs, tile_seg, seg_ncmd, seg_trail, seg_ring, hist, codes, tree_bits, tree_nbits,
       tile_bits, tile_off, tile_model, warp_base, thr_off, shard_bytes, huff_meta, model_arena, misc_arena, d_models, d_splits, d_cb, d_cx, d_bh_ptrs, d_bh_strides, d_cx_outs,
       h10_bstart, h10_bend, h10_short, h10_forest, h10_m, h10_off, h10_cnt, h10_cursor, h10_full, h10_hot,
-      zop_bytehist, zop_model, zop_lc, zop_nodes, zop_ring, stats, dec_arena, dec_results, dec_jobs, seg_aux;
+      zop_bytehist, zop_model, zop_lc, zop_nodes, zop_ring, stats, dec_arena, dec_results, dec_jobs, seg_aux, tile_stage, tile_flag, fb_count;
   uint32_t h10_cap = 0;
   uint64_t counters[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // [0] H10 match entries; [1..3] model table bytes (BGPU_F_MODEL_STATS); [4] shards that failed BGPU_F_VERIFY
   bool lut_ready = false;
@@ -625,7 +625,7 @@ void bgpu_ctx_destroy(bgpu_ctx* c) {
                  &c->seg_trail, &c->seg_ring, &c->hist, &c->codes, &c->tree_bits, &c->tree_nbits, &c->tile_bits, &c->tile_off, &c->tile_model, &c->warp_base, &c->thr_off, &c->shard_bytes, &c->huff_meta,
                  &c->model_arena, &c->misc_arena, &c->d_models, &c->d_splits, &c->d_cb, &c->d_cx, &c->d_bh_ptrs, &c->d_bh_strides, &c->d_cx_outs,
                  &c->h10_bstart, &c->h10_bend, &c->h10_short, &c->h10_forest, &c->h10_m, &c->h10_off, &c->h10_cnt, &c->h10_cursor, &c->h10_full, &c->h10_hot,
-                 &c->zop_bytehist, &c->zop_model, &c->zop_lc, &c->zop_nodes, &c->zop_ring, &c->stats, &c->dec_arena, &c->dec_results, &c->dec_jobs, &c->seg_aux};
+                 &c->zop_bytehist, &c->zop_model, &c->zop_lc, &c->zop_nodes, &c->zop_ring, &c->stats, &c->dec_arena, &c->dec_results, &c->dec_jobs, &c->seg_aux, &c->tile_stage, &c->tile_flag, &c->fb_count};
   for (DBuf* b : all) b->release();
   for (bgpu_ctx* l : c->lanes) bgpu_ctx_destroy(l);
   c->lanes.clear();

@@ -270,37 +270,117 @@ __global__ void __launch_bounds__(256) k_offsets2(const ShardD* __restrict__ sha
   }
 }
 
+// Round-1 token writer, now the fall-back of k_tile_pack / k_tile_copy: emits the tiles listed in fb_list[0 .. *fb_count)
+// (tiles whose bits did not fit the packed form) by recomputing their tokens.  A fixed grid walks the list.
 __global__ void __launch_bounds__(256) k_write2(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
                                                 const SegD* __restrict__ segs, const uint32_t* __restrict__ tile_seg,
                                                 const MbModel* __restrict__ models, const uint8_t* __restrict__ role,
                                                 const uint32_t* __restrict__ ins_at, const Cmd* __restrict__ cmds,
                                                 const uint32_t* __restrict__ tile_model, const uint32_t* __restrict__ tile_bits,
                                                 const uint32_t* __restrict__ tile_off, const uint32_t* __restrict__ warp_base,
-                                                const uint16_t* __restrict__ thr_off, uint8_t* __restrict__ out, Params P) {
+                                                const uint16_t* __restrict__ thr_off, uint8_t* __restrict__ out,
+                                                const uint32_t* __restrict__ fb_list, const uint32_t* __restrict__ fb_count, Params P) {
   __shared__ uint32_t s_stage[STAGE_WORDS];
   __shared__ uint32_t s_w[8][3];
   __shared__ TileModel s_T;
-  const uint32_t tile = blockIdx.x;
-  const uint32_t total = tile_bits[tile];
-  if (total == 0) return;
+  const uint32_t n_fb = *fb_count;
+  for (uint32_t idx = blockIdx.x; idx < n_fb; idx += gridDim.x) {
+    const uint32_t tile = fb_list[idx];
+    const uint32_t total = tile_bits[tile];
+    if (total == 0) continue;
+    const SegD sg = segs[tile_seg[tile]];
+    const ShardD sh = shards[sg.shard];
+    const MbModel& M = models[sg.mb];
+    const bool trivial = M.cnt[4] != 0;
+    const uint32_t tid = threadIdx.x;
+    const uint32_t off = tile_off[tile];
+    const uint32_t head = off & 31;
+    const uint32_t nwords = (head + total + 31) >> 5;
+    const bool staged = nwords + 2 <= STAGE_WORDS;
+    __syncthreads();   // the previous tile of this CTA is done with the shared arrays
+    if (staged) for (uint32_t i = tid; i < nwords + 2; i += 256) s_stage[i] = 0;
+    const uint32_t tile_rel = sg.rel_pos + (tile - sg.first_tile) * TILE;
+    const uint32_t tile_end = min(sg.rel_pos + sg.len, tile_rel + TILE);
+    tile_model_load(M, tile, tile_model, trivial, s_T);
+    TileRanks R = tile_ranks(M, tile, sh, tile_rel, tile_end, role, cmds, P.sh, s_w);   // contains a __syncthreads
+    uint32_t bitpos = head + warp_base[(size_t)tile * 8 + (tid >> 5)] + thr_off[(size_t)tile * 256 + tid];
+    uint32_t* gw = reinterpret_cast<uint32_t*>(out + sh.out_off) + (off >> 5);
+#pragma unroll
+    for (int k = 0; k < 4; k++) {
+      const uint32_t r = R.r[k];
+      if (!r) continue;
+      const uint64_t p = sh.in_off + tile_rel + 4 * tid + k;
+      const Tok4 t = position_tokens2(in, p, r, ins_at, cmds, M, R.il, R.ic, R.id, P.sh, trivial, s_T);
+      R.il += r & 1; R.ic += (r >> 2) & 1; R.id += (r >> 4) & 1;
+#pragma unroll
+      for (int f = 0; f < 4; f++) {
+        if (staged) sput(s_stage, bitpos, t.n[f], t.v[f]); else sput(gw, bitpos, t.n[f], t.v[f]);
+        bitpos += t.n[f];
+      }
+    }
+    if (!staged) continue;
+    __syncthreads();
+    for (uint32_t i = tid; i < nwords; i += 256) {
+      const uint32_t v = s_stage[i];
+      if (i == 0 || i == nwords - 1) { if (v) atomicOr(&gw[i], v); }
+      else gw[i] = v;
+    }
+  }
+}
+
+// ---- One-pass form of the bit writer: the tokens of a tile are computed ONCE.
+//   k_tile_pack   k_tilebits2 + the token half of k_write2: every thread appends the tokens of its 4 positions to a
+//                 private 256-bit slot in shared memory, a CTA scan of the bit counts gives each thread its offset in
+//                 the tile, the slots are OR-ed into the tile's bit string (shared memory) and the string goes to
+//                 tile_stage[tile] (PACK_WORDS words per tile) in coalesced stores.
+//   k_offsets2    unchanged (bit offset of every tile inside its shard).
+//   k_tile_copy   shifts each tile's string to its final bit offset: reads M bytes, writes M bytes; `in`, `role`,
+//                 `ins`, `cmds`, the codes and the block model are not touched again (k_write2 re-read all of them:
+//                 15.2 GB of DRAM traffic per GiB against 1.56 GB algorithmic, profiles/traffic.json).
+// A tile that does not fit (a thread with > 256 bits, or > PACK_WORDS words in the tile: incompressible data with long
+// codes) takes the round-1 path: k_tile_pack leaves thr_off / warp_base for it and appends it to fb_list, which
+// k_write2 (a fixed grid) walks.
+constexpr uint32_t PACK_WORDS = 640;          // 20 bits per position of a 1024-position tile
+constexpr uint32_t PACK_SLOT_WORDS = 8;       // private bits per thread (4 positions)
+
+__device__ __forceinline__ void pput(uint32_t* slot, uint32_t pos, uint32_t nbits, uint64_t value) {   // slot: word w at slot[w * 256]
+  if (!nbits) return;
+  const uint32_t i = pos >> 5, o = pos & 31;
+  const unsigned long long lo = (unsigned long long)value << o;
+  slot[i * 256] |= (uint32_t)lo;
+  if (o + nbits > 32) slot[(i + 1) * 256] |= (uint32_t)(lo >> 32);
+  if (o + nbits > 64) slot[(i + 2) * 256] |= (uint32_t)(value >> (64 - o));
+}
+
+__global__ void __launch_bounds__(256) k_tile_pack(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
+                                                   const SegD* __restrict__ segs, const uint32_t* __restrict__ tile_seg,
+                                                   const MbModel* __restrict__ models, const uint8_t* __restrict__ role,
+                                                   const uint32_t* __restrict__ ins_at, const Cmd* __restrict__ cmds,
+                                                   const uint32_t* __restrict__ tile_model, uint32_t* __restrict__ tile_bits,
+                                                   uint32_t* __restrict__ warp_base, uint16_t* __restrict__ thr_off,
+                                                   uint32_t* __restrict__ tile_stage, uint8_t* __restrict__ tile_flag,
+                                                   uint32_t* __restrict__ fb_list, uint32_t* __restrict__ fb_count, Params P) {
+  __shared__ uint32_t s_w[8][3];
+  __shared__ uint32_t s_sum[8];
+  __shared__ uint32_t s_over;
+  __shared__ TileModel s_T;
+  __shared__ uint32_t s_slot[(PACK_SLOT_WORDS + 3) * 256];   // + 3: a put that overflows the slot stays inside the array
+  __shared__ uint32_t s_str[PACK_WORDS + 2];
+  const uint32_t tile = blockIdx.x, tid = threadIdx.x;
   const SegD sg = segs[tile_seg[tile]];
   const ShardD sh = shards[sg.shard];
   const MbModel& M = models[sg.mb];
   const bool trivial = M.cnt[4] != 0;
-  const uint32_t tid = threadIdx.x;
-  const uint32_t off = tile_off[tile];
-  const uint32_t head = off & 31;
-  const uint32_t nwords = (head + total + 31) >> 5;
-  const bool staged = nwords + 2 <= STAGE_WORDS;
-  if (staged) for (uint32_t i = tid; i < nwords + 2; i += 256) s_stage[i] = 0;
   const uint32_t tile_rel = sg.rel_pos + (tile - sg.first_tile) * TILE;
   const uint32_t tile_end = min(sg.rel_pos + sg.len, tile_rel + TILE);
+#pragma unroll
+  for (uint32_t w = 0; w < PACK_SLOT_WORDS + 3; w++) s_slot[w * 256 + tid] = 0;
+  for (uint32_t i = tid; i < PACK_WORDS + 2; i += 256) s_str[i] = 0;
+  if (tid == 0) s_over = 0;
   tile_model_load(M, tile, tile_model, trivial, s_T);
   TileRanks R = tile_ranks(M, tile, sh, tile_rel, tile_end, role, cmds, P.sh, s_w);   // contains a __syncthreads
-  // the thread's bit offset comes from k_tilebits2, so each position's tokens are packed as soon as they
-  // are known: no token array, no second scan (80 -> fewer registers, more resident CTAs)
-  uint32_t bitpos = head + warp_base[(size_t)tile * 8 + (tid >> 5)] + thr_off[(size_t)tile * 256 + tid];
-  uint32_t* gw = reinterpret_cast<uint32_t*>(out + sh.out_off) + (off >> 5);
+  uint32_t bits = 0;
+  uint32_t* slot = s_slot + tid;
 #pragma unroll
   for (int k = 0; k < 4; k++) {
     const uint32_t r = R.r[k];
@@ -310,14 +390,64 @@ __global__ void __launch_bounds__(256) k_write2(const uint8_t* __restrict__ in, 
     R.il += r & 1; R.ic += (r >> 2) & 1; R.id += (r >> 4) & 1;
 #pragma unroll
     for (int f = 0; f < 4; f++) {
-      if (staged) sput(s_stage, bitpos, t.n[f], t.v[f]); else sput(gw, bitpos, t.n[f], t.v[f]);
-      bitpos += t.n[f];
+      if (bits + t.n[f] <= PACK_SLOT_WORDS * 32) pput(slot, bits, t.n[f], t.v[f]);
+      bits += t.n[f];
     }
   }
-  if (!staged) return;
+  if (bits > PACK_SLOT_WORDS * 32) s_over = 1;   // benign race: every writer stores 1
+  uint32_t incl = bits;
+  for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, incl, o); if ((tid & 31) >= (uint32_t)o) incl += y; }
+  if ((tid & 31) == 31) s_sum[tid >> 5] = incl;
   __syncthreads();
-  for (uint32_t i = tid; i < nwords; i += 256) {
-    const uint32_t v = s_stage[i];
+  uint32_t wb = 0, total = 0;
+  for (uint32_t i = 0; i < 8; i++) { if (i < (tid >> 5)) wb += s_sum[i]; total += s_sum[i]; }
+  const bool packed = !s_over && total <= PACK_WORDS * 32;
+  if (tid == 0) { tile_bits[tile] = total; tile_flag[tile] = packed ? 1 : 0; if (!packed && total) fb_list[atomicAdd(fb_count, 1u)] = tile; }
+  if (!packed) {   // round-1 path: k_write2 recomputes the tokens of this tile
+    thr_off[(size_t)tile * 256 + tid] = (uint16_t)(incl - bits);
+    if ((tid & 31) == 0) warp_base[(size_t)tile * 8 + (tid >> 5)] = wb;
+    return;
+  }
+  const uint32_t toff = wb + incl - bits;
+  for (uint32_t w = 0; w * 32 < bits; w++) {
+    const uint32_t v = slot[w * 256];
+    if (!v) continue;
+    const uint32_t d = toff + w * 32, i = d >> 5, o = d & 31;
+    atomicOr(&s_str[i], v << o);
+    if (o) atomicOr(&s_str[i + 1], v >> (32 - o));
+  }
+  __syncthreads();
+  uint32_t* dst = tile_stage + (size_t)tile * PACK_WORDS;
+  for (uint32_t i = tid; i * 32 < total; i += 256) dst[i] = s_str[i];
+}
+
+__global__ void __launch_bounds__(256) k_fb_all(uint32_t* __restrict__ fb_list, uint32_t* __restrict__ fb_count, uint32_t n_tile) {
+  const uint32_t i = blockIdx.x * 256 + threadIdx.x;
+  if (i < n_tile) fb_list[i] = i;
+  if (i == 0) *fb_count = n_tile;
+}
+
+// One warp per tile: the tile's bit string moves to bit offset tile_off[tile] of its shard's output region
+// (zeroed; neighbouring tiles share the first and last word, hence the OR there).
+__global__ void __launch_bounds__(256) k_tile_copy(const ShardD* __restrict__ shards, const SegD* __restrict__ segs, const uint32_t* __restrict__ tile_seg,
+                                                   const uint32_t* __restrict__ tile_bits, const uint32_t* __restrict__ tile_off,
+                                                   const uint32_t* __restrict__ tile_stage, const uint8_t* __restrict__ tile_flag,
+                                                   uint8_t* __restrict__ out, uint32_t n_tile) {
+  const uint32_t tile = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (tile >= n_tile || !tile_flag[tile]) return;
+  const uint32_t total = tile_bits[tile];
+  if (total == 0) return;
+  const ShardD sh = shards[segs[tile_seg[tile]].shard];
+  const uint32_t off = tile_off[tile], head = off & 31;
+  const uint32_t nsrc = (total + 31) >> 5, nwords = (head + total + 31) >> 5;
+  const uint32_t* src = tile_stage + (size_t)tile * PACK_WORDS;
+  uint32_t* gw = reinterpret_cast<uint32_t*>(out + sh.out_off) + (off >> 5);
+  const uint32_t tail_mask = (total & 31) ? (1u << (total & 31)) - 1u : 0xFFFFFFFFu;
+  for (uint32_t i = lane; i < nwords; i += 32) {
+    uint32_t cur = i < nsrc ? src[i] : 0u, prev = (i > 0 && head) ? src[i - 1] : 0u;
+    if (i == nsrc - 1) cur &= tail_mask;
+    if (i > 0 && i - 1 == nsrc - 1) prev &= tail_mask;
+    const uint32_t v = head ? (cur << head) | (prev >> (32 - head)) : cur;
     if (i == 0 || i == nwords - 1) { if (v) atomicOr(&gw[i], v); }
     else gw[i] = v;
   }
