@@ -425,7 +425,7 @@ int run_frontend(bgpu_ctx* ctx, const Job& job, const EncParams& P, const uint8_
     ctx->launches++;
   }
   stage_mark(ctx, "k_parse");
-  k_stitch<<<(n_mb + 63) / 64, 64, 0, st>>>(d_sh, d_mb, d_sg, n_mb, ctx->role.as<uint8_t>(), ctx->ins.as<uint32_t>(), ctx->cmds.as<Cmd>(),
+  k_stitch<<<n_mb, 32, 0, st>>>(d_sh, d_mb, d_sg, n_mb, ctx->role.as<uint8_t>(), ctx->ins.as<uint32_t>(), ctx->cmds.as<Cmd>(),
                                             ctx->seg_ncmd.as<uint32_t>(), ctx->seg_trail.as<uint32_t>(), Pk);
   ctx->launches++;
   if (n_seg > 1) {

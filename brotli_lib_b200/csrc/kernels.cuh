@@ -199,34 +199,54 @@ __global__ void __launch_bounds__(128) k_parse(const uint8_t* __restrict__ in, c
 // Joins the segments of a metablock: literals left over at the end of a segment become part of the
 // next segment's first command; what remains at the metablock end is the insert-only command of
 // encode.ts:253-267 / command.ts:183-208.
-__global__ void k_stitch(const ShardD* __restrict__ shards, const MbD* __restrict__ mbs, const SegD* __restrict__ segs,
+// One warp per metablock.  The pending literal run ("carry") after segment s is a function of the carry before it:
+// a segment with commands replaces it by its own trailing literals (or none), a segment without commands keeps a
+// pending run and otherwise starts one.  These functions compose ({keeps, own value}), so the carry entering every
+// segment comes from a warp scan over 32 segments at a time, and the segments then apply their edits in parallel
+// (each pending run is consumed by exactly one later segment).  Round 1 walked the 512 segments of a 4 MiB
+// metablock with one thread: 1.3 ms per job whatever its size.
+__global__ void __launch_bounds__(32) k_stitch(const ShardD* __restrict__ shards, const MbD* __restrict__ mbs, const SegD* __restrict__ segs,
                          uint32_t n_mb, uint8_t* __restrict__ role, uint32_t* __restrict__ ins_at, Cmd* __restrict__ cmds,
                          const uint32_t* __restrict__ seg_ncmd, const uint32_t* __restrict__ seg_trail, Params P) {
-  const uint32_t m = blockIdx.x * blockDim.x + threadIdx.x;
+  const uint32_t m = blockIdx.x, lane = threadIdx.x;
   if (m >= n_mb) return;
   const MbD mb = mbs[m];
   const ShardD sh = shards[mb.shard];
   uint8_t* srole = role + sh.in_off;
-  int64_t carry = -1;  // start of the pending (not yet terminated) literal run, shard-relative
-  for (uint32_t s = mb.first_seg; s < mb.first_seg + mb.n_seg; s++) {
-    const SegD sg = segs[s];
+  int64_t carry = -1;  // carry entering the current chunk of 32 segments (warp-uniform), shard-relative start of the pending run
+  for (uint32_t s0 = 0; s0 < mb.n_seg; s0 += 32) {
+    const uint32_t s = mb.first_seg + s0 + lane;
+    const bool live = s0 + lane < mb.n_seg;
+    SegD sg; sg.rel_pos = 0; sg.len = 0;
+    uint32_t nc = 0, trail = 0;
+    if (live) { sg = segs[s]; nc = seg_ncmd[s]; trail = seg_trail[s]; }
     const uint32_t seg_end = sg.rel_pos + sg.len;
-    const uint32_t nc = seg_ncmd[s], trail = seg_trail[s];
-    if (carry >= 0) {
+    // f(x) = (keeps && x >= 0) ? x : own;  dead lanes are the identity (keeps, own = -1)
+    bool keeps = !live || nc == 0;
+    int64_t own = (live && trail < seg_end) ? (int64_t)trail : -1;
+    // inclusive scan of the composition "earlier first"
+    for (int o = 1; o < 32; o <<= 1) {
+      const bool pk = __shfl_up_sync(0xffffffffu, keeps, o) != 0;
+      const int64_t po = __shfl_up_sync(0xffffffffu, own, o);
+      if (lane >= (uint32_t)o) { if (keeps) { own = po >= 0 ? po : own; keeps = pk; } }
+    }
+    const int64_t out = (keeps && carry >= 0) ? carry : own;            // carry after this lane's segment
+    int64_t in_c = __shfl_up_sync(0xffffffffu, out, 1);                 // carry before it
+    if (lane == 0) in_c = carry;
+    if (live && in_c >= 0) {
       srole[sg.rel_pos] &= ~4;
       if (nc > 0) {
-        uint32_t ins_old = ins_at[(sh.in_off + sg.rel_pos) >> P.sh];
-        uint32_t ins_new = ins_old + (sg.rel_pos - (uint32_t)carry);
+        const uint32_t ins_old = ins_at[(sh.in_off + sg.rel_pos) >> P.sh];
+        const uint32_t ins_new = ins_old + (sg.rel_pos - (uint32_t)in_c);
         Cmd* c = &cmds[(sh.in_off + sg.rel_pos + ins_old) >> P.sh];
         c->insertLen = ins_new;
         c->cmdPrefix = (uint16_t)combine_codes(ins_code(ins_new), copy_code(c->copyLen & 0x1FFFFFF), (c->distPrefix & 0x3FF) == 0);
-        ins_at[(sh.in_off + (uint32_t)carry) >> P.sh] = ins_new;
-        carry = -1;
+        ins_at[(sh.in_off + (uint32_t)in_c) >> P.sh] = ins_new;
       }
     }
-    if (nc > 0 || carry < 0) carry = trail < seg_end ? (int64_t)trail : -1;
+    carry = __shfl_sync(0xffffffffu, out, 31);
   }
-  if (carry >= 0) {
+  if (lane == 0 && carry >= 0) {
     srole[carry] |= 8;
     ins_at[(sh.in_off + (uint32_t)carry) >> P.sh] = mb.rel_pos + mb.len - (uint32_t)carry;
   }
