@@ -80,13 +80,16 @@ namespace bgpu {
 // command (the ring only changes at accepted matches, so the speculation is exact).
 __device__ __forceinline__ uint32_t distance_to_code(uint32_t distance, const int* ring) {
   // backward-references.ts:146-158, plus a guard so that ring entries not yet learned in this
-  // segment (0) are never referenced.
-  const int8_t off[16] = {0, 0, 0, 0, -1, 1, -2, 2, -3, 3, -1, 1, -2, 2, -3, 3};
+  // segment (0) are never referenced.  The reference tries 16 candidates in order: ring[0..3], then ring[0] -1 +1 -2 +2
+  // -3 +3, then the same around ring[1]; the six offsets of a base are distinct, so at most one of them fits and
+  // the order inside a base does not matter (r5m: the unrolled 16-way compare was 17 % of k_parse's instructions).
+  const int d = (int)distance;
 #pragma unroll
-  for (int i = 0; i < 16; i++) {
-    int base = i < 4 ? ring[i] : (i < 10 ? ring[0] : ring[1]);
-    int cached = base + off[i];
-    if (base > 0 && cached > 0 && (int)distance == cached) return i;
+  for (int i = 0; i < 4; i++) if (ring[i] > 0 && d == ring[i]) return (uint32_t)i;
+#pragma unroll
+  for (int k = 0; k < 2; k++) {
+    const int delta = d - ring[k], a = delta < 0 ? -delta : delta;
+    if (ring[k] > 0 && a >= 1 && a <= 3) return (uint32_t)(4 + 6 * k + 2 * (a - 1) + (delta > 0 ? 1 : 0));
   }
   return distance + 15;
 }
