@@ -443,7 +443,7 @@ def measure(args, wl, ctx, torch, dist, dev, rank, world, local_rank, steps, war
         "vs_baseline": None, "dtype": "u8", "data": "synthetic",
         "config": {"workload": wl["label"].format(mb=wl["size_mb"], shards=(n + (1 << 22) - 1) >> 22),
                    "timing": "CUDA events on the launching stream (lanes fork from / join to it), max over ranks",
-                   "lanes": tune.get("lanes") or "library default (4 lanes, groups of shards/4 clamped to 16..64, for q5-9; 1 lane for q10/11)",
+                   "lanes": tune.get("lanes") or "library default (4 lanes, groups of shards/4 clamped to 16..64, at every quality >= 1; at q10/11 a lane defers its H10 capacity check to the host loop)",
                    "stage_timing": f"roofline.stages / launch_ms: one-lane in-order passes after the timed region ({round(t_one_lane * 1e3, 1)} ms per step)",
                    "l2": f"input ({wl['size_mb']} MiB) and every intermediate array exceed the 126 MB L2; no flush needed",
                    "compressed_ratio": round(M / n, 4), "verified_roundtrip": verified, "verified_on_device": device_verified,

@@ -75,6 +75,9 @@ __device__ __forceinline__ float hist_cost(const uint32_t* a, const uint32_t* b,
       if (b) { const uint4 y = SHARED ? b4[i] : __ldcg(b4 + i); v[t].x += y.x; v[t].y += y.y; v[t].z += y.z; v[t].w += y.w; }
     }
   }
+  // The entropy term is the only float reduction (5 butterfly steps).  The non-zero count and the zero-run count come
+  // from ballots of the four bins of every lane — the same value in all lanes, no reduction — and the total from one
+  // REDUX (r5m: the four 5-step shuffle reductions + 2 shuffles per piece were most of a pair evaluation).
   float ent = 0.f; uint32_t tot = 0, nnz = 0, runs = 0, carry = 1;
 #pragma unroll
   for (int t = 0; t < NV; t++) {
@@ -85,19 +88,16 @@ __device__ __forceinline__ float hist_cost(const uint32_t* a, const uint32_t* b,
       if (x.y) ent -= (float)x.y * flog2((float)x.y);
       if (x.z) ent -= (float)x.z * flog2((float)x.z);
       if (x.w) ent -= (float)x.w * flog2((float)x.w);
-      const uint32_t m = (x.x ? 1u : 0u) | (x.y ? 2u : 0u) | (x.z ? 4u : 0u) | (x.w ? 8u : 0u);
+      const uint32_t b0 = __ballot_sync(0xffffffffu, x.x != 0), b1 = __ballot_sync(0xffffffffu, x.y != 0),
+                     b2 = __ballot_sync(0xffffffffu, x.z != 0), b3 = __ballot_sync(0xffffffffu, x.w != 0);
+      nnz += __popc(b0) + __popc(b1) + __popc(b2) + __popc(b3);
       // zero runs that END at a non-zero bin (leading and interior ones, never the trailing run)
-      uint32_t prev = __shfl_up_sync(0xffffffffu, m >> 3, 1);
-      if (lane == 0) prev = carry;
-      nnz += __popc(m);
-      runs += __popc(m & ~((m << 1) | prev) & 15u);
-      carry = __shfl_sync(0xffffffffu, m >> 3, 31);
+      runs += __popc(b0 & ~((b3 << 1) | carry)) + __popc(b1 & ~b0) + __popc(b2 & ~b1) + __popc(b3 & ~b2);
+      carry = b3 >> 31;
     }
   }
-  for (int o = 16; o; o >>= 1) {
-    ent += __shfl_xor_sync(0xffffffffu, ent, o); tot += __shfl_xor_sync(0xffffffffu, tot, o);
-    nnz += __shfl_xor_sync(0xffffffffu, nnz, o); runs += __shfl_xor_sync(0xffffffffu, runs, o);
-  }
+  for (int o = 16; o; o >>= 1) ent += __shfl_xor_sync(0xffffffffu, ent, o);
+  tot = __reduce_add_sync(0xffffffffu, tot);
   if (total_out) *total_out = tot;
   if (nnz <= 1) return 12.f;
   const float T = (float)tot;
