@@ -382,21 +382,33 @@ int run_frontend(bgpu_ctx* ctx, const Job& job, const EncParams& P, const uint8_
     const uint32_t max_npos = job.max_shard_len - 3;
     const dim3 gs((max_npos + SORT_TILE - 1) / SORT_TILE, n_shard), gp((max_npos + PROBE_TILE - 1) / PROBE_TILE, n_shard);
     const int bb = P.k.bucket_bits, nb0 = 1 << SORT_LOW_BITS, nb1 = 1 << (bb - SORT_LOW_BITS);
+    // depth <= 32 (q5, q6): packed sort entries — one u32 per entry between the passes and positions only into the probe
+    // (r5q: same order and same best[]; DRAM traffic of the stage 49.8 -> ~33 GB per GiB, time 45.6 -> 45.3 ms: the kernels
+    // are not DRAM-bound).  Deeper chains (q7-9) keep the (position, key bytes) pairs: their probe resolves 16..19-byte
+    // matches from shared memory, which the packed form sends to the input (q9: 233 -> 245 ms per GiB).
+    const bool packed = P.k.depth <= 32 && !(ctx->tune.flags & BGPU_F_SORT_UNPACKED);
+    const size_t sm = (size_t)(PROBE_TILE + P.k.depth) * 24;
     k_sort_hist<0><<<gs, 256, 0, st>>>(d_in, nullptr, d_sh, sh_hist, bb, 0, SORT_LOW_BITS);
     k_sort_scan<<<n_shard, 1024, 0, st>>>(d_sh, sh_hist, nb0);
-    k_sort_scatter<0><<<gs, 256, SORT_SCATTER_SMEM, st>>>(d_in, nullptr, nullptr, d_sh, sh_hist, sa_pos, sa_v, bb, 0, SORT_LOW_BITS);
+    if (packed) k_sort_scatter_packed<0><<<gs, 256, 0, st>>>(d_in, nullptr, d_sh, sh_hist, sa_pos, bb, SORT_LOW_BITS);
+    else k_sort_scatter<0><<<gs, 256, SORT_SCATTER_SMEM, st>>>(d_in, nullptr, nullptr, d_sh, sh_hist, sa_pos, sa_v, bb, 0, SORT_LOW_BITS);
     ctx->launches += 3; stage_mark(ctx, "k_sort_pass0");
-    k_sort_hist<1><<<gs, 256, 0, st>>>(d_in, sa_v, d_sh, sh_hist, bb, SORT_LOW_BITS, bb - SORT_LOW_BITS);
+    if (packed) k_sort_hist_packed<<<gs, 256, 0, st>>>(sa_pos, d_sh, sh_hist, bb - SORT_LOW_BITS);
+    else k_sort_hist<1><<<gs, 256, 0, st>>>(d_in, sa_v, d_sh, sh_hist, bb, SORT_LOW_BITS, bb - SORT_LOW_BITS);
     k_sort_scan<<<n_shard, 1024, 0, st>>>(d_sh, sh_hist, nb1);
-    k_sort_scatter<1><<<gs, 256, SORT_SCATTER_SMEM, st>>>(d_in, sa_pos, sa_v, d_sh, sh_hist, sb_pos, sb_v, bb, SORT_LOW_BITS, bb - SORT_LOW_BITS);
+    if (packed) k_sort_scatter_packed<1><<<gs, 256, 0, st>>>(d_in, sa_pos, d_sh, sh_hist, sb_pos, bb, bb - SORT_LOW_BITS);
+    else k_sort_scatter<1><<<gs, 256, SORT_SCATTER_SMEM, st>>>(d_in, sa_pos, sa_v, d_sh, sh_hist, sb_pos, sb_v, bb, SORT_LOW_BITS, bb - SORT_LOW_BITS);
     ctx->launches += 3; stage_mark(ctx, "k_sort_pass1");
-    if (!(ctx->tune.flags & BGPU_F_PROBE_WINDOW)) {
-      const size_t sm = (size_t)(PROBE_TILE + P.k.depth) * 24;
-      CK(cudaFuncSetAttribute(k_probe_diag, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-      k_probe_diag<<<gp, 256, sm, st>>>(d_in, d_sh, sb_pos, sb_v, best, P.k.depth, bb);
-    } else {
+    if (ctx->tune.flags & BGPU_F_PROBE_WINDOW) {   // the round-1 probe needs the key bytes: only with the unpacked sort
+      if (packed) { g_cuda_err = "BGPU_F_PROBE_WINDOW needs BGPU_F_SORT_UNPACKED at quality 5-6"; return BGPU_E_INVALID; }
       CK(cudaFuncSetAttribute(k_probe_sorted, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PROBE_SMEM));
       k_probe_sorted<<<gp, 256, PROBE_SMEM, st>>>(d_in, d_sh, sb_pos, sb_v, best, P.k.depth, bb);
+    } else if (packed) {
+      CK(cudaFuncSetAttribute(k_probe_diag<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+      k_probe_diag<true><<<gp, 256, sm, st>>>(d_in, d_sh, sb_pos, nullptr, best, P.k.depth, bb);
+    } else {
+      CK(cudaFuncSetAttribute(k_probe_diag<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+      k_probe_diag<false><<<gp, 256, sm, st>>>(d_in, d_sh, sb_pos, sb_v, best, P.k.depth, bb);
     }
     ctx->launches++; stage_mark(ctx, "k_probe");
   } else {

@@ -214,6 +214,119 @@ __global__ void __launch_bounds__(32 * WARPS, 2048 / (32 * WARPS) > 5 ? 5 : 2048
   }
 }
 
+// ---- Packed form of the two passes for the hash-chain path (q5-9): ONE u32 per entry between the passes.
+// A shard-relative position needs 22 bits (shards <= 4 MiB) and pass 1 only needs the key's high digit (<= 8 bits), so
+// pass 0 writes  position | high digit << 22  and pass 1 writes the bare position; the probe takes the 4 key bytes from
+// its own 16-byte gather.  Per entry and pass: 4 bytes written and read back instead of 8 (round 1: 49.8 GB of DRAM per
+// GiB for this stage, profiles/traffic.json), and one reorder array in shared memory instead of two.
+//   k_sort_hist_packed          digit histogram of pass 1 from the packed entries
+//   k_sort_scatter_packed<0>    input -> packed entries, ordered by the low 7 key bits
+//   k_sort_scatter_packed<1>    packed entries -> positions, ordered by the whole key
+constexpr int SORT_POS_BITS = 22;
+__global__ void __launch_bounds__(256) k_sort_hist_packed(const uint32_t* __restrict__ src, const ShardD* __restrict__ shards, uint32_t* __restrict__ hist, int nbits) {
+  __shared__ uint32_t s_h[SORT_BINS];
+  const ShardD sh = shards[blockIdx.y];
+  const uint32_t npos = shard_npos(sh), n_stile = shard_nstile(sh), tile = blockIdx.x;
+  if (tile >= n_stile) return;
+  s_h[threadIdx.x] = 0;
+  __syncthreads();
+  const uint32_t base = tile * SORT_TILE;
+  const uint32_t* sv = src + sh.in_off;
+#pragma unroll 4
+  for (uint32_t k = 0; k < SORT_TILE / 256; k++) {
+    const uint32_t e = base + k * 256 + threadIdx.x;
+    if (e < npos) atomicAdd(&s_h[__ldg(sv + e) >> SORT_POS_BITS], 1u);
+  }
+  __syncthreads();
+  const uint32_t nb = 1u << nbits;
+  if (threadIdx.x < nb) hist[(size_t)sh.first_stile * SORT_BINS + (size_t)threadIdx.x * n_stile + tile] = s_h[threadIdx.x];
+}
+
+template <int PASS>
+__global__ void __launch_bounds__(256, 5) k_sort_scatter_packed(const uint8_t* __restrict__ in, const uint32_t* __restrict__ src,
+                                                             const ShardD* __restrict__ shards, const uint32_t* __restrict__ hist,
+                                                             uint32_t* __restrict__ dst, int bucket_bits, int nbits) {
+  constexpr int WARPS = 8, ROUNDS = SORT_TILE / 256;
+  constexpr uint32_t SLICE = SORT_TILE / WARPS;
+  __shared__ uint16_t s_cnt[WARPS][SORT_BINS];
+  __shared__ uint32_t s_base[SORT_BINS];
+  __shared__ uint32_t s_goff[SORT_BINS];
+  __shared__ uint32_t s_e[SORT_TILE];      // reorder buffer: the entries as they will be stored ...
+  __shared__ uint8_t s_d[SORT_TILE];       // ... and their digit of this pass
+  __shared__ uint32_t s_ws[8];
+  const ShardD sh = shards[blockIdx.y];
+  const uint32_t npos = shard_npos(sh), n_stile = shard_nstile(sh), tile = blockIdx.x;
+  if (tile >= n_stile) return;
+  const uint32_t tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+  const uint32_t nb = 1u << nbits;
+  for (uint32_t i = tid; i < WARPS * SORT_BINS / 2; i += 256) reinterpret_cast<uint32_t*>(&s_cnt[0][0])[i] = 0;
+  const uint32_t goff = tid < nb ? hist[(size_t)sh.first_stile * SORT_BINS + (size_t)tid * n_stile + tile] : 0;
+  __syncthreads();
+  const uint32_t base = tile * SORT_TILE;
+  const uint8_t* sin = in + sh.in_off;
+  // v[r]: the entry as it leaves this pass; dg[r]: its digit in this pass
+  uint32_t v[ROUNDS]; uint16_t rk[ROUNDS]; uint8_t dg[ROUNDS];
+#pragma unroll
+  for (int r = 0; r < ROUNDS; r++) {
+    const uint32_t e = base + w * SLICE + r * 32 + lane;
+    if (PASS == 0) {
+      const uint32_t key = e < npos ? hash4(ld32u(sin, e), bucket_bits) : 0;
+      dg[r] = (uint8_t)(key & ((1u << SORT_LOW_BITS) - 1));
+      v[r] = e | ((key >> SORT_LOW_BITS) << SORT_POS_BITS);
+    } else {
+      const uint32_t x = e < npos ? __ldg(src + sh.in_off + e) : 0;
+      dg[r] = (uint8_t)(x >> SORT_POS_BITS);
+      v[r] = x & ((1u << SORT_POS_BITS) - 1);
+    }
+  }
+#pragma unroll
+  for (int r = 0; r < ROUNDS; r++) {
+    const uint32_t e = base + w * SLICE + r * 32 + lane;
+    const bool valid = e < npos;
+    const uint32_t d = valid ? (uint32_t)dg[r] : (0x10000u | lane);
+    const uint32_t peers = __match_any_sync(0xffffffffu, d);
+    const uint32_t before = __popc(peers & ((1u << lane) - 1));
+    uint32_t b = 0;
+    if (valid) b = s_cnt[w][d];
+    __syncwarp();
+    if (valid && (peers >> lane) == 1u) s_cnt[w][d] = (uint16_t)(b + __popc(peers));
+    __syncwarp();
+    rk[r] = (uint16_t)(b + before);
+  }
+  __syncthreads();
+  uint32_t tot = 0;
+  if (tid < nb) {
+#pragma unroll
+    for (int ww = 0; ww < WARPS; ww++) { uint32_t c = s_cnt[ww][tid]; s_cnt[ww][tid] = (uint16_t)tot; tot += c; }
+  }
+  uint32_t incl = tot;
+  for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, incl, o); if (lane >= (uint32_t)o) incl += y; }
+  if (lane == 31) s_ws[w] = incl;
+  tot = incl - tot;
+  __syncthreads();
+  {
+    uint32_t wb = 0;
+    for (uint32_t i = 0; i < w; i++) wb += s_ws[i];
+    s_base[tid] = wb + tot;
+    s_goff[tid] = goff - (wb + tot);
+  }
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < ROUNDS; r++) {
+    const uint32_t e = base + w * SLICE + r * 32 + lane;
+    if (e < npos) {
+      const uint32_t d = dg[r];
+      const uint32_t lp = s_base[d] + s_cnt[w][d] + rk[r];
+      s_e[lp] = v[r]; s_d[lp] = (uint8_t)d;
+    }
+  }
+  __syncthreads();
+  const uint32_t nvalid = min(SORT_TILE, npos - base);
+  uint32_t* dp = dst + sh.in_off;
+#pragma unroll 4
+  for (uint32_t j = tid; j < nvalid; j += 256) dp[s_goff[s_d[j]] + j] = s_e[j];
+}
+
 // Window probe over the key-sorted entries of a shard.  grid (ceil(max npos / PROBE_TILE), shards).
 // Every entry of the tile (and of the halo of `depth` entries before it) first fetches the 16 input
 // bytes that follow its 4 key bytes into shared memory — the only random input reads of the common
@@ -449,6 +562,7 @@ __global__ void __launch_bounds__(256, PROBE_MIN_BLOCKS) k_probe_sorted(const ui
 //   * matches of >= 20 bytes are deferred to the input as in k_probe_sorted.
 // Issue-bound (r5e: issue active 84 %, 28 warp instructions per position at depth 16).
 // Shared memory: (PROBE_TILE + depth) * 24 bytes.
+template <uint32_t HAVE>   // bytes known equal from shared memory: 20 (key bytes + the 16 after them) or 16 (packed sort: 16 from the position)
 __device__ __forceinline__ void probe_deferred(const uint8_t* sin, const uint32_t* s_p, uint32_t i0, uint32_t jc, uint32_t p, uint32_t mlen, uint32_t lm,
                                                uint32_t& bLen, uint32_t& bDist, int& bScore) {
   while (lm) {   // newest first
@@ -460,12 +574,12 @@ __device__ __forceinline__ void probe_deferred(const uint8_t* sin, const uint32_
     // wins, so ">=" when the current best is nearer, ">" when it is farther.
     const int ub = 135 * (int)mlen + dcost;
     if (ub < bScore || (ub == bScore && bDist <= backward)) continue;
-    const uint32_t len = 20 + match_len16(sin, p + 20, c + 20, mlen - 20);
+    const uint32_t len = HAVE + match_len16(sin, p + HAVE, c + HAVE, mlen - HAVE);
     const int score = 135 * (int)len + dcost;
     if (score > bScore || (score == bScore && backward < bDist)) { bScore = score; bLen = len; bDist = backward; }
   }
 }
-template <bool EDGE>
+template <bool EDGE, uint32_t HAVE>
 __device__ __forceinline__ void probe_entry(const uint8_t* sin, const uint4* s_x, const uint32_t* s_p, const uint32_t* s_v, uint32_t i0, uint32_t g,
                                             uint32_t shard_len, int depth, uint32_t* sbest) {
   const uint32_t v = s_v[i0], p = s_p[i0];
@@ -483,8 +597,8 @@ __device__ __forceinline__ void probe_entry(const uint8_t* sin, const uint4* s_x
         const uint4 cx = s_x[ci];
         const uint32_t backward = p - cp;
         const bool near = backward <= MAX_BACKWARD;
-        uint32_t len = 4 + prefix16(x, cx);
-        if (len == 20 && mlen > 20) { if (near) lm |= 1u << jj; }
+        uint32_t len = (HAVE - 16) + prefix16(x, cx);
+        if (len == HAVE && mlen > HAVE) { if (near) lm |= 1u << jj; }
         else {
           len = min(len, mlen);
           if (len > bLen) {
@@ -494,10 +608,13 @@ __device__ __forceinline__ void probe_entry(const uint8_t* sin, const uint4* s_x
         }
       }
     }
-    probe_deferred(sin, s_p, i0, jc, p, mlen, lm, bLen, bDist, bScore);
+    probe_deferred<HAVE>(sin, s_p, i0, jc, p, mlen, lm, bLen, bDist, bScore);
   }
   sbest[p] = (bLen << 24) | bDist;
 }
+// PACKED: the entries come from the packed sort (positions only); the 4 key bytes are the first word of the entry's own
+// 16-byte gather, which then starts AT the position (matches of >= 16 bytes go to the input instead of >= 20).
+template <bool PACKED>
 __global__ void __launch_bounds__(256, 6) k_probe_diag(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
                                                       const uint32_t* __restrict__ srt_pos, const uint32_t* __restrict__ srt_v,
                                                       uint32_t* __restrict__ best, int depth, int bucket_bits) {
@@ -528,21 +645,22 @@ __global__ void __launch_bounds__(256, 6) k_probe_diag(const uint8_t* __restrict
       const int64_t g = (int64_t)g0 - halo + i;
       ok[t] = i < n_ent && g >= 0 && g < (int64_t)npos;
       pp[t] = ok[t] ? __ldg(sp + g) : 0;
-      vv[t] = ok[t] ? __ldg(sv + g) : 0;
+      vv[t] = (ok[t] && !PACKED) ? __ldg(sv + g) : 0;
     }
 #pragma unroll
-    for (int t = 0; t < NST; t++) xx[t] = ok[t] ? ld128v(sin + pp[t] + 4) : make_uint4(0, 0, 0, 0);   // reads <= 36 bytes past p: inside the padded input
+    for (int t = 0; t < NST; t++) xx[t] = ok[t] ? ld128v(sin + pp[t] + (PACKED ? 0 : 4)) : make_uint4(0, 0, 0, 0);   // reads <= 36 bytes past p: inside the padded input
 #pragma unroll
     for (int t = 0; t < NST; t++) {
       const uint32_t i = tid + 256 * t;
-      if (i < n_ent) { s_p[i] = pp[t]; s_v[i] = vv[t]; s_x[i] = xx[t]; }
+      if (i < n_ent) { s_p[i] = pp[t]; s_v[i] = PACKED ? xx[t].x : vv[t]; s_x[i] = xx[t]; }
     }
   }
   __syncthreads();
+  constexpr uint32_t HAVE = PACKED ? 16 : 20;
   if (g0 < halo) {
-    for (uint32_t r = 0; r < PROBE_TILE / 256; r++) { const uint32_t e = r * 256 + tid; if (g0 + e < npos) probe_entry<true>(sin, s_x, s_p, s_v, halo + e, g0 + e, sh.len, depth, sbest); }
+    for (uint32_t r = 0; r < PROBE_TILE / 256; r++) { const uint32_t e = r * 256 + tid; if (g0 + e < npos) probe_entry<true, HAVE>(sin, s_x, s_p, s_v, halo + e, g0 + e, sh.len, depth, sbest); }
   } else {
-    for (uint32_t r = 0; r < PROBE_TILE / 256; r++) { const uint32_t e = r * 256 + tid; if (g0 + e < npos) probe_entry<false>(sin, s_x, s_p, s_v, halo + e, g0 + e, sh.len, depth, sbest); }
+    for (uint32_t r = 0; r < PROBE_TILE / 256; r++) { const uint32_t e = r * 256 + tid; if (g0 + e < npos) probe_entry<false, HAVE>(sin, s_x, s_p, s_v, halo + e, g0 + e, sh.len, depth, sbest); }
   }
 }
 

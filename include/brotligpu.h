@@ -54,6 +54,7 @@ typedef struct bgpu_tuning {
 #define BGPU_F_PRIO_MODEL 128u       /* lanes: the modelling phase (block split .. header) of each lane runs on a high-priority side stream (A/B runs) */
 #define BGPU_F_WRITER_TWO_PASS 256u   /* bit writer q5-11: the round-1 two-pass writer (k_tilebits2 + k_write2 recompute every token) instead of k_tile_pack + k_tile_copy (A/B runs; same bytes) */
 #define BGPU_F_SPLIT_3ITER 1024u     /* block split q5-8: the reference's 3 refinement iterations instead of 2 (size -0.007 points, step +6 %) */
+#define BGPU_F_SORT_UNPACKED 2048u   /* match finding q5-6: (position, key bytes) pairs between the sort passes, as q7-9 and round 1 (A/B runs; same best[]) */
 #define BGPU_F_NO_REFINE 32u         /* greedy parse: skip the second pass over segments that start inside a running copy (A/B runs) */
 #define BGPU_F_MODEL_STATS 8u        /* bench: after the call bgpu_last_counter(1..3) hold the table bytes of the clustering / Huffman stages (one extra tiny kernel + a blocking read-back) */
 #define BGPU_F_VERIFY 16u            /* after encoding, every shard is decoded ON THE DEVICE (csrc/decode.cuh, one thread per shard) and compared with the

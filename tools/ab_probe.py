@@ -9,14 +9,14 @@ bad = 0
 for name, data in inputs:
     for q in (5, 6, 7, 9):
         ctx.set_tuning(flags=0); a = ctx.stage_match_candidates(data, q, 22)
-        ctx.set_tuning(flags=64); b = ctx.stage_match_candidates(data, q, 22)
+        ctx.set_tuning(flags=64 | 2048); b = ctx.stage_match_candidates(data, q, 22)
         same = all(np.array_equal(x, y) for x, y in zip(a, b))
         if not same:
             bad += 1; print("MISMATCH", name, q, [int((x != y).sum()) for x, y in zip(a, b)])
 print("mismatches:", bad)
 big = np.concatenate([W.mixed_segment(i % 8, i // 8) for i in range(64)])   # 256 MiB of config 2
 for q in (5, 9):
-    for flags in (0, 64, 0, 64):
+    for flags in (0, 2048, 64 | 2048, 0):
         ctx.set_tuning(flags=flags, lanes=1)
         ctx.encode(big, q, 22, 0)
         t = dict(ctx.timings())

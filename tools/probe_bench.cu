@@ -88,10 +88,28 @@ int main(int argc, char** argv) {
   CKX(cudaFuncSetAttribute(k_probe_sorted, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)PROBE_SMEM));
   timed("k_probe_sorted", [&] { k_probe_sorted<<<gp, 256, PROBE_SMEM>>>(d_in, d_sh, sb_pos, sb_v, ref, depth, bb); });
   const size_t sm = (size_t)(PROBE_TILE + depth) * 24;
-  CKX(cudaFuncSetAttribute(k_probe_diag, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+  CKX(cudaFuncSetAttribute(k_probe_diag<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+  CKX(cudaFuncSetAttribute(k_probe_diag<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
   CKX(cudaMemset(best, 0xFF, n * 4));
-  timed("k_probe_diag", [&] { k_probe_diag<<<gp, 256, sm>>>(d_in, d_sh, sb_pos, sb_v, best, depth, bb); });
+  timed("k_probe_diag", [&] { k_probe_diag<false><<<gp, 256, sm>>>(d_in, d_sh, sb_pos, sb_v, best, depth, bb); });
   check("k_probe_diag", best);
+  {   // packed sort: one u32 per entry between the passes; sa_v / best reused as its buffers
+    uint32_t* pk = sa_v; uint32_t* ppos = sa_pos;
+    timed("packed sort, both passes", [&] {
+      k_sort_hist<0><<<gs, 256>>>(d_in, nullptr, d_sh, hist, bb, 0, SORT_LOW_BITS);
+      k_sort_scan<<<n_shard, 1024>>>(d_sh, hist, nb0);
+      k_sort_scatter_packed<0><<<gs, 256>>>(d_in, nullptr, d_sh, hist, pk, bb, SORT_LOW_BITS);
+      k_sort_hist_packed<<<gs, 256>>>(pk, d_sh, hist, bb - SORT_LOW_BITS);
+      k_sort_scan<<<n_shard, 1024>>>(d_sh, hist, nb1);
+      k_sort_scatter_packed<1><<<gs, 256>>>(d_in, pk, d_sh, hist, ppos, bb, bb - SORT_LOW_BITS);
+    });
+    unsigned long long s2[2]; const uint32_t* arr[2] = {sb_pos, ppos};
+    for (int k = 0; k < 2; k++) { cudaMemset(d_sum, 0, 8); k_checksum<<<1024, 256>>>(arr[k], n - 3, d_sum); cudaMemcpy(&s2[k], d_sum, 8, cudaMemcpyDeviceToHost); }
+    printf("    packed sort: %s\n", s2[0] == s2[1] ? "same order" : "DIFFERENT order");
+    CKX(cudaMemset(best, 0xFF, n * 4));
+    timed("k_probe_diag<packed>", [&] { k_probe_diag<true><<<gp, 256, sm>>>(d_in, d_sh, ppos, nullptr, best, depth, bb); });
+    check("k_probe_diag<packed>", best);
+  }
   run_variants(d_in, d_sh, sb_pos, sb_v, best, depth, bb, max_npos, n_shard, timed, check);
   CKX(cudaDeviceSynchronize());
   return 0;
