@@ -12,7 +12,7 @@
 // reference, not to bit parity.  The B200 formulation therefore keeps the
 // reference's structure where it parallelises and replaces what does not (DESIGN.md "Modelling"):
 //   * findBlocks runs over GRANULES of 128 literals / 16 commands / 16 distances instead of single
-//     symbols, in independent chunks of 2048 granules, one warp per chunk (64 entropy codes = 2 per
+//     symbols, in independent chunks of 512 granules, one warp per chunk (64 entropy codes = 2 per
 //     lane, warp-min by redux).  The per-symbol switch bitmap of the reference (8 B per symbol)
 //     becomes 8 B per granule.
 //   * entropy codes are seeded from contiguous slices of the stream, not from an LCG sample.
@@ -29,7 +29,7 @@
 namespace bgpu {
 
 constexpr int SPLIT_MAXK = 64;          // entropy codes per split problem
-constexpr int SPLIT_CHUNK = 2048;       // granules per DP chunk (one warp)
+constexpr int SPLIT_CHUNK = 512;       // granules per DP chunk (one warp)
 constexpr int MAX_BLOCKS = 2048;        // blocks per (metablock, category)
 constexpr int CL_BATCH = 64;
 constexpr int CL_FINAL_MAX = 256;
