@@ -289,6 +289,12 @@ int run_backend(bgpu_ctx* ctx, const Job& job, const EncParams& P, const uint8_t
 
 int upload_plan(bgpu_ctx* ctx, const Job& job) {
   int rc;
+  // shards, metablocks and 3 x metablocks are gridDim.y of the kernels (<= 65535).  Batches are split on the host and large
+  // streams run as lane groups of <= 64 shards, so this is only reached with lanes off and tiny shards (lgwin 10: ~66 MB)
+  if (job.shards.size() > 65535 || job.mbs.size() * 3 > 65535) {
+    g_cuda_err = "one device job is limited to 65535 shards and 21845 metablocks (use the default lanes, or larger shards / metablocks)";
+    return BGPU_E_INVALID;
+  }
   if ((rc = upload(ctx, ctx->shards, job.shards.data(), job.shards.size() * sizeof(ShardD)))) return rc;
   if ((rc = upload(ctx, ctx->mbs, job.mbs.data(), job.mbs.size() * sizeof(MbD)))) return rc;
   if ((rc = upload(ctx, ctx->segs, job.segs.data(), job.segs.size() * sizeof(SegD)))) return rc;
@@ -696,6 +702,27 @@ int bgpu_encode_batch(bgpu_ctx* c, int count, const uint8_t* const* in, const si
     } else { map.push_back(i); lens.push_back(n[i]); ptrs.push_back(in[i]); }
   }
   if (map.empty()) return result;
+  // Shards, metablocks and 3 x metablocks index gridDim.y (<= 65535) in the kernels: a batch of many streams goes to the
+  // device as several jobs of at most BATCH_JOB_STREAMS streams, each holding at most BATCH_JOB_BYTES.
+  if (lens.size() > 1) {
+    constexpr size_t BATCH_JOB_STREAMS = 8192, BATCH_JOB_BYTES = (size_t)8 << 30;
+    size_t first = 0, bytes = 0, cnt = 0; bool split = false;
+    for (size_t s = 0; s < lens.size(); s++) { bytes += lens[s]; cnt++; if (cnt > BATCH_JOB_STREAMS || bytes > BATCH_JOB_BYTES) { split = true; break; } }
+    if (split) {
+      while (first < lens.size()) {
+        size_t last = first, b = 0;
+        while (last < lens.size() && last - first < BATCH_JOB_STREAMS && (last == first || b + lens[last] <= BATCH_JOB_BYTES)) b += lens[last++];
+        const int k = (int)(last - first);
+        std::vector<const uint8_t*> in_k(k); std::vector<size_t> n_k(k), cap_k(k), len_k(k, 0); std::vector<uint8_t*> out_k(k);
+        for (int i = 0; i < k; i++) { const int o = map[first + i]; in_k[i] = ptrs[first + i]; n_k[i] = lens[first + i]; out_k[i] = out[o]; cap_k[i] = out_cap[o]; }
+        rc = bgpu_encode_batch(c, k, in_k.data(), n_k.data(), quality, lgwin, mode, out_k.data(), cap_k.data(), len_k.data());
+        for (int i = 0; i < k; i++) out_len[map[first + i]] = len_k[i];
+        if (rc == BGPU_E_OUTPUT_TOO_SMALL) result = rc; else if (rc) return rc;
+        first = last;
+      }
+      return result;
+    }
+  }
   if (lens.size() == 1 && multi_apply(c, P, lens[0])) {
     rc = encode_multi(c, ptrs[0], lens[0], P, out[map[0]], out_cap[map[0]], &out_len[map[0]]);
     return rc ? rc : result;

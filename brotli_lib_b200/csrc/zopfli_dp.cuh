@@ -3,6 +3,9 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#ifndef ZOP_DP_BLOCKS
+#define ZOP_DP_BLOCKS 8
+#endif
 namespace bgpu {
 
 constexpr uint32_t ZOP_W = 512;   // node costs of [i, i + ZOP_W) live in shared memory (power of two)
@@ -37,7 +40,7 @@ __device__ __forceinline__ void zop_relax(uint4* __restrict__ nodes, float* __re
 // the H10 list header of a position come from registers loaded 32 positions at a time; the match
 // entries of position i + 1 are fetched while position i is processed.  What stays on the chain is
 // one L2 round trip for the distance-cache probes.
-__global__ void __launch_bounds__(128, 8) k_zop_dp(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
+__global__ void __launch_bounds__(128, ZOP_DP_BLOCKS) k_zop_dp(const uint8_t* __restrict__ in, const ShardD* __restrict__ shards,
                                                 const SegD* __restrict__ segs, uint32_t n_seg, H10Out O,
                                                 const float* __restrict__ model, const float* __restrict__ lc,
                                                 uint4* __restrict__ nodes, int4* __restrict__ ringarr, uint8_t* __restrict__ role,

@@ -94,7 +94,9 @@ size_t bgpu_max_compressed_size(size_t n);
 int bgpu_encode(bgpu_ctx* ctx, const uint8_t* in, size_t n, int quality, int lgwin, int mode,
                 uint8_t* out, size_t out_cap, size_t* out_len);
 
-/* Batch of independent streams (BASELINE config 5): item i is brotliEncode(in[i], ...). */
+/* Batch of independent streams (BASELINE config 5): item i is brotliEncode(in[i], ...).  Batches of more than 8192 streams (or 8 GiB) are
+ * run as several device jobs; one device job holds at most 65535 shards / 21845 metablocks (BGPU_E_INVALID beyond: only
+ * reachable with lanes switched off and tiny shards). */
 int bgpu_encode_batch(bgpu_ctx* ctx, int count, const uint8_t* const* in, const size_t* n,
                       int quality, int lgwin, int mode, uint8_t* const* out, const size_t* out_cap,
                       size_t* out_len);

@@ -514,3 +514,18 @@ def test_streaming_blocks_and_window_carry_over(gpu_ctx):
         enc = B.BrotliEncoder(quality=5, lgwin=lgwin, context=gpu_ctx)
         parts = [enc.update(small[i:i + 7001]) for i in range(0, len(small), 7001)] + [enc.finish()]
         _rt(b"".join(parts), small)
+
+
+def test_batch_larger_than_one_device_job(gpu_ctx):
+    """More streams than one device job holds (shards index gridDim.y; bgpu_encode_batch runs such a batch as several
+    jobs of <= 8192 streams): every stream is still its own valid Brotli stream, in the caller's order."""
+    rng = np.random.default_rng(5)
+    words = [bytes(rng.integers(97, 123, int(rng.integers(2, 9))).astype(np.uint8)) for _ in range(200)]
+    items = []
+    for i in range(8192 + 700):
+        k = int(rng.integers(20, 60))
+        items.append(b" ".join(words[int(j)] for j in rng.integers(0, 200, k)) + str(i).encode())
+    outs = gpu_ctx.encode_batch(items, 5, 22, 0)
+    assert len(outs) == len(items)
+    for i in list(range(0, len(items), 97)) + [8191, 8192, len(items) - 1]:
+        assert O.decode(outs[i], len(items[i])) == items[i], i
