@@ -179,29 +179,67 @@ __global__ void __launch_bounds__(256) k_mb_compact(const uint8_t* __restrict__ 
   const uint32_t ex = incl - packed;
   const uint32_t* tb = M.tile_base + (tile - M.first_tile) * 3;
   uint32_t il = tb[0] + bl + (ex & 2047), ic = tb[1] + bc + ((ex >> 11) & 2047), id = tb[2] + bd + (ex >> 22);
+  // By kind, not by position (the lanes of a warp hold different roles at every position; r5m: 19 of 32 lanes active):
+  // all literals of the thread from two aligned words, then its command starts, then its copy starts.  The streams are
+  // indexed by rank, so the three kinds are independent.
+  const uint64_t p0 = sh.in_off + tile_rel + 4 * tid;
+  if ((r[0] | r[1] | r[2] | r[3]) & 1) {
+    const uint32_t w1 = *reinterpret_cast<const uint32_t*>(in + p0);
+    const uint32_t w0 = p0 >= 4 ? *reinterpret_cast<const uint32_t*>(in + p0 - 4) : 0u;
+    const uint64_t six = ((uint64_t)w1 << 32) | w0;   // byte j = in[p0 - 4 + j]
 #pragma unroll
-  for (int k = 0; k < 4; k++) {
-    if (!r[k]) continue;
-    const uint32_t rel = tile_rel + 4 * tid + k;
-    const uint64_t p = sh.in_off + rel;
-    if (r[k] & 4) {
-      const uint32_t ins = ins_at[p >> P.sh];
-      M.csym[ic++] = (uint16_t)((r[k] & 8) ? insert_only_prefix(ins) : cmds[(p + ins) >> P.sh].cmdPrefix);
+    for (int k = 0; k < 4; k++) {
+      if (r[k] & 1) {
+        // literal context from the two previous bytes of the stream (context.ts:169-171); (0, 0) at the stream start
+        const uint64_t p = p0 + k;
+        const bool s1 = M.stream_start && p == M.abs, s2 = M.stream_start && p <= M.abs + 1;
+        const uint32_t p1 = s1 ? 0 : (uint32_t)(six >> (8 * (k + 3))) & 0xFF, p2 = s2 ? 0 : (uint32_t)(six >> (8 * (k + 2))) & 0xFF;
+        M.clit[il] = (uint8_t)(six >> (8 * (k + 4)));
+        M.clctx[il] = lut[p1] | lut[256 + p2];
+        il++;
+      }
     }
-    if (r[k] & 1) {
-      // literal context from the two previous bytes of the stream (context.ts:169-171); (0, 0) at the stream start
-      const bool s1 = M.stream_start && p == M.abs, s2 = M.stream_start && p <= M.abs + 1;
-      const uint32_t p1 = s1 ? 0 : in[p - 1], p2 = s2 ? 0 : in[p - 2];
-      M.clit[il] = in[p];
-      M.clctx[il] = lut[p1] | lut[256 + p2];
-      il++;
+  }
+  // the first command start / copy start of the thread is handled outside the position loop, so that the body runs once
+  // per thread whatever position it sits at; further ones (q10/11: copies of 2 bytes) take the loop
+  if (nc) {
+    const int kc = (r[0] & 4) ? 0 : (r[1] & 4) ? 1 : (r[2] & 4) ? 2 : 3;
+    const uint32_t rc = kc == 0 ? r[0] : kc == 1 ? r[1] : kc == 2 ? r[2] : r[3];
+    const uint64_t p = p0 + kc;
+    const uint32_t ins = ins_at[p >> P.sh];
+    M.csym[ic++] = (uint16_t)((rc & 8) ? insert_only_prefix(ins) : cmds[(p + ins) >> P.sh].cmdPrefix);
+    if (nc > 1) {
+#pragma unroll
+      for (int k = 1; k < 4; k++) {
+        if (k > kc && (r[k] & 4)) {
+          const uint64_t q = p0 + k;
+          const uint32_t ins2 = ins_at[q >> P.sh];
+          M.csym[ic++] = (uint16_t)((r[k] & 8) ? insert_only_prefix(ins2) : cmds[(q + ins2) >> P.sh].cmdPrefix);
+        }
+      }
     }
-    if (cmd_has_dist(r[k], pre[k])) {
-      const Cmd c = cmds[p >> P.sh];
+  }
+  if (nd) {
+    const bool h0 = cmd_has_dist(r[0], pre[0]), h1 = cmd_has_dist(r[1], pre[1]), h2 = cmd_has_dist(r[2], pre[2]);
+    const int kd = h0 ? 0 : h1 ? 1 : h2 ? 2 : 3;
+    {
+      const Cmd c = cmds[(p0 + kd) >> P.sh];
       const uint32_t copyLen = c.copyLen & 0x1FFFFFF;
       M.dsym[id] = c.distPrefix & 0x3FF;
       M.ddctx[id] = (uint8_t)(copyLen > 4 ? 3 : copyLen - 2);   // metablock.ts:622
       id++;
+    }
+    if (nd > 1) {
+#pragma unroll
+      for (int k = 1; k < 4; k++) {
+        if (k > kd && cmd_has_dist(r[k], pre[k])) {
+          const Cmd c = cmds[(p0 + k) >> P.sh];
+          const uint32_t copyLen = c.copyLen & 0x1FFFFFF;
+          M.dsym[id] = c.distPrefix & 0x3FF;
+          M.ddctx[id] = (uint8_t)(copyLen > 4 ? 3 : copyLen - 2);
+          id++;
+        }
+      }
     }
   }
 }
